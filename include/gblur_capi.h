@@ -1,0 +1,110 @@
+/* gblur_capi.h — C ABI of the B200-native LibGaussianBlur hot path.
+ *
+ * This is the drop-in boundary: the only way host code (the C++ gaussianblur:: API in
+ * include/gaussianblur/, the pybind11 module, the Python/ctypes layer, a foreign-language FFI)
+ * reaches the sm_100a kernels. Plain pointers and sizes only; opaque plan handle; int status
+ * (0 = ok, otherwise a GBLUR_E_* code with text from gblur_last_error()). There is NO CPU
+ * fallback behind any of these calls: without a CUDA device they fail with GBLUR_E_CUDA.
+ *
+ * What each entry point replaces in the reference (paths under /root/reference/):
+ *   gblur_plan_create        prepare_kernel_DFT                src/gaussianblur.cpp:100-172
+ *                            (+ pffft_new_setup twiddles       include/pffft_pommier/pffft.c:1231-1280)
+ *   gblur_plan_info          KernelDFT.pad / .trailing_zeros   include/gaussianblur/helpers.hpp:125-132
+ *   gblur_plan_spectrum      KernelDFT.kerf_1D_col / _row      include/gaussianblur/helpers.hpp:126-127
+ *   gblur_run_host           gaussianblur::gaussianblur        src/gaussianblur.cpp:307-325
+ *   gblur_run_device         the same, device-resident buffers (deinterleave :174-200, pffft driver
+ *                            :246-287, process_channel_tiles :202-244, interleave :289-305)
+ *   gblur_run_batch_device   a loop of the above over frames with ONE kernel spectrum (additive)
+ *   gblur_rowpass_device     process_channel_tiles, first call  src/gaussianblur.cpp:268-272
+ *   gblur_colpass_device     process_channel_tiles, second call src/gaussianblur.cpp:275-279
+ *   gblur_dump_intermediate  (test hook) the fp32 plane after pass 1
+ */
+#ifndef GBLUR_CAPI_H_
+#define GBLUR_CAPI_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gblur_plan gblur_plan;
+
+enum {
+  GBLUR_OK = 0,
+  GBLUR_E_INVALID = 1,     /* bad argument (null pointer, sigma <= 0, channels not in {1,3,4}, ...) */
+  GBLUR_E_PRECOND = 2,     /* pad > min(rows, cols) - 1: the reference reads out of bounds here      */
+  GBLUR_E_UNSUPPORTED = 3, /* FFT length does not fit one CTA's shared memory (yet)                  */
+  GBLUR_E_CUDA = 4         /* CUDA runtime failure, including "no device"                            */
+};
+
+/* Geometry + sigma -> immutable plan on `device`: reference window/pad/FFT-length rules, kernel
+ * spectra, twiddles, workspace for `max_frames` frames. channels in {1,3,4} (1 is additive). */
+int gblur_plan_create(gblur_plan** out, int device, int rows, int cols, int channels, float sigma);
+int gblur_plan_create_batch(gblur_plan** out, int device, int rows, int cols, int channels, float sigma,
+                            int max_frames);
+/* Band plan for row-band sharding of one (full_rows x full_cols) image: window, pad and FFT
+ * lengths come from the FULL geometry; the row pass runs on `band_rows` rows, the column pass on
+ * `band_cols` pixel columns. */
+int gblur_plan_create_band(gblur_plan** out, int device, int full_rows, int full_cols, int channels, float sigma,
+                           int band_rows, int band_cols);
+void gblur_plan_destroy(gblur_plan* plan);
+
+/* Any out pointer may be NULL. n_rowpass = FFT length along a row (the reference's sizes[1]),
+ * n_colpass = along a column (sizes[0]); tz_* are KernelDFT.trailing_zeros.{rows,cols}. */
+int gblur_plan_info(const gblur_plan* plan, int* ksize, int* pad, int* n_rowpass, int* n_colpass, int* tz_rows,
+                    int* tz_cols);
+/* axis 0: kerf_1D_col (n_rowpass floats), axis 1: kerf_1D_row (n_colpass floats); pffft "ordered"
+ * layout [K0, K_{N/2}, Re1, Im1, ...] (include/pffft_pommier/pffft.h:143-146). */
+int gblur_plan_spectrum(const gblur_plan* plan, int axis, float* host_out);
+/* Stage radices chosen for an axis (for logs/tests): writes up to 5 ints, returns count via *n. */
+int gblur_plan_radices(const gblur_plan* plan, int axis, int* radices, int* n, int* static_kernel);
+
+/* Host buffer in place: H2D, blur, D2H, synchronous. */
+int gblur_run_host(gblur_plan* plan, uint8_t* hwc_inout, int apply_to_alpha);
+int gblur_run_batch_host(gblur_plan* plan, uint8_t* hwc_inout, int n_frames, int apply_to_alpha);
+/* Device buffers (d_in may equal d_out); asynchronous on `cuda_stream` (a cudaStream_t, may be 0). */
+int gblur_run_device(gblur_plan* plan, const uint8_t* d_in, uint8_t* d_out, int apply_to_alpha, void* cuda_stream);
+int gblur_run_batch_device(gblur_plan* plan, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
+                           void* cuda_stream);
+
+/* The two passes separately, for band sharding. Row pass: u8 [band_rows][cols*channels] ->
+ * fp32 [band_rows][inter_pitch] with element (r, x*Cp + ch), Cp = processed channels.
+ * Column pass: fp32 [full_rows][inter_pitch] holding band_cols*Cp valid columns -> u8
+ * [full_rows][out_pitch bytes] with band_cols*channels valid bytes per row. */
+int gblur_rowpass_device(gblur_plan* plan, const uint8_t* d_in, float* d_inter, long long inter_pitch_floats,
+                         int apply_to_alpha, void* cuda_stream);
+int gblur_colpass_device(gblur_plan* plan, const float* d_inter, long long inter_pitch_floats, uint8_t* d_out,
+                         long long out_pitch_bytes, int apply_to_alpha, void* cuda_stream);
+
+/* Test hook: fp32 row-pass output of the last gblur_run_* call on this plan (frame 0), copied to
+ * host as [rows][cols*Cp]. */
+int gblur_dump_intermediate(gblur_plan* plan, float* host_out, int apply_to_alpha);
+
+/* Kernels launched through this library since load (bench.py reports the delta). */
+unsigned long long gblur_launch_count(void);
+/* Thread-local message for the last non-zero status. */
+const char* gblur_last_error(void);
+/* Number of CUDA devices visible, or -1 with an error message. */
+int gblur_device_count(void);
+
+/* ---- host-only helpers: no CUDA device needed (reference semantics, used by CPU-side tests) ----
+ * gblur_host_plan_sizes  gaussian_window + sizes/trailing zeros   src/gaussianblur.cpp:11-26,104-123
+ * gblur_host_taps        get_gaussian's normalised float taps     src/gaussianblur.cpp:28-48
+ * gblur_host_spectrum    kerf_1D_* for (sigma, ksize, n), ordered layout, computed in double
+ * gblur_host_line_plan   stage radices / CTA shape chosen for FFT length n
+ * gblur_host_kperm       1/n-scaled gains in the digit-reversed order the kernels use, with the
+ *                        reference's Nyquist-bin behaviour (bin n/2 gets K[0])  src/gaussianblur.cpp:62-79 */
+int gblur_host_plan_sizes(int rows, int cols, float sigma, int* ksize, int* pad, int* n_rowpass, int* n_colpass,
+                          int* tz_rows, int* tz_cols);
+int gblur_host_taps(float sigma, int ksize, float* out);
+int gblur_host_spectrum(float sigma, int ksize, int n, float* out_ordered);
+int gblur_host_line_plan(int n, int* radices, int* nstages, int* nseq, int* static_kernel, long long* smem_bytes,
+                         int* nthreads);
+int gblur_host_kperm(float sigma, int ksize, int n, float* out_n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GBLUR_CAPI_H_ */

@@ -1,0 +1,266 @@
+"""libgaussianblur_b200 — B200-native (sm_100a) implementation of LibGaussianBlur's hot path.
+
+Python host layer over the C ABI in include/gblur_capi.h (ctypes; torch only supplies device
+memory and streams). The reference's own Python surface — module ``gaussianblur`` with
+``ImgGeom``, ``Image`` and ``gaussianblur(image, sigma, apply_to_alpha)``
+(/root/reference/python/bindings/gaussianblur_py.cpp:7-32) — is the pybind11 module built next to
+the library and re-exported here as ``libgaussianblur_b200.gaussianblur_module()``.
+
+There is no CPU implementation in this package: every blur call goes to the CUDA library and
+raises if it (or a GPU) is missing.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import importlib.util
+import os
+import sys
+
+import numpy as np
+
+from . import build as _build
+
+__all__ = ["Plan", "GblurError", "lib", "gaussianblur", "gaussianblur_module", "host_plan_sizes", "host_spectrum",
+           "host_line_plan", "host_kperm", "host_taps", "launch_count", "EXPORTED_SYMBOLS"]
+
+# every symbol include/gblur_capi.h declares
+EXPORTED_SYMBOLS = [
+    "gblur_plan_create", "gblur_plan_create_batch", "gblur_plan_create_band", "gblur_plan_destroy",
+    "gblur_plan_info", "gblur_plan_spectrum", "gblur_plan_radices", "gblur_run_host", "gblur_run_batch_host",
+    "gblur_run_device", "gblur_run_batch_device", "gblur_rowpass_device", "gblur_colpass_device",
+    "gblur_dump_intermediate", "gblur_launch_count", "gblur_last_error", "gblur_device_count",
+    "gblur_host_plan_sizes", "gblur_host_taps", "gblur_host_spectrum", "gblur_host_line_plan", "gblur_host_kperm",
+]
+
+
+class GblurError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"gblur error {code}: {msg}")
+        self.code = code
+
+
+_lib = None
+
+
+def lib():
+    """The loaded C-ABI library. Fails loudly if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    path = _build.lib_path()
+    if not os.path.exists(path):
+        raise ImportError(f"{path} is missing: run `python -m libgaussianblur_b200.build` (needs nvcc); "
+                          "there is no CPU fallback")
+    L = C.CDLL(path)
+    ip, fp, u8p, vp, ll = C.POINTER(C.c_int), C.POINTER(C.c_float), C.c_void_p, C.c_void_p, C.c_longlong
+    pp = C.POINTER(C.c_void_p)
+    sig = {
+        "gblur_plan_create": (C.c_int, [pp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float]),
+        "gblur_plan_create_batch": (C.c_int, [pp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int]),
+        "gblur_plan_create_band": (C.c_int, [pp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int]),
+        "gblur_plan_destroy": (None, [vp]),
+        "gblur_plan_info": (C.c_int, [vp, ip, ip, ip, ip, ip, ip]),
+        "gblur_plan_spectrum": (C.c_int, [vp, C.c_int, fp]),
+        "gblur_plan_radices": (C.c_int, [vp, C.c_int, ip, ip, ip]),
+        "gblur_run_host": (C.c_int, [vp, u8p, C.c_int]),
+        "gblur_run_batch_host": (C.c_int, [vp, u8p, C.c_int, C.c_int]),
+        "gblur_run_device": (C.c_int, [vp, u8p, u8p, C.c_int, vp]),
+        "gblur_run_batch_device": (C.c_int, [vp, u8p, u8p, C.c_int, C.c_int, vp]),
+        "gblur_rowpass_device": (C.c_int, [vp, u8p, vp, ll, C.c_int, vp]),
+        "gblur_colpass_device": (C.c_int, [vp, vp, ll, u8p, ll, C.c_int, vp]),
+        "gblur_dump_intermediate": (C.c_int, [vp, fp, C.c_int]),
+        "gblur_launch_count": (C.c_ulonglong, []),
+        "gblur_last_error": (C.c_char_p, []),
+        "gblur_device_count": (C.c_int, []),
+        "gblur_host_plan_sizes": (C.c_int, [C.c_int, C.c_int, C.c_float, ip, ip, ip, ip, ip, ip]),
+        "gblur_host_taps": (C.c_int, [C.c_float, C.c_int, fp]),
+        "gblur_host_spectrum": (C.c_int, [C.c_float, C.c_int, C.c_int, fp]),
+        "gblur_host_line_plan": (C.c_int, [C.c_int, ip, ip, ip, ip, C.POINTER(C.c_longlong), ip]),
+        "gblur_host_kperm": (C.c_int, [C.c_float, C.c_int, C.c_int, fp]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = L
+    return L
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise GblurError(rc, lib().gblur_last_error().decode())
+
+
+def launch_count() -> int:
+    return int(lib().gblur_launch_count())
+
+
+# ---------------------------------------------------------------------------------------------
+# host-only semantics (no GPU needed)
+# ---------------------------------------------------------------------------------------------
+def host_plan_sizes(rows: int, cols: int, sigma: float) -> dict:
+    v = [C.c_int() for _ in range(6)]
+    _check(lib().gblur_host_plan_sizes(rows, cols, sigma, *[C.byref(x) for x in v]))
+    k = ["ksize", "pad", "n_rowpass", "n_colpass", "tz_rows", "tz_cols"]
+    return dict(zip(k, [x.value for x in v]))
+
+
+def host_taps(sigma: float, ksize: int) -> np.ndarray:
+    out = np.empty(ksize, dtype=np.float32)
+    _check(lib().gblur_host_taps(sigma, ksize, out.ctypes.data_as(C.POINTER(C.c_float))))
+    return out
+
+
+def host_spectrum(sigma: float, ksize: int, n: int) -> np.ndarray:
+    out = np.empty(n, dtype=np.float32)
+    _check(lib().gblur_host_spectrum(sigma, ksize, n, out.ctypes.data_as(C.POINTER(C.c_float))))
+    return out
+
+
+def host_line_plan(n: int) -> dict:
+    rad = (C.c_int * 5)()
+    ns, nseq, st, nt = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    smem = C.c_longlong()
+    _check(lib().gblur_host_line_plan(n, rad, C.byref(ns), C.byref(nseq), C.byref(st), C.byref(smem), C.byref(nt)))
+    return dict(radices=[rad[i] for i in range(ns.value)], nseq=nseq.value, static=bool(st.value),
+                smem_bytes=smem.value, nthreads=nt.value)
+
+
+def host_kperm(sigma: float, ksize: int, n: int) -> np.ndarray:
+    out = np.empty(n, dtype=np.float32)
+    _check(lib().gblur_host_kperm(sigma, ksize, n, out.ctypes.data_as(C.POINTER(C.c_float))))
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# GPU plan
+# ---------------------------------------------------------------------------------------------
+def _ptr(t):
+    """Device pointer of a torch tensor / int / None."""
+    if t is None:
+        return None
+    if isinstance(t, int):
+        return C.c_void_p(t)
+    return C.c_void_p(t.data_ptr())
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        import torch
+
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    if isinstance(stream, int):
+        return C.c_void_p(stream)
+    return C.c_void_p(stream.cuda_stream)
+
+
+class Plan:
+    """Immutable GPU plan for one geometry + sigma (the GPU counterpart of KernelDFT,
+    /root/reference/include/gaussianblur/helpers.hpp:125-132)."""
+
+    def __init__(self, rows: int, cols: int, channels: int, sigma: float, device: int = 0, max_frames: int = 1,
+                 band_rows: int | None = None, band_cols: int | None = None):
+        self._h = C.c_void_p()
+        L = lib()
+        if band_rows is not None or band_cols is not None:
+            _check(L.gblur_plan_create_band(C.byref(self._h), device, rows, cols, channels, sigma,
+                                            band_rows or rows, band_cols or cols))
+        else:
+            _check(L.gblur_plan_create_batch(C.byref(self._h), device, rows, cols, channels, sigma, max_frames))
+        self.rows, self.cols, self.channels, self.sigma = rows, cols, channels, float(sigma)
+        self.device, self.max_frames = device, max_frames
+        self.band_rows, self.band_cols = band_rows, band_cols
+        v = [C.c_int() for _ in range(6)]
+        _check(L.gblur_plan_info(self._h, *[C.byref(x) for x in v]))
+        self.ksize, self.pad, self.n_rowpass, self.n_colpass, self.tz_rows, self.tz_cols = [x.value for x in v]
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().gblur_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
+
+    def spectrum(self, axis: int) -> np.ndarray:
+        out = np.empty(self.n_rowpass if axis == 0 else self.n_colpass, dtype=np.float32)
+        _check(lib().gblur_plan_spectrum(self._h, axis, out.ctypes.data_as(C.POINTER(C.c_float))))
+        return out
+
+    def radices(self, axis: int):
+        rad = (C.c_int * 5)()
+        n, st = C.c_int(), C.c_int()
+        _check(lib().gblur_plan_radices(self._h, axis, rad, C.byref(n), C.byref(st)))
+        return [rad[i] for i in range(n.value)], bool(st.value)
+
+    def processed_channels(self, apply_to_alpha: bool) -> int:
+        return 3 if (self.channels == 4 and not apply_to_alpha) else self.channels
+
+    # -- host buffers (H2D + blur + D2H inside the call) --
+    def run_host(self, img: np.ndarray, apply_to_alpha: bool = False, n_frames: int | None = None) -> np.ndarray:
+        """Blur a C-contiguous uint8 numpy array (or pinned torch CPU tensor) in place."""
+        if hasattr(img, "data_ptr"):
+            ptr, nbytes = C.c_void_p(img.data_ptr()), img.numel()
+        else:
+            assert img.dtype == np.uint8 and img.flags.c_contiguous and img.flags.writeable
+            ptr, nbytes = C.c_void_p(img.ctypes.data), img.size
+        frames = n_frames if n_frames is not None else 1
+        assert nbytes == frames * self.rows * self.cols * self.channels, "buffer size does not match the plan"
+        _check(lib().gblur_run_batch_host(self._h, ptr, frames, int(bool(apply_to_alpha))))
+        return img
+
+    # -- device buffers (torch uint8 CUDA tensors), asynchronous on the current stream --
+    def run_device(self, d_in, d_out=None, apply_to_alpha: bool = False, n_frames: int = 1, stream=None):
+        d_out = d_in if d_out is None else d_out
+        _check(lib().gblur_run_batch_device(self._h, _ptr(d_in), _ptr(d_out), n_frames, int(bool(apply_to_alpha)),
+                                            _stream_ptr(stream)))
+        return d_out
+
+    def rowpass(self, d_in, d_inter, inter_pitch_floats: int, apply_to_alpha: bool = False, stream=None):
+        _check(lib().gblur_rowpass_device(self._h, _ptr(d_in), _ptr(d_inter), inter_pitch_floats,
+                                          int(bool(apply_to_alpha)), _stream_ptr(stream)))
+
+    def colpass(self, d_inter, inter_pitch_floats: int, d_out, out_pitch_bytes: int, apply_to_alpha: bool = False,
+                stream=None):
+        _check(lib().gblur_colpass_device(self._h, _ptr(d_inter), inter_pitch_floats, _ptr(d_out), out_pitch_bytes,
+                                          int(bool(apply_to_alpha)), _stream_ptr(stream)))
+
+    def dump_intermediate(self, apply_to_alpha: bool = False) -> np.ndarray:
+        cp = self.processed_channels(apply_to_alpha)
+        out = np.empty((self.rows, self.cols * cp), dtype=np.float32)
+        _check(lib().gblur_dump_intermediate(self._h, out.ctypes.data_as(C.POINTER(C.c_float)),
+                                             int(bool(apply_to_alpha))))
+        return out
+
+
+def gaussianblur(img: np.ndarray, sigma: float, apply_to_alpha: bool = False, device: int = 0) -> np.ndarray:
+    """Blur an HWC (channels 3/4) or HW uint8 numpy array in place on the GPU and return it.
+    Error behaviour follows gaussianblur::gaussianblur (/root/reference/src/gaussianblur.cpp:307-317):
+    sigma <= 0 or an unsupported channel count leaves the data untouched."""
+    if sigma <= 0:
+        print("Invalid smoothing factor")
+        return img
+    ch = 1 if img.ndim == 2 else img.shape[2]
+    if ch not in (1, 3, 4):
+        print("Unsupported number of channels", file=sys.stderr)
+        return img
+    plan = Plan(img.shape[0], img.shape[1], ch, sigma, device=device)
+    try:
+        plan.run_host(img, apply_to_alpha)
+    finally:
+        plan.close()
+    return img
+
+
+def gaussianblur_module():
+    """The pybind11 module `gaussianblur` (reference-compatible Python surface)."""
+    name = "gaussianblur"
+    if name in sys.modules and getattr(sys.modules[name], "__file__", "") == _build.pymod_path():
+        return sys.modules[name]
+    path = _build.pymod_path()
+    if not os.path.exists(path):
+        raise ImportError(f"{path} is missing: run `python -m libgaussianblur_b200.build`")
+    spec = importlib.util.spec_from_file_location(name, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    sys.modules[name] = mod
+    return mod

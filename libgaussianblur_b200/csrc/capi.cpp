@@ -1,0 +1,420 @@
+// capi.cpp — implementation of include/gblur_capi.h: plans, workspaces and the pass drivers.
+// Host semantics follow the reference (see hostsem.hpp / planner.hpp for file:line citations);
+// all pixel work happens in the sm_100a kernels (kernels.h). No CPU fallback exists.
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/gblur_capi.h"
+#include "hostsem.hpp"
+#include "kernels.h"
+#include "planner.hpp"
+
+using namespace gblur;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CU(call)                                                                         \
+  do {                                                                                   \
+    cudaError_t e_ = (call);                                                             \
+    if (e_ != cudaSuccess) return fail(GBLUR_E_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
+  } while (0)
+
+struct DeviceGuard {
+  int prev = -1;
+  bool ok = false;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) == cudaSuccess) ok = (cudaSetDevice(dev) == cudaSuccess);
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+struct LineTables {
+  LinePlan lp;
+  float* d_tw = nullptr;
+  float* d_kperm = nullptr;
+  std::vector<float> kerf;  // host copy, pffft ordered layout
+};
+
+}  // namespace
+
+struct gblur_plan {
+  int device = 0;
+  int num_sms = 148;
+  int channels = 0;
+  float sigma = 0.f;
+  int full_rows = 0, full_cols = 0;  // geometry the window / FFT lengths come from
+  int rows = 0, cols = 0;            // rows the row pass covers, pixel columns the column pass covers
+  int max_frames = 1;
+  bool band = false;
+  host::Sizes sz{};
+  LineTables row, col;  // row pass (N = n_rowpass), column pass (N = n_colpass)
+  float* d_inter = nullptr;
+  size_t inter_floats = 0;
+  uint8_t* d_stage = nullptr;  // device image for gblur_run_host
+  size_t stage_bytes = 0;
+  cudaStream_t stream = nullptr;
+  int last_cp = 0;
+};
+
+namespace {
+
+int build_tables(LineTables& t, int N, const std::vector<float>& taps) {
+  if (!host::plan_line(N, t.lp))
+    return fail(GBLUR_E_UNSUPPORTED, "FFT length %d does not fit one CTA's shared memory", N);
+  const std::vector<double> gains = host::kernel_gains(taps, N);
+  t.kerf = host::kerf_ordered(gains, N);
+  std::vector<float> tw;
+  size_t off[kHostMaxStages] = {0, 0, 0, 0, 0};
+  host::build_twiddles(t.lp, tw, off);
+  const std::vector<float> kp = host::build_kperm(t.lp, gains);
+  if (!tw.empty()) {
+    CU(cudaMalloc(&t.d_tw, tw.size() * sizeof(float)));
+    CU(cudaMemcpy(t.d_tw, tw.data(), tw.size() * sizeof(float), cudaMemcpyHostToDevice));
+  }
+  CU(cudaMalloc(&t.d_kperm, kp.size() * sizeof(float)));
+  CU(cudaMemcpy(t.d_kperm, kp.data(), kp.size() * sizeof(float), cudaMemcpyHostToDevice));
+  for (int s = 0; s < t.lp.nstages - 1; ++s) t.lp.d_tw[s] = reinterpret_cast<const float2*>(t.d_tw) + off[s];
+  t.lp.d_kperm = t.d_kperm;
+  return GBLUR_OK;
+}
+
+void free_tables(LineTables& t) {
+  if (t.d_tw) cudaFree(t.d_tw);
+  if (t.d_kperm) cudaFree(t.d_kperm);
+  t.d_tw = t.d_kperm = nullptr;
+}
+
+int processed_channels(const gblur_plan* p, int apply_to_alpha) {
+  return (p->channels == 4 && !apply_to_alpha) ? 3 : p->channels;
+}
+
+long long default_pitch(long long w) { return (w + 3) / 4 * 4; }
+
+int ensure_inter(gblur_plan* p, size_t floats) {
+  if (p->inter_floats >= floats) return GBLUR_OK;
+  if (p->d_inter) cudaFree(p->d_inter);
+  p->d_inter = nullptr;
+  p->inter_floats = 0;
+  CU(cudaMalloc(&p->d_inter, floats * sizeof(float)));
+  // pad columns of the intermediate are read (never stored) by the column pass: keep them finite
+  CU(cudaMemset(p->d_inter, 0, floats * sizeof(float)));
+  CU(cudaDeviceSynchronize());
+  p->inter_floats = floats;
+  return GBLUR_OK;
+}
+
+int create_common(gblur_plan** out, int device, int full_rows, int full_cols, int channels, float sigma, int rows,
+                  int cols, int max_frames, bool band) {
+  if (!out) return fail(GBLUR_E_INVALID, "null plan out pointer");
+  *out = nullptr;
+  if (!(sigma > 0.0f)) return fail(GBLUR_E_INVALID, "Invalid smoothing factor");
+  if (channels != 1 && channels != 3 && channels != 4) return fail(GBLUR_E_INVALID, "Unsupported number of channels");
+  if (full_rows < 1 || full_cols < 1 || rows < 1 || cols < 1 || max_frames < 1)
+    return fail(GBLUR_E_INVALID, "non-positive geometry");
+  const host::Sizes sz = host::plan_sizes(full_rows, full_cols, sigma);
+  if (sz.pad > std::min(full_rows, full_cols) - 1)
+    return fail(GBLUR_E_PRECOND, "pad %d exceeds min(rows, cols) - 1 = %d (reference precondition)", sz.pad,
+                std::min(full_rows, full_cols) - 1);
+  int ndev = 0;
+  CU(cudaGetDeviceCount(&ndev));
+  if (device < 0 || device >= ndev) return fail(GBLUR_E_CUDA, "device %d not available (%d visible)", device, ndev);
+  DeviceGuard guard(device);
+  if (!guard.ok) return fail(GBLUR_E_CUDA, "cudaSetDevice(%d) failed", device);
+
+  gblur_plan* p = new gblur_plan();
+  p->device = device;
+  p->channels = channels;
+  p->sigma = sigma;
+  p->full_rows = full_rows;
+  p->full_cols = full_cols;
+  p->rows = rows;
+  p->cols = cols;
+  p->max_frames = max_frames;
+  p->band = band;
+  p->sz = sz;
+  cudaDeviceGetAttribute(&p->num_sms, cudaDevAttrMultiProcessorCount, device);
+  const std::vector<float> taps = host::gaussian_taps(sigma, sz.ksize);
+  int rc = GBLUR_OK;
+  if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess)
+    rc = fail(GBLUR_E_CUDA, "cudaStreamCreate failed");
+  if (rc == GBLUR_OK) rc = build_tables(p->row, sz.n_rowpass, taps);
+  if (rc == GBLUR_OK) rc = build_tables(p->col, sz.n_colpass, taps);
+  if (rc != GBLUR_OK) {
+    std::string keep = g_err;
+    gblur_plan_destroy(p);
+    g_err = keep;
+    return rc;
+  }
+  *out = p;
+  return GBLUR_OK;
+}
+
+int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pitch, int frames, int alpha,
+                cudaStream_t s) {
+  const int cp = processed_channels(p, alpha);
+  RowLaunch a{};
+  a.in = d_in;
+  a.in_pitch = (long long)p->full_cols * p->channels;
+  a.C = p->channels;
+  a.Cp = cp;
+  a.T = p->full_cols;
+  a.pad = p->sz.pad;
+  a.rows_total = (long long)p->rows * frames;
+  a.inter = d_inter;
+  a.inter_pitch = pitch;
+  CU(launch_rowpass(p->row.lp, a, p->num_sms, s));
+  return GBLUR_OK;
+}
+
+int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d_out, long long out_pitch, int frames,
+                int alpha, cudaStream_t s) {
+  const int cp = processed_channels(p, alpha);
+  ColLaunch a{};
+  a.inter = d_inter;
+  a.pitch = pitch;
+  a.frame_stride = (long long)p->full_rows * pitch;
+  a.frames = frames;
+  a.T = p->full_rows;
+  a.pad = p->sz.pad;
+  a.W = p->cols * cp;
+  a.out = d_out;
+  a.out_pitch = out_pitch;
+  a.out_frame_stride = (long long)p->full_rows * out_pitch;
+  a.C = p->channels;
+  a.Cp = cp;
+  CU(launch_colpass(p->col.lp, a, p->num_sms, s));
+  return GBLUR_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* gblur_last_error(void) { return g_err.c_str(); }
+
+unsigned long long gblur_launch_count(void) { return launch_counter(); }
+
+int gblur_device_count(void) {
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess) {
+    fail(GBLUR_E_CUDA, "cudaGetDeviceCount: %s", cudaGetErrorString(e));
+    return -1;
+  }
+  return n;
+}
+
+int gblur_plan_create(gblur_plan** out, int device, int rows, int cols, int channels, float sigma) {
+  return create_common(out, device, rows, cols, channels, sigma, rows, cols, 1, false);
+}
+
+int gblur_plan_create_batch(gblur_plan** out, int device, int rows, int cols, int channels, float sigma,
+                            int max_frames) {
+  return create_common(out, device, rows, cols, channels, sigma, rows, cols, max_frames, false);
+}
+
+int gblur_plan_create_band(gblur_plan** out, int device, int full_rows, int full_cols, int channels, float sigma,
+                           int band_rows, int band_cols) {
+  if (band_rows > full_rows || band_cols > full_cols) return fail(GBLUR_E_INVALID, "band larger than the image");
+  return create_common(out, device, full_rows, full_cols, channels, sigma, band_rows, band_cols, 1, true);
+}
+
+void gblur_plan_destroy(gblur_plan* p) {
+  if (!p) return;
+  DeviceGuard guard(p->device);
+  if (p->stream) cudaStreamSynchronize(p->stream);
+  free_tables(p->row);
+  free_tables(p->col);
+  if (p->d_inter) cudaFree(p->d_inter);
+  if (p->d_stage) cudaFree(p->d_stage);
+  if (p->stream) cudaStreamDestroy(p->stream);
+  delete p;
+}
+
+int gblur_plan_info(const gblur_plan* p, int* ksize, int* pad, int* n_rowpass, int* n_colpass, int* tz_rows,
+                    int* tz_cols) {
+  if (!p) return fail(GBLUR_E_INVALID, "null plan");
+  if (ksize) *ksize = p->sz.ksize;
+  if (pad) *pad = p->sz.pad;
+  if (n_rowpass) *n_rowpass = p->sz.n_rowpass;
+  if (n_colpass) *n_colpass = p->sz.n_colpass;
+  if (tz_rows) *tz_rows = p->sz.tz_rows;
+  if (tz_cols) *tz_cols = p->sz.tz_cols;
+  return GBLUR_OK;
+}
+
+int gblur_plan_spectrum(const gblur_plan* p, int axis, float* host_out) {
+  if (!p || !host_out || (axis != 0 && axis != 1)) return fail(GBLUR_E_INVALID, "bad spectrum query");
+  const std::vector<float>& k = axis == 0 ? p->row.kerf : p->col.kerf;
+  std::memcpy(host_out, k.data(), k.size() * sizeof(float));
+  return GBLUR_OK;
+}
+
+int gblur_plan_radices(const gblur_plan* p, int axis, int* radices, int* n, int* static_kernel) {
+  if (!p || (axis != 0 && axis != 1)) return fail(GBLUR_E_INVALID, "bad radices query");
+  const LinePlan& lp = axis == 0 ? p->row.lp : p->col.lp;
+  if (radices)
+    for (int s = 0; s < lp.nstages; ++s) radices[s] = lp.radix[s];
+  if (n) *n = lp.nstages;
+  if (static_kernel) *static_kernel = lp.static_id >= 0 ? 1 : 0;
+  return GBLUR_OK;
+}
+
+int gblur_run_batch_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
+                           void* cuda_stream) {
+  if (!p || !d_in || !d_out) return fail(GBLUR_E_INVALID, "null argument");
+  if (p->band) return fail(GBLUR_E_INVALID, "band plans run through gblur_rowpass_device / gblur_colpass_device");
+  if (n_frames < 1 || n_frames > p->max_frames)
+    return fail(GBLUR_E_INVALID, "n_frames %d outside [1, %d]", n_frames, p->max_frames);
+  DeviceGuard guard(p->device);
+  cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+  const int cp = processed_channels(p, apply_to_alpha);
+  const long long pitch = default_pitch((long long)p->cols * cp);
+  int rc = ensure_inter(p, (size_t)p->max_frames * p->rows * default_pitch((long long)p->cols * p->channels));
+  if (rc != GBLUR_OK) return rc;
+  rc = run_rowpass(p, d_in, p->d_inter, pitch, n_frames, apply_to_alpha, s);
+  if (rc != GBLUR_OK) return rc;
+  if (d_in != d_out && cp < p->channels)
+    CU(launch_copy_channel(d_in, d_out, (long long)p->rows * p->cols * n_frames, p->channels, 3, s));
+  p->last_cp = cp;
+  return run_colpass(p, p->d_inter, pitch, d_out, (long long)p->cols * p->channels, n_frames, apply_to_alpha, s);
+}
+
+int gblur_run_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int apply_to_alpha, void* cuda_stream) {
+  return gblur_run_batch_device(p, d_in, d_out, 1, apply_to_alpha, cuda_stream);
+}
+
+int gblur_run_batch_host(gblur_plan* p, uint8_t* hwc, int n_frames, int apply_to_alpha) {
+  if (!p || !hwc) return fail(GBLUR_E_INVALID, "null argument");
+  if (n_frames < 1 || n_frames > p->max_frames)
+    return fail(GBLUR_E_INVALID, "n_frames %d outside [1, %d]", n_frames, p->max_frames);
+  DeviceGuard guard(p->device);
+  const size_t bytes = (size_t)p->rows * p->cols * p->channels * (size_t)n_frames;
+  if (p->stage_bytes < bytes) {
+    if (p->d_stage) cudaFree(p->d_stage);
+    p->d_stage = nullptr;
+    p->stage_bytes = 0;
+    CU(cudaMalloc(&p->d_stage, bytes));
+    p->stage_bytes = bytes;
+  }
+  CU(cudaMemcpyAsync(p->d_stage, hwc, bytes, cudaMemcpyHostToDevice, p->stream));
+  int rc = gblur_run_batch_device(p, p->d_stage, p->d_stage, n_frames, apply_to_alpha, p->stream);
+  if (rc != GBLUR_OK) return rc;
+  CU(cudaMemcpyAsync(hwc, p->d_stage, bytes, cudaMemcpyDeviceToHost, p->stream));
+  CU(cudaStreamSynchronize(p->stream));
+  return GBLUR_OK;
+}
+
+int gblur_run_host(gblur_plan* p, uint8_t* hwc, int apply_to_alpha) {
+  return gblur_run_batch_host(p, hwc, 1, apply_to_alpha);
+}
+
+int gblur_rowpass_device(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long inter_pitch_floats,
+                         int apply_to_alpha, void* cuda_stream) {
+  if (!p || !d_in || !d_inter) return fail(GBLUR_E_INVALID, "null argument");
+  const int cp = processed_channels(p, apply_to_alpha);
+  if (inter_pitch_floats < (long long)p->full_cols * cp) return fail(GBLUR_E_INVALID, "intermediate pitch too small");
+  DeviceGuard guard(p->device);
+  return run_rowpass(p, d_in, d_inter, inter_pitch_floats, 1, apply_to_alpha, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int gblur_colpass_device(gblur_plan* p, const float* d_inter, long long inter_pitch_floats, uint8_t* d_out,
+                         long long out_pitch_bytes, int apply_to_alpha, void* cuda_stream) {
+  if (!p || !d_inter || !d_out) return fail(GBLUR_E_INVALID, "null argument");
+  const int cp = processed_channels(p, apply_to_alpha);
+  if (inter_pitch_floats % 4 || inter_pitch_floats < default_pitch((long long)p->cols * cp))
+    return fail(GBLUR_E_INVALID, "intermediate pitch must be a multiple of 4 floats covering band_cols*Cp rounded up to 4");
+  if (out_pitch_bytes < (long long)p->cols * p->channels) return fail(GBLUR_E_INVALID, "output pitch too small");
+  DeviceGuard guard(p->device);
+  return run_colpass(p, d_inter, inter_pitch_floats, d_out, out_pitch_bytes, 1, apply_to_alpha,
+                     static_cast<cudaStream_t>(cuda_stream));
+}
+
+int gblur_dump_intermediate(gblur_plan* p, float* host_out, int apply_to_alpha) {
+  if (!p || !host_out) return fail(GBLUR_E_INVALID, "null argument");
+  if (!p->d_inter) return fail(GBLUR_E_INVALID, "no run has happened on this plan");
+  DeviceGuard guard(p->device);
+  const int cp = processed_channels(p, apply_to_alpha);
+  const long long w = (long long)p->cols * cp, pitch = default_pitch(w);
+  CU(cudaDeviceSynchronize());
+  CU(cudaMemcpy2D(host_out, (size_t)w * sizeof(float), p->d_inter, (size_t)pitch * sizeof(float),
+                  (size_t)w * sizeof(float), (size_t)p->rows, cudaMemcpyDeviceToHost));
+  return GBLUR_OK;
+}
+
+/* ---- host-only helpers (no device needed): the semantics tests call these on CPU boxes ---- */
+
+int gblur_host_plan_sizes(int rows, int cols, float sigma, int* ksize, int* pad, int* n_rowpass, int* n_colpass,
+                          int* tz_rows, int* tz_cols) {
+  const host::Sizes s = host::plan_sizes(rows, cols, sigma);
+  if (ksize) *ksize = s.ksize;
+  if (pad) *pad = s.pad;
+  if (n_rowpass) *n_rowpass = s.n_rowpass;
+  if (n_colpass) *n_colpass = s.n_colpass;
+  if (tz_rows) *tz_rows = s.tz_rows;
+  if (tz_cols) *tz_cols = s.tz_cols;
+  return GBLUR_OK;
+}
+
+int gblur_host_taps(float sigma, int ksize, float* out) {
+  if (!out || ksize < 1) return fail(GBLUR_E_INVALID, "bad taps query");
+  const std::vector<float> t = host::gaussian_taps(sigma, ksize);
+  std::memcpy(out, t.data(), t.size() * sizeof(float));
+  return GBLUR_OK;
+}
+
+int gblur_host_spectrum(float sigma, int ksize, int n, float* out_ordered) {
+  if (!out_ordered || n < 32 || ksize < 1) return fail(GBLUR_E_INVALID, "bad spectrum query");
+  const std::vector<float> k = host::kerf_ordered(host::kernel_gains(host::gaussian_taps(sigma, ksize), n), n);
+  std::memcpy(out_ordered, k.data(), k.size() * sizeof(float));
+  return GBLUR_OK;
+}
+
+/* Stage plan for FFT length n: radices[<=5], *nstages, *nseq, *static_kernel, *smem_bytes, *nthreads.
+ * Returns GBLUR_E_UNSUPPORTED when n does not fit one CTA. */
+int gblur_host_line_plan(int n, int* radices, int* nstages, int* nseq, int* static_kernel, long long* smem_bytes,
+                         int* nthreads) {
+  LinePlan lp;
+  if (!host::is_valid_size(n)) return fail(GBLUR_E_INVALID, "%d is not a valid transform size", n);
+  if (!host::plan_line(n, lp)) return fail(GBLUR_E_UNSUPPORTED, "FFT length %d does not fit one CTA's shared memory", n);
+  if (radices)
+    for (int s = 0; s < lp.nstages; ++s) radices[s] = lp.radix[s];
+  if (nstages) *nstages = lp.nstages;
+  if (nseq) *nseq = lp.nseq;
+  if (static_kernel) *static_kernel = lp.static_id >= 0;
+  if (smem_bytes) *smem_bytes = (long long)lp.smem_bytes;
+  if (nthreads) *nthreads = lp.nthreads;
+  return GBLUR_OK;
+}
+
+/* Digit-reversed, 1/N-scaled gains for FFT length n exactly as uploaded to the device, plus the
+ * twiddle table; lets CPU tests check the permutation against a numpy FFT. */
+int gblur_host_kperm(float sigma, int ksize, int n, float* out_n) {
+  LinePlan lp;
+  if (!out_n) return fail(GBLUR_E_INVALID, "null out");
+  if (!host::plan_line(n, lp)) return fail(GBLUR_E_UNSUPPORTED, "FFT length %d does not fit one CTA's shared memory", n);
+  const std::vector<float> kp = host::build_kperm(lp, host::kernel_gains(host::gaussian_taps(sigma, ksize), n));
+  std::memcpy(out_n, kp.data(), kp.size() * sizeof(float));
+  return GBLUR_OK;
+}
+
+}  // extern "C"

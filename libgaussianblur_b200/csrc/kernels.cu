@@ -1,0 +1,110 @@
+// kernels.cu — dispatch from the host plan to the kernel instantiations (static_impl.cu per
+// compile-time shape, generic_row.cu / generic_col.cu for every other valid FFT length).
+#include "kernels.h"
+
+#include <atomic>
+
+#include "line_kernels.cuh"
+#include "static_shapes.h"
+
+namespace gblur {
+
+static std::atomic<unsigned long long> g_launches{0};
+unsigned long long launch_counter() { return g_launches.load(); }
+void count_launch() { g_launches.fetch_add(1); }
+
+__global__ void copy_channel_kernel(const uint8_t* __restrict__ src, uint8_t* __restrict__ dst,
+                                    long long npixels, int C, int ch) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < npixels;
+       i += (long long)gridDim.x * blockDim.x)
+    dst[i * C + ch] = src[i * C + ch];
+}
+
+struct StaticEntry {
+  int id, nseq, r[4], nthreads;
+};
+static const StaticEntry kStaticTable[] = {
+#define X(ID, NSEQ, R0, R1, R2, R3, NT, MINB) {ID, NSEQ, {R0, R1, R2, R3}, NT},
+    GBLUR_STATIC_SHAPES(X)
+#undef X
+};
+
+int find_static_shape(int N, int nseq, int* radices, int* nthreads) {
+  for (const auto& e : kStaticTable) {
+    if (e.nseq == nseq && e.r[0] * e.r[1] * e.r[2] * e.r[3] == N) {
+      for (int i = 0; i < 4; ++i) radices[i] = e.r[i];
+      *nthreads = e.nthreads;
+      return e.id;
+    }
+  }
+  return -1;
+}
+
+cudaError_t kernels_init(int) { return cudaSuccess; }
+
+cudaError_t launch_rowpass(const LinePlan& lp, const RowLaunch& a, int num_sms, cudaStream_t stream) {
+  RowParams P{};
+  P.in = a.in;
+  P.in_pitch = a.in_pitch;
+  P.C = a.C;
+  P.Cp = a.Cp;
+  P.T = a.T;
+  P.pad = a.pad;
+  P.nreal = a.rows_total * a.Cp;
+  P.inter = a.inter;
+  P.inter_pitch = a.inter_pitch;
+  const long long L = 2 * lp.nseq;
+  P.nunits = (int)((P.nreal + L - 1) / L);
+  const bool rgba = lp.nseq == 2 && a.C == 4 && a.Cp == 4 && (a.in_pitch % 4) == 0 && (a.inter_pitch % 4) == 0 &&
+                    (reinterpret_cast<uintptr_t>(a.in) % 4) == 0 && (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0;
+  switch (lp.static_id) {
+#define X(ID, NSEQ, R0, R1, R2, R3, NT, MINB) \
+  case ID:                                    \
+    return launch_row_static<ID>(lp, P, rgba, num_sms, stream);
+    GBLUR_STATIC_SHAPES(X)
+#undef X
+    default:
+      return launch_row_generic(lp, P, rgba, num_sms, stream);
+  }
+}
+
+cudaError_t launch_colpass(const LinePlan& lp, const ColLaunch& a, int num_sms, cudaStream_t stream) {
+  ColParams P{};
+  P.inter = a.inter;
+  P.pitch = a.pitch;
+  P.frame_stride = a.frame_stride;
+  P.T = a.T;
+  P.pad = a.pad;
+  P.W = a.W;
+  const int L = 2 * lp.nseq;
+  P.groups_per_frame = (a.W + L - 1) / L;
+  P.nunits = a.frames * P.groups_per_frame;
+  P.out = a.out;
+  P.out_pitch = a.out_pitch;
+  P.out_frame_stride = a.out_frame_stride;
+  P.C = a.C;
+  P.Cp = a.Cp;
+  const bool packed = a.C == a.Cp && (a.W % L) == 0 && (a.out_pitch % L) == 0 && (a.out_frame_stride % L) == 0 &&
+                      (reinterpret_cast<uintptr_t>(a.out) % L) == 0;
+  switch (lp.static_id) {
+#define X(ID, NSEQ, R0, R1, R2, R3, NT, MINB) \
+  case ID:                                    \
+    return launch_col_static<ID>(lp, P, packed, num_sms, stream);
+    GBLUR_STATIC_SHAPES(X)
+#undef X
+    default:
+      return launch_col_generic(lp, P, packed, num_sms, stream);
+  }
+}
+
+cudaError_t launch_copy_channel(const uint8_t* src, uint8_t* dst, long long npixels, int C, int ch,
+                                cudaStream_t stream) {
+  if (npixels <= 0) return cudaSuccess;
+  long long blocks = (npixels + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  copy_channel_kernel<<<(unsigned)blocks, 256, 0, stream>>>(src, dst, npixels, C, ch);
+  count_launch();
+  return cudaGetLastError();
+}
+
+}  // namespace gblur

@@ -1,0 +1,66 @@
+// kernels.h — host-visible launch interface of the sm_100a line-convolution kernels.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+
+namespace gblur {
+
+constexpr int kHostMaxStages = 5;
+
+// Host mirror of the device LineShape plus launch facts, filled by the planner (plan.cpp).
+struct LinePlan {
+  int N = 0;
+  int nstages = 0;
+  int radix[kHostMaxStages] = {0, 0, 0, 0, 0};
+  int M[kHostMaxStages] = {0, 0, 0, 0, 0};
+  int padq = 0;
+  const float2* d_tw[kHostMaxStages] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  const float* d_kperm = nullptr;
+  int nseq = 2;          // complex sequences per line unit (1 or 2)
+  int nthreads = 0;      // CTA size for the runtime-radix kernel
+  int static_id = -1;    // index into the compile-time shape table, -1 = runtime-radix kernel
+  size_t smem_bytes = 0; // dynamic shared memory per CTA
+};
+
+struct RowLaunch {
+  const uint8_t* in;
+  long long in_pitch;
+  int C, Cp;
+  int T, pad;
+  long long rows_total;
+  float* inter;
+  long long inter_pitch;
+};
+
+struct ColLaunch {
+  const float* inter;
+  long long pitch;
+  long long frame_stride;
+  int frames;
+  int T, pad;
+  int W;
+  uint8_t* out;
+  long long out_pitch;
+  long long out_frame_stride;
+  int C, Cp;
+};
+
+// Returns the static shape id for (N, nseq) or -1; fills radices when found.
+int find_static_shape(int N, int nseq, int* radices /*[4]*/, int* nthreads);
+
+// One-time per-process kernel attribute setup (max dynamic smem). Returns cudaSuccess or error.
+cudaError_t kernels_init(int device);
+
+cudaError_t launch_rowpass(const LinePlan& lp, const RowLaunch& a, int num_sms, cudaStream_t stream);
+cudaError_t launch_colpass(const LinePlan& lp, const ColLaunch& a, int num_sms, cudaStream_t stream);
+
+// Copies channel `ch` of every pixel from src to dst (alpha pass-through when out != in).
+cudaError_t launch_copy_channel(const uint8_t* src, uint8_t* dst, long long npixels, int C, int ch,
+                                cudaStream_t stream);
+
+// counts of kernel launches issued through this interface (for bench.py's gpu_launches)
+unsigned long long launch_counter();
+
+}  // namespace gblur

@@ -1,0 +1,93 @@
+// line_kernels.cuh — the two kernel templates (runtime-radix and compile-time shape) and the
+// persistent-grid launcher shared by every translation unit that instantiates them.
+#pragma once
+#include <cuda_runtime.h>
+
+#include "fftconv.cuh"
+#include "kernels.h"
+#include "problems.cuh"
+
+namespace gblur {
+
+void count_launch();  // kernels.cu
+
+template <int NSEQ, class Problem, class Params>
+__global__ void __launch_bounds__(512, 1)
+    line_kernel_generic(const __grid_constant__ LineShape sh, const __grid_constant__ Params P) {
+  extern __shared__ float4 smem_raw[];
+  auto* sm = reinterpret_cast<typename SmemElem<NSEQ>::type*>(smem_raw);
+  for (int unit = blockIdx.x; unit < P.nunits; unit += gridDim.x) {
+    typename Problem::Loader ld;
+    typename Problem::Storer st;
+    Problem::make(P, unit, ld, st);
+    run_line_generic<NSEQ>(sh, ld, st, sm, (int)threadIdx.x, (int)blockDim.x);
+  }
+}
+
+template <int NSEQ, class SS, int NT, int MINB, class Problem, class Params>
+__global__ void __launch_bounds__(NT, MINB)
+    line_kernel_static(const __grid_constant__ LineShape sh, const __grid_constant__ Params P) {
+  extern __shared__ float4 smem_raw[];
+  auto* sm = reinterpret_cast<typename SmemElem<NSEQ>::type*>(smem_raw);
+  for (int unit = blockIdx.x; unit < P.nunits; unit += gridDim.x) {
+    typename Problem::Loader ld;
+    typename Problem::Storer st;
+    Problem::make(P, unit, ld, st);
+    run_line_static<NSEQ, SS>(sh, ld, st, sm, (int)threadIdx.x, NT);
+  }
+}
+
+inline LineShape to_device_shape(const LinePlan& lp) {
+  LineShape sh{};
+  sh.N = lp.N;
+  sh.nstages = lp.nstages;
+  for (int i = 0; i < kMaxStages; ++i) {
+    sh.radix[i] = lp.radix[i];
+    sh.M[i] = lp.M[i];
+    sh.tw[i] = lp.d_tw[i];
+  }
+  sh.padq = lp.padq;
+  sh.kperm = lp.d_kperm;
+  return sh;
+}
+
+// Persistent grid: one CTA per resident slot (SMs x occupancy), each looping over line units.
+// The occupancy query and the smem opt-in are done once per (kernel, smem size).
+template <auto k, class Params>
+cudaError_t launch_line(const LinePlan& lp, const Params& P, int nthreads, int num_sms, cudaStream_t stream) {
+  if (P.nunits <= 0) return cudaSuccess;
+  static thread_local size_t cached_smem = (size_t)-1;
+  static thread_local int cached_threads = -1;
+  static thread_local int cached_device = -1;
+  static thread_local int cached_per_sm = 0;
+  int device = 0;
+  cudaGetDevice(&device);
+  if (cached_smem != lp.smem_bytes || cached_threads != nthreads || cached_device != device) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    if (e != cudaSuccess) return e;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, nthreads, lp.smem_bytes);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    cached_smem = lp.smem_bytes;
+    cached_threads = nthreads;
+    cached_device = device;
+    cached_per_sm = per_sm;
+  }
+  long long grid = (long long)num_sms * cached_per_sm;
+  if (grid > P.nunits) grid = P.nunits;
+  LineShape sh = to_device_shape(lp);
+  k<<<(unsigned)grid, nthreads, lp.smem_bytes, stream>>>(sh, P);
+  count_launch();
+  return cudaGetLastError();
+}
+
+// entry points implemented one per translation unit
+template <int ID>
+cudaError_t launch_row_static(const LinePlan&, const RowParams&, bool rgba, int num_sms, cudaStream_t);
+template <int ID>
+cudaError_t launch_col_static(const LinePlan&, const ColParams&, bool packed, int num_sms, cudaStream_t);
+cudaError_t launch_row_generic(const LinePlan&, const RowParams&, bool rgba, int num_sms, cudaStream_t);
+cudaError_t launch_col_generic(const LinePlan&, const ColParams&, bool packed, int num_sms, cudaStream_t);
+
+}  // namespace gblur

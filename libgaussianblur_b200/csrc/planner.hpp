@@ -1,0 +1,151 @@
+// planner.hpp — host-only: choose stage radices for an FFT length and build the twiddle and
+// permuted-spectrum tables the kernels consume. Replaces pffft_new_setup's decompose()/rffti1_ps
+// (/root/reference/include/pffft_pommier/pffft.c:1073-1152,1231-1280) for the GPU path.
+#pragma once
+#include <cmath>
+#include <cstddef>
+#include <vector>
+
+#include "hostsem.hpp"
+#include "kernels.h"
+
+namespace gblur {
+namespace host {
+
+constexpr size_t kMaxSmemBytes = 227 * 1024;
+constexpr double kTwoPi = 6.28318530717958647692528676655900577;
+
+struct Factorization {
+  int nstages = 0;
+  int radix[kHostMaxStages] = {0, 0, 0, 0, 0};
+};
+
+// radices the runtime-radix kernel instantiates (keep in sync with GBLUR_FOR_EACH_GENERIC_RADIX)
+inline const std::vector<int>& generic_radices() {
+  static const std::vector<int> r = {16, 15, 12, 10, 9, 8, 6, 5, 4, 3, 2};
+  return r;
+}
+
+namespace detail {
+inline void search(int rem, int max_r, int depth, int* cur, Factorization& best, long long& best_cost) {
+  if (rem == 1) {
+    if (depth < 2) return;
+    long long sum = 0;
+    for (int i = 0; i < depth; ++i) sum += cur[i];
+    const long long cost = (long long)depth * 1000 + sum;  // fewest stages, then most balanced
+    if (cost < best_cost) {
+      best_cost = cost;
+      best.nstages = depth;
+      for (int i = 0; i < kHostMaxStages; ++i) best.radix[i] = i < depth ? cur[i] : 1;
+    }
+    return;
+  }
+  if (depth == kHostMaxStages) return;
+  for (int r : generic_radices()) {
+    if (r > max_r || rem % r) continue;
+    cur[depth] = r;
+    search(rem / r, r, depth + 1, cur, best, best_cost);
+  }
+}
+}  // namespace detail
+
+// Fewest stages, most balanced radices; a radix divisible by 4 goes last when there is one
+// (its per-thread spectrum gains are then 16-byte vectorisable).
+inline bool factorize_generic(int N, Factorization& f) {
+  int cur[kHostMaxStages];
+  long long best_cost = 1LL << 60;
+  detail::search(N, 16, 0, cur, f, best_cost);
+  if (f.nstages == 0) return false;
+  for (int i = f.nstages - 1; i >= 0; --i) {
+    if (f.radix[i] % 4 == 0) {
+      std::swap(f.radix[i], f.radix[f.nstages - 1]);
+      break;
+    }
+  }
+  return true;
+}
+
+inline size_t smem_bytes_for(int N, int rlast, int nseq) {
+  const int padq = (rlast % 2 == 0) ? rlast : 0;
+  const size_t elems = (size_t)N + (padq ? (size_t)N / padq : 0);
+  return elems * 8 * (size_t)nseq;
+}
+
+// Fill everything of a LinePlan that does not live on the device. Returns false when the length
+// does not fit one CTA's shared memory even with a single sequence.
+inline bool plan_line(int N, LinePlan& lp) {
+  lp = LinePlan{};
+  lp.N = N;
+  for (int nseq = 2; nseq >= 1; --nseq) {
+    Factorization f;
+    int st_r[4], st_threads = 0;
+    const int sid = find_static_shape(N, nseq, st_r, &st_threads);
+    if (sid >= 0) {
+      f.nstages = 0;
+      for (int i = 0; i < 4; ++i)
+        if (st_r[i] > 1) f.radix[f.nstages++] = st_r[i];
+    } else if (!factorize_generic(N, f)) {
+      return false;
+    }
+    const int rlast = f.radix[f.nstages - 1];
+    const size_t smem = smem_bytes_for(N, rlast, nseq);
+    if (smem > kMaxSmemBytes) continue;
+    lp.nseq = nseq;
+    lp.nstages = f.nstages;
+    int m = N, max_nb = 1;
+    for (int s = 0; s < f.nstages; ++s) {
+      lp.radix[s] = f.radix[s];
+      m /= f.radix[s];
+      lp.M[s] = m;
+      max_nb = std::max(max_nb, N / f.radix[s]);
+    }
+    lp.padq = (rlast % 2 == 0) ? rlast : 0;
+    lp.smem_bytes = smem;
+    lp.static_id = sid;
+    lp.nthreads = sid >= 0 ? st_threads : std::min(512, std::max(32, ((max_nb + 31) / 32) * 32));
+    return true;
+  }
+  return false;
+}
+
+// tw[s][(j-1)*M + m] = exp(-2 pi i m j / (R*M)) as (cos, -sin) pairs, concatenated over s < S-1.
+inline void build_twiddles(const LinePlan& lp, std::vector<float>& flat, size_t offsets[kHostMaxStages]) {
+  flat.clear();
+  for (int s = 0; s < lp.nstages - 1; ++s) {
+    const int R = lp.radix[s], M = lp.M[s];
+    const long long B = (long long)R * M;
+    offsets[s] = flat.size() / 2;
+    for (int j = 1; j < R; ++j)
+      for (int m = 0; m < M; ++m) {
+        const long long e = ((long long)m * j) % B;
+        const double a = kTwoPi * (double)e / (double)B;
+        flat.push_back((float)std::cos(a));
+        flat.push_back((float)(-std::sin(a)));
+      }
+  }
+}
+
+// Gains in the digit-reversed position order the forward (decimation-in-frequency) stages leave
+// the spectrum in, pre-scaled by 1/N, with the reference's Nyquist behaviour: the bin N/2 is
+// multiplied by K[0] (src/gaussianblur.cpp:62-79 with pffft.h:143-146).
+inline std::vector<float> build_kperm(const LinePlan& lp, const std::vector<double>& gains) {
+  const int N = lp.N;
+  std::vector<float> kp((size_t)N);
+  for (int p = 0; p < N; ++p) {
+    int rem = p;
+    long long k = 0, weight = 1;
+    for (int s = 0; s < lp.nstages; ++s) {
+      const int digit = rem / lp.M[s];
+      rem -= digit * lp.M[s];
+      k += digit * weight;
+      weight *= lp.radix[s];
+    }
+    const int kk = (int)std::min<long long>(k, N - k);
+    const double g = (kk == N / 2) ? gains[0] : gains[(size_t)kk];
+    kp[(size_t)p] = (float)(g / (double)N);
+  }
+  return kp;
+}
+
+}  // namespace host
+}  // namespace gblur

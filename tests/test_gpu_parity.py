@@ -1,0 +1,218 @@
+"""GPU parity tests (pytest -m gpu): the CUDA path, called through the C ABI, against
+(1) the golden vectors minted from the compiled reference, (2) the compiled reference itself when
+oracle/_ref travelled with the repo (else the pinned numpy restatement), on the same seeded inputs.
+Bar (BASELINE.json north_star): max |delta| <= 1 LSB per 8-bit channel; fp32 row-pass
+intermediate within 5e-4 absolute; kernel spectra within 1e-4 of max|K|.
+Nothing here reads /root/reference."""
+import numpy as np
+import pytest
+
+from oracle import gblur_oracle as go
+from tests.cases import DIGEST_CASES, SMALL_CASES, make_input
+
+pytestmark = pytest.mark.gpu
+
+LSB = 1
+INTER_TOL = 5e-4
+
+
+def _blur_gpu(gb, img, sigma, alpha):
+    ch = 1 if img.ndim == 2 else img.shape[2]
+    plan = gb.Plan(img.shape[0], img.shape[1], ch, sigma)
+    out = img.copy()
+    plan.run_host(out, alpha)
+    inter = plan.dump_intermediate(alpha)
+    rad = (plan.radices(0), plan.radices(1))
+    plan.close()
+    return out, inter, rad
+
+
+def _assert_close_u8(out, want, what):
+    d = np.abs(out.astype(np.int16) - want.astype(np.int16))
+    assert d.max() <= LSB, f"{what}: max |delta| = {d.max()} LSB at {np.unravel_index(d.argmax(), d.shape)}"
+    return float((d > 0).mean())
+
+
+def test_native_library_is_what_runs(gb):
+    import torch
+
+    assert torch.cuda.is_available()
+    assert gb.lib().gblur_device_count() >= 1
+    before = gb.launch_count()
+    img = go.synth_u8((32, 32, 3), 1)
+    gb.gaussianblur(img, 2.0, False)
+    assert gb.launch_count() - before == 2  # row pass + column pass
+
+
+@pytest.mark.parametrize("case", SMALL_CASES, ids=[c[0] for c in SMALL_CASES])
+def test_small_cases_vs_golden(gb, golden_small, case):
+    name, rows, cols, ch, sigma, alpha, pat = case
+    img = make_input(rows, cols, ch, pat)
+    out, inter, _ = _blur_gpu(gb, img, sigma, alpha)
+    _assert_close_u8(out, golden_small[name], name)
+    cp = 3 if (ch == 4 and not alpha) else ch
+    got = inter.reshape(rows, cols, cp)[..., 0]
+    assert np.abs(got - golden_small[name + "__rowpass_ch0"]).max() < INTER_TOL
+    if ch == 4 and not alpha:
+        assert np.array_equal(out[..., 3], img[..., 3])  # alpha untouched bit for bit
+
+
+def test_gray_plane_vs_golden(gb, golden_small):
+    plane = go.synth_u8((48, 64), 0x1234 + 3)
+    out, _, _ = _blur_gpu(gb, plane, 4.0, False)
+    _assert_close_u8(out, golden_small["gray_48x64_s4"], "gray")
+
+
+@pytest.mark.parametrize("case", DIGEST_CASES, ids=[c[0] for c in DIGEST_CASES])
+def test_medium_cases_vs_reference(gb, refcheck, golden_digests, case):
+    name, rows, cols, ch, sigma, alpha, pat = case
+    img = make_input(rows, cols, ch, pat)
+    out, inter, rad = _blur_gpu(gb, img, sigma, alpha)
+    want = refcheck.blur(img, sigma, alpha)
+    frac = _assert_close_u8(out, want, name)
+    assert frac < 0.02, f"{name}: {frac:.4f} of the bytes differ by 1 LSB (expected only rounding-boundary flips)"
+    rec = golden_digests["outputs"][name]
+    step = max(1, out.size // 64)
+    sample = out.reshape(-1)[::step][:64].astype(int)
+    assert np.abs(sample - np.array(rec["sample"])).max() <= LSB
+    assert abs(int(out.astype(np.uint64).sum()) - rec["sum"]) <= out.size * 0.02
+    cp = 3 if (ch == 4 and not alpha) else ch
+    got = inter.reshape(rows, cols, cp)[..., 1]
+    assert np.abs(got - refcheck.rowpass(img, 1, sigma)).max() < INTER_TOL
+
+
+@pytest.mark.parametrize("sigma", [0.3, 1.0, 3.0, 5.0, 20.0, 50.0])
+@pytest.mark.parametrize("pat", ["synth", "altcols", "altrows", "checker", "const255", "impulse", "hramp", "vramp"])
+def test_adversarial_patterns(gb, refcheck, pat, sigma):
+    rows, cols, ch = 270, 480, 4
+    img = make_input(rows, cols, ch, pat)
+    out, _, _ = _blur_gpu(gb, img, sigma, True)
+    _assert_close_u8(out, refcheck.blur(img, sigma, True), f"{pat} sigma={sigma}")
+
+
+@pytest.mark.parametrize("shape", [(3, 3, 3), (4, 4, 3), (5, 7, 4), (17, 33, 3), (33, 17, 4), (31, 97, 3), (1, 40, 3),
+                                   (40, 1, 3), (2, 2, 4), (129, 255, 3), (200, 333, 4)])
+def test_small_odd_shapes(gb, refcheck, shape):
+    rows, cols, ch = shape
+    img = go.synth_u8(shape, 99)
+    for sigma in (0.5, 1.0, 2.0):
+        sz = gb.host_plan_sizes(rows, cols, sigma)
+        if sz["pad"] > min(rows, cols) - 1:
+            with pytest.raises(gb.GblurError) as ei:  # reference precondition (it reads out of bounds)
+                gb.Plan(rows, cols, ch, sigma)
+            assert ei.value.code == 2
+            continue
+        for alpha in (False, True):
+            out, _, _ = _blur_gpu(gb, img, sigma, alpha)
+            _assert_close_u8(out, refcheck.blur(img, sigma, alpha), f"{shape} sigma={sigma} alpha={alpha}")
+
+
+@pytest.mark.parametrize("n_target", [96, 160, 192, 288, 320, 480, 576, 800, 864, 960, 1440, 2400, 2592, 4000, 6912])
+def test_many_fft_lengths_runtime_radix_kernel(gb, refcheck, n_target):
+    """Line lengths chosen so the row pass lands on FFT length n_target (mixed radices 2/3/5)."""
+    sigma = 2.0
+    pad = (go.gaussian_window(sigma, 10000) - 1) // 2
+    cols = n_target - 2 * pad
+    rows = 24
+    assert gb.host_plan_sizes(rows, cols, sigma)["n_rowpass"] == n_target
+    for ch in (3, 4):
+        img = go.synth_u8((rows, cols, ch), n_target)
+        out, _, _ = _blur_gpu(gb, img, sigma, True)
+        _assert_close_u8(out, refcheck.blur(img, sigma, True), f"N={n_target} ch={ch}")
+
+
+def test_single_sequence_kernel_long_lines(gb, refcheck):
+    """FFT length 17280 does not fit two sequences in shared memory -> one-sequence kernel."""
+    sigma = 3.0
+    cols = 17280 - 2 * ((go.gaussian_window(sigma, 20000) - 1) // 2)
+    lp = gb.host_line_plan(17280)
+    assert lp["nseq"] == 1
+    img = go.synth_u8((40, cols, 3), 5)
+    out, _, _ = _blur_gpu(gb, img, sigma, False)
+    _assert_close_u8(out, refcheck.blur(img, sigma, False), "N=17280")
+
+
+def test_spectra_within_1e4(gb, refcheck):
+    from oracle import ref_lib
+
+    for rows, cols, sigma in [(270, 480, 5.0), (1080, 1920, 5.0), (1080, 1920, 10.0)]:
+        plan = gb.Plan(rows, cols, 3, sigma)
+        mine0, mine1 = plan.spectrum(0), plan.spectrum(1)
+        plan.close()
+        ks, pad, n_rp, n_cp, *_ = go.plan_sizes(rows, cols, sigma)
+        if ref_lib.available():
+            k = ref_lib.kernel_dft(rows, cols, sigma)
+            want0, want1 = k["kerf_col"], k["kerf_row"]
+        else:
+            want0, want1 = go.kerf_ordered(sigma, ks, n_rp), go.kerf_ordered(sigma, ks, n_cp)
+        assert np.abs(mine0 - want0).max() < 1e-4 and np.abs(mine1 - want1).max() < 1e-4
+        big = np.abs(want0) > 1e-3
+        assert (np.abs(mine0 - want0)[big] / np.abs(want0)[big]).max() < 1e-4
+
+
+def test_device_buffers_in_place_and_out_of_place(gb, refcheck):
+    import torch
+
+    img = go.synth_u8((270, 480, 4), 3)
+    want = refcheck.blur(img, 5.0, False)
+    plan = gb.Plan(270, 480, 4, 5.0)
+    d_in = torch.from_numpy(img).cuda()
+    d_out = torch.zeros_like(d_in)
+    plan.run_device(d_in, d_out, apply_to_alpha=False)
+    torch.cuda.synchronize()
+    assert np.array_equal(d_in.cpu().numpy(), img)  # input untouched
+    _assert_close_u8(d_out.cpu().numpy(), want, "out of place")
+    assert np.array_equal(d_out.cpu().numpy()[..., 3], img[..., 3])
+    plan.run_device(d_in, None, apply_to_alpha=False)  # in place
+    torch.cuda.synchronize()
+    assert np.array_equal(d_in.cpu().numpy(), d_out.cpu().numpy())
+    plan.close()
+
+
+def test_batch_matches_per_frame(gb, refcheck):
+    frames = np.stack([go.synth_u8((135, 240, 3), 0x1234 + 2 + f) for f in range(5)])
+    plan = gb.Plan(135, 240, 3, 10.0, max_frames=5)
+    out = frames.copy()
+    plan.run_host(out, False, n_frames=5)
+    plan.close()
+    for f in range(5):
+        _assert_close_u8(out[f], refcheck.blur(frames[f], 10.0, False), f"frame {f}")
+
+
+def test_repeat_runs_are_bit_identical(gb):
+    img = go.synth_u8((270, 480, 4), 11)
+    plan = gb.Plan(270, 480, 4, 5.0)
+    a = plan.run_host(img.copy(), True)
+    b = plan.run_host(img.copy(), True)
+    plan.close()
+    assert np.array_equal(a, b)
+
+
+def test_band_passes_equal_whole_image(gb):
+    """Row bands through gblur_rowpass_device + column bands through gblur_colpass_device give
+    exactly the bytes of the single-GPU run (the band-sharded multi-GPU path, on one GPU)."""
+    import torch
+
+    rows, cols, ch, sigma, g = 96, 160, 3, 4.0, 4
+    img = go.synth_u8((rows, cols, ch), 21)
+    whole = gb.Plan(rows, cols, ch, sigma).run_host(img.copy(), False)
+    w = cols * ch
+    inter = torch.zeros((rows, w), dtype=torch.float32, device="cuda")
+    d_img = torch.from_numpy(img).cuda()
+    br = rows // g
+    for k in range(g):
+        p = gb.Plan(rows, cols, ch, sigma, band_rows=br, band_cols=cols)
+        p.rowpass(d_img[k * br:(k + 1) * br], inter[k * br:(k + 1) * br], w)
+        torch.cuda.synchronize()
+        p.close()
+    out = torch.zeros((rows, cols, ch), dtype=torch.uint8, device="cuda")
+    bc = cols // g
+    for k in range(g):
+        p = gb.Plan(rows, cols, ch, sigma, band_rows=rows, band_cols=bc)
+        band_inter = inter[:, k * bc * ch:(k + 1) * bc * ch].contiguous()
+        band_out = torch.zeros((rows, bc, ch), dtype=torch.uint8, device="cuda")
+        p.colpass(band_inter, bc * ch, band_out, bc * ch)
+        torch.cuda.synchronize()
+        out[:, k * bc:(k + 1) * bc] = band_out
+        p.close()
+    assert np.array_equal(out.cpu().numpy(), whole)
