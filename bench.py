@@ -50,64 +50,78 @@ def load_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region."""
+    """SM clocks and throttle reasons sampled DURING the timed region (NVML in a thread, 5 ms period;
+    falls back to one `nvidia-smi` query)."""
 
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
-         "clocks_event_reasons.sw_power_cap")
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
 
     def __init__(self, gpu_index: int):
         self.idx = gpu_index
-        self.proc = None
-        self.lines = []
+        self.sm, self.reasons, self.power = [], set(), []
+        self.smax = None
+        self._stop = threading.Event()
+        self.thread = None
+        self.nvml = None
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i",
-                 str(self.idx)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-            self.thread = threading.Thread(target=self._read, daemon=True)
-            self.thread.start()
-        except Exception:
-            self.proc = None
+            import pynvml
 
-    def _read(self):
-        for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = self.idx
+            if vis:
+                try:
+                    phys = int(vis.split(",")[self.idx])
+                except ValueError:
+                    phys = self.idx
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(phys)
+            self.smax = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.nvml = None
+            return
+        self.thread = threading.Thread(target=self._loop, daemon=True)
+        self.thread.start()
+
+    def _loop(self):
+        n = self.nvml
+        while not self._stop.is_set():
+            try:
+                self.sm.append(float(n.nvmlDeviceGetClockInfo(self.h, n.NVML_CLOCK_SM)))
+                mask = int(n.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                for bit, name in self.REASONS.items():
+                    if mask & bit:
+                        self.reasons.add(name)
+                self.power.append(n.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+            except Exception:
+                pass
+            time.sleep(0.005)
 
     def stop(self):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
-        sm, smax, reasons = [], [], set()
-        for ln in self.lines:
-            f = [x.strip() for x in ln.split(",")]
-            if len(f) < 8:
-                continue
+        if self.nvml is None:
             try:
-                sm.append(float(f[1]))
-                smax.append(float(f[2]))
-            except ValueError:
-                continue
-            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+                out = subprocess.run(["nvidia-smi", "--query-gpu=clocks.sm,clocks.max.sm", "--format=csv,noheader,nounits",
+                                      "-i", str(self.idx)], capture_output=True, text=True, timeout=20).stdout
+                a, b = [float(x) for x in out.strip().split(",")]
+                return {"sm_mhz": a, "sm_max_mhz": b, "samples": 1, "reasons": [], "note": "single idle sample"}
+            except Exception:
+                return {"sm_mhz": None, "sm_max_mhz": None, "samples": 0, "reasons": ["clock query unavailable"]}
+        self._stop.set()
+        self.thread.join(timeout=2)
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None, "sm_max_mhz": self.smax,
+                "samples": len(self.sm), "power_w_max": max(self.power) if self.power else None,
+                "reasons": sorted(self.reasons)}
 
 
 def cpu_reference_run(rows, cols, ch, sigma, alpha, runs, warm=1):
     """Times gaussianblur::gaussianblur of the compiled reference on all host cores."""
-    from oracle import gblur_oracle as go
-    from oracle import ref_lib
+    from libgaussianblur_b200.synth import synth_u8
+    from oracle import ref_lib  # the compiled, unmodified reference: the thing this leg measures
 
     if not ref_lib.available():
         return None
-    img = go.synth_u8((rows, cols, ch), 0x1234 + 1)
+    img = synth_u8((rows, cols, ch), 0x1234 + 1)
     times = []
     for i in range(warm + runs):
         _, secs = ref_lib.gaussianblur(img, sigma, alpha, return_seconds=True)
@@ -160,7 +174,7 @@ def main():
     import torch.distributed as dist
 
     import libgaussianblur_b200 as gb
-    from oracle import gblur_oracle as go  # synthetic input generator only
+    from libgaussianblur_b200.synth import synth_u8
 
     rows, cols, ch, sigma, alpha = WORKLOADS[wl]
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -180,7 +194,7 @@ def main():
     gb.lib()
     plan = gb.Plan(rows, cols, ch, sigma, device=local)
     npx = rows * cols
-    img = go.synth_u8((rows, cols, ch), 0x1234 + 1 + rank)
+    img = synth_u8((rows, cols, ch), 0x1234 + 1 + rank)
     h_pinned = torch.from_numpy(img.copy()).pin_memory()
     d_in = torch.from_numpy(img).cuda()
     d_out = torch.empty_like(d_in)
