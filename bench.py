@@ -220,11 +220,9 @@ def main():
 
     # ---- per-kernel durations (same stream, CUDA events) for the roofline ----
     cp = plan.processed_channels(alpha)
-    pitch = (cols * cp + 3) // 4 * 4
-    inter = torch.empty((rows, pitch), dtype=torch.float32, device="cuda")
     kern_ms = {}
-    for name, fn in (("row_pass", lambda: plan.rowpass(d_in, inter, pitch, alpha)),
-                     ("col_pass", lambda: plan.colpass(inter, pitch, d_out, cols * ch, alpha))):
+    for name, fn in (("row_pass", lambda: plan.run_stage(1, d_in, d_out, alpha)),
+                     ("col_pass", lambda: plan.run_stage(2, d_in, d_out, alpha))):
         for _ in range(3):
             fn()
         torch.cuda.synchronize()

@@ -69,6 +69,11 @@ int gblur_run_device(gblur_plan* plan, const uint8_t* d_in, uint8_t* d_out, int 
 int gblur_run_batch_device(gblur_plan* plan, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
                            void* cuda_stream);
 
+/* Profiling hook: the same fused run restricted to stages = 1 (row pass into the plan's workspace),
+ * 2 (column pass out of it) or 3 (both); lets bench.py time each kernel with CUDA events. */
+int gblur_run_stage_device(gblur_plan* plan, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
+                           void* cuda_stream, int stages);
+
 /* The two passes separately, for band sharding. Row pass: u8 [band_rows][cols*channels] ->
  * fp32 [band_rows][inter_pitch] with element (r, x*Cp + ch), Cp = processed channels.
  * Column pass: fp32 [full_rows][inter_pitch] holding band_cols*Cp valid columns -> u8

@@ -27,7 +27,7 @@ __all__ = ["Plan", "GblurError", "lib", "gaussianblur", "gaussianblur_module", "
 EXPORTED_SYMBOLS = [
     "gblur_plan_create", "gblur_plan_create_batch", "gblur_plan_create_band", "gblur_plan_destroy",
     "gblur_plan_info", "gblur_plan_spectrum", "gblur_plan_radices", "gblur_run_host", "gblur_run_batch_host",
-    "gblur_run_device", "gblur_run_batch_device", "gblur_rowpass_device", "gblur_colpass_device",
+    "gblur_run_device", "gblur_run_batch_device", "gblur_run_stage_device", "gblur_rowpass_device", "gblur_colpass_device",
     "gblur_dump_intermediate", "gblur_launch_count", "gblur_last_error", "gblur_device_count",
     "gblur_host_plan_sizes", "gblur_host_taps", "gblur_host_spectrum", "gblur_host_line_plan", "gblur_host_kperm",
 ]
@@ -66,6 +66,7 @@ def lib():
         "gblur_run_batch_host": (C.c_int, [vp, u8p, C.c_int, C.c_int]),
         "gblur_run_device": (C.c_int, [vp, u8p, u8p, C.c_int, vp]),
         "gblur_run_batch_device": (C.c_int, [vp, u8p, u8p, C.c_int, C.c_int, vp]),
+        "gblur_run_stage_device": (C.c_int, [vp, u8p, u8p, C.c_int, C.c_int, vp, C.c_int]),
         "gblur_rowpass_device": (C.c_int, [vp, u8p, vp, ll, C.c_int, vp]),
         "gblur_colpass_device": (C.c_int, [vp, vp, ll, u8p, ll, C.c_int, vp]),
         "gblur_dump_intermediate": (C.c_int, [vp, fp, C.c_int]),
@@ -214,6 +215,12 @@ class Plan:
         _check(lib().gblur_run_batch_device(self._h, _ptr(d_in), _ptr(d_out), n_frames, int(bool(apply_to_alpha)),
                                             _stream_ptr(stream)))
         return d_out
+
+    def run_stage(self, stages: int, d_in, d_out=None, apply_to_alpha: bool = False, n_frames: int = 1, stream=None):
+        """Profiling hook: 1 = row pass only, 2 = column pass only, 3 = both (same kernels as run_device)."""
+        d_out = d_in if d_out is None else d_out
+        _check(lib().gblur_run_stage_device(self._h, _ptr(d_in), _ptr(d_out), n_frames, int(bool(apply_to_alpha)),
+                                            _stream_ptr(stream), stages))
 
     def rowpass(self, d_in, d_inter, inter_pitch_floats: int, apply_to_alpha: bool = False, stream=None):
         _check(lib().gblur_rowpass_device(self._h, _ptr(d_in), _ptr(d_inter), inter_pitch_floats,

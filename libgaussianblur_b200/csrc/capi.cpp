@@ -72,7 +72,9 @@ struct gblur_plan {
   uint8_t* d_stage = nullptr;  // device image for gblur_run_host
   size_t stage_bytes = 0;
   cudaStream_t stream = nullptr;
-  int last_cp = 0;
+  int last_cp = 0;       // processed channels of the last run (layout of d_inter)
+  int inter_cp = 0;      // processed-channel count the blocked workspace is currently laid out for
+  int last_frames = 0;
 };
 
 namespace {
@@ -108,6 +110,20 @@ int processed_channels(const gblur_plan* p, int apply_to_alpha) {
 }
 
 long long default_pitch(long long w) { return (w + 3) / 4 * 4; }
+
+// Blocked intermediate of the fused run: one contiguous unit of np slots x L floats per column group.
+BlockedLayout blocked_layout(const gblur_plan* p, int cp) {
+  BlockedLayout b;
+  const LinePlan& c = p->col.lp;
+  b.enabled = 1;
+  b.L = 2 * c.nseq;
+  b.np = (int)(c.smem_bytes / (8 * (size_t)c.nseq));
+  b.padq = c.padq;
+  b.rows_per_frame = p->full_rows;
+  const long long groups = ((long long)p->cols * cp + b.L - 1) / b.L;
+  b.frame_stride = groups * b.np * b.L;
+  return b;
+}
 
 int ensure_inter(gblur_plan* p, size_t floats) {
   if (p->inter_floats >= floats) return GBLUR_OK;
@@ -169,7 +185,7 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
 }
 
 int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pitch, int frames, int alpha,
-                cudaStream_t s) {
+                cudaStream_t s, const BlockedLayout* blk = nullptr) {
   const int cp = processed_channels(p, alpha);
   RowLaunch a{};
   a.in = d_in;
@@ -181,12 +197,13 @@ int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pi
   a.rows_total = (long long)p->rows * frames;
   a.inter = d_inter;
   a.inter_pitch = pitch;
+  if (blk) a.blk = *blk;
   CU(launch_rowpass(p->row.lp, a, p->num_sms, s));
   return GBLUR_OK;
 }
 
 int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d_out, long long out_pitch, int frames,
-                int alpha, cudaStream_t s) {
+                int alpha, cudaStream_t s, const BlockedLayout* blk = nullptr) {
   const int cp = processed_channels(p, alpha);
   ColLaunch a{};
   a.inter = d_inter;
@@ -201,6 +218,7 @@ int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d
   a.out_frame_stride = (long long)p->full_rows * out_pitch;
   a.C = p->channels;
   a.Cp = cp;
+  if (blk) a.blk = *blk;
   CU(launch_colpass(p->col.lp, a, p->num_sms, s));
   return GBLUR_OK;
 }
@@ -279,8 +297,8 @@ int gblur_plan_radices(const gblur_plan* p, int axis, int* radices, int* n, int*
   return GBLUR_OK;
 }
 
-int gblur_run_batch_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
-                           void* cuda_stream) {
+static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
+                     void* cuda_stream, int stages) {
   if (!p || !d_in || !d_out) return fail(GBLUR_E_INVALID, "null argument");
   if (p->band) return fail(GBLUR_E_INVALID, "band plans run through gblur_rowpass_device / gblur_colpass_device");
   if (n_frames < 1 || n_frames > p->max_frames)
@@ -288,15 +306,37 @@ int gblur_run_batch_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, i
   DeviceGuard guard(p->device);
   cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
   const int cp = processed_channels(p, apply_to_alpha);
-  const long long pitch = default_pitch((long long)p->cols * cp);
-  int rc = ensure_inter(p, (size_t)p->max_frames * p->rows * default_pitch((long long)p->cols * p->channels));
+  // workspace sized for the widest layout (all channels processed)
+  const BlockedLayout widest = blocked_layout(p, p->channels);
+  int rc = ensure_inter(p, (size_t)p->max_frames * (size_t)widest.frame_stride);
   if (rc != GBLUR_OK) return rc;
-  rc = run_rowpass(p, d_in, p->d_inter, pitch, n_frames, apply_to_alpha, s);
-  if (rc != GBLUR_OK) return rc;
+  const BlockedLayout blk = blocked_layout(p, cp);
+  if (p->inter_cp != 0 && p->inter_cp != cp) {
+    // the zero tail / padding slots of the new layout may hold samples of the old one
+    CU(cudaMemsetAsync(p->d_inter, 0, p->inter_floats * sizeof(float), s));
+  }
+  p->inter_cp = cp;
+  if (stages & 1) {
+    rc = run_rowpass(p, d_in, p->d_inter, 0, n_frames, apply_to_alpha, s, &blk);
+    if (rc != GBLUR_OK) return rc;
+  }
+  p->last_cp = cp;
+  p->last_frames = n_frames;
+  if (!(stages & 2)) return GBLUR_OK;
   if (d_in != d_out && cp < p->channels)
     CU(launch_copy_channel(d_in, d_out, (long long)p->rows * p->cols * n_frames, p->channels, 3, s));
-  p->last_cp = cp;
-  return run_colpass(p, p->d_inter, pitch, d_out, (long long)p->cols * p->channels, n_frames, apply_to_alpha, s);
+  return run_colpass(p, p->d_inter, 0, d_out, (long long)p->cols * p->channels, n_frames, apply_to_alpha, s, &blk);
+}
+
+int gblur_run_batch_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
+                           void* cuda_stream) {
+  return run_fused(p, d_in, d_out, n_frames, apply_to_alpha, cuda_stream, 3);
+}
+
+int gblur_run_stage_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
+                           void* cuda_stream, int stages) {
+  if (stages < 1 || stages > 3) return fail(GBLUR_E_INVALID, "stages must be 1 (row), 2 (column) or 3 (both)");
+  return run_fused(p, d_in, d_out, n_frames, apply_to_alpha, cuda_stream, stages);
 }
 
 int gblur_run_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int apply_to_alpha, void* cuda_stream) {
@@ -351,13 +391,21 @@ int gblur_colpass_device(gblur_plan* p, const float* d_inter, long long inter_pi
 
 int gblur_dump_intermediate(gblur_plan* p, float* host_out, int apply_to_alpha) {
   if (!p || !host_out) return fail(GBLUR_E_INVALID, "null argument");
-  if (!p->d_inter) return fail(GBLUR_E_INVALID, "no run has happened on this plan");
+  if (!p->d_inter || p->inter_cp == 0) return fail(GBLUR_E_INVALID, "no run has happened on this plan");
   DeviceGuard guard(p->device);
   const int cp = processed_channels(p, apply_to_alpha);
-  const long long w = (long long)p->cols * cp, pitch = default_pitch(w);
+  if (cp != p->inter_cp) return fail(GBLUR_E_INVALID, "last run used a different apply_to_alpha");
+  const BlockedLayout b = blocked_layout(p, cp);
+  std::vector<float> blk((size_t)b.frame_stride);
   CU(cudaDeviceSynchronize());
-  CU(cudaMemcpy2D(host_out, (size_t)w * sizeof(float), p->d_inter, (size_t)pitch * sizeof(float),
-                  (size_t)w * sizeof(float), (size_t)p->rows, cudaMemcpyDeviceToHost));
+  CU(cudaMemcpy(blk.data(), p->d_inter, blk.size() * sizeof(float), cudaMemcpyDeviceToHost));
+  const long long w = (long long)p->cols * cp;
+  for (int r = 0; r < p->rows; ++r) {
+    const int n = p->sz.pad + r;
+    const long long slot = b.padq ? n + n / b.padq : n;
+    for (long long x = 0; x < w; ++x)
+      host_out[(size_t)r * w + x] = blk[(size_t)((x / b.L) * b.np + slot) * b.L + (size_t)(x % b.L)];
+  }
   return GBLUR_OK;
 }
 

@@ -202,7 +202,9 @@ __device__ __forceinline__ void inv_stage(const Storer& st, typename SmemElem<NS
 // radices the runtime-dispatched (any valid N) kernel may use
 #define GBLUR_FOR_EACH_GENERIC_RADIX(X) X(2) X(3) X(4) X(5) X(6) X(8) X(9) X(10) X(12) X(15) X(16)
 
-template <int NSEQ, class Loader, class Storer>
+// SMEM_IN: the padded line already sits in shared memory (bulk-copied there), so stage 0 reads it
+// in place instead of calling the loader.
+template <int NSEQ, bool SMEM_IN, class Loader, class Storer>
 __device__ __forceinline__ void run_line_generic(const LineShape& sh, const Loader& ld, const Storer& st,
                                                  typename SmemElem<NSEQ>::type* sm, int tid, int nthreads) {
   const int S = sh.nstages;
@@ -211,7 +213,7 @@ __device__ __forceinline__ void run_line_generic(const LineShape& sh, const Load
     switch (sh.radix[s]) {
 #define X(R_)                                                                                        \
   case R_:                                                                                           \
-    if (s == 0)                                                                                      \
+    if (s == 0 && !SMEM_IN)                                                                          \
       fwd_stage<R_, NSEQ, true>(ld, sm, sh.tw[s], sh.N, sh.M[s], sh.padq, tid, nthreads);            \
     else                                                                                             \
       fwd_stage<R_, NSEQ, false>(ld, sm, sh.tw[s], sh.N, sh.M[s], sh.padq, tid, nthreads);           \
@@ -256,11 +258,11 @@ struct StaticShape {
   static constexpr int M0 = N / R0, M1 = M0 / R1, M2 = M1 / R2;
 };
 
-template <int NSEQ, class SS, class Loader, class Storer>
+template <int NSEQ, class SS, bool SMEM_IN, class Loader, class Storer>
 __device__ __forceinline__ void run_line_static(const LineShape& sh, const Loader& ld, const Storer& st,
                                                 typename SmemElem<NSEQ>::type* sm, int tid, int nthreads) {
   constexpr int N = SS::N, PQ = SS::PADQ;
-  fwd_stage<N / SS::M0, NSEQ, true>(ld, sm, sh.tw[0], N, SS::M0, PQ, tid, nthreads);
+  fwd_stage<N / SS::M0, NSEQ, !SMEM_IN>(ld, sm, sh.tw[0], N, SS::M0, PQ, tid, nthreads);
   __syncthreads();
   if constexpr (SS::S >= 3) {
     fwd_stage<SS::M0 / SS::M1, NSEQ, false>(ld, sm, sh.tw[1], N, SS::M1, PQ, tid, nthreads);

@@ -2,11 +2,16 @@
 #include "line_kernels.cuh"
 
 namespace gblur {
-cudaError_t launch_row_generic(const LinePlan& lp, const RowParams& P, bool rgba, int num_sms, cudaStream_t s) {
+cudaError_t launch_row_generic(const LinePlan& lp, const RowParams& P, bool rgba, bool blocked, int num_sms,
+                               cudaStream_t s) {
+  const int nt = lp.nthreads;
   if (lp.nseq == 2) {
-    if (rgba) return launch_line<line_kernel_generic<2, RowProblemRGBA, RowParams>>(lp, P, lp.nthreads, num_sms, s);
-    return launch_line<line_kernel_generic<2, RowProblemGeneric<2>, RowParams>>(lp, P, lp.nthreads, num_sms, s);
+    if (rgba && blocked) return launch_line<line_kernel_generic<2, RowProblemRGBA<true>, RowParams>>(lp, P, nt, num_sms, s);
+    if (rgba) return launch_line<line_kernel_generic<2, RowProblemRGBA<false>, RowParams>>(lp, P, nt, num_sms, s);
+    if (blocked) return launch_line<line_kernel_generic<2, RowProblemGeneric<2, true>, RowParams>>(lp, P, nt, num_sms, s);
+    return launch_line<line_kernel_generic<2, RowProblemGeneric<2, false>, RowParams>>(lp, P, nt, num_sms, s);
   }
-  return launch_line<line_kernel_generic<1, RowProblemGeneric<1>, RowParams>>(lp, P, lp.nthreads, num_sms, s);
+  if (blocked) return launch_line<line_kernel_generic<1, RowProblemGeneric<1, true>, RowParams>>(lp, P, nt, num_sms, s);
+  return launch_line<line_kernel_generic<1, RowProblemGeneric<1, false>, RowParams>>(lp, P, nt, num_sms, s);
 }
 }  // namespace gblur

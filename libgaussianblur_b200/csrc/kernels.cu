@@ -3,6 +3,8 @@
 #include "kernels.h"
 
 #include <atomic>
+#include <cstdio>
+#include <cstdlib>
 
 #include "line_kernels.cuh"
 #include "static_shapes.h"
@@ -30,12 +32,22 @@ static const StaticEntry kStaticTable[] = {
 };
 
 int find_static_shape(int N, int nseq, int* radices, int* nthreads) {
+  // tuning override: GBLUR_VARIANT_<N>=<id> forces one table entry for that FFT length
+  char name[64];
+  snprintf(name, sizeof name, "GBLUR_VARIANT_%d", N);
+  const char* forced = getenv(name);
+  const int forced_id = forced ? atoi(forced) : -1;
   for (const auto& e : kStaticTable) {
-    if (e.nseq == nseq && e.r[0] * e.r[1] * e.r[2] * e.r[3] == N) {
-      for (int i = 0; i < 4; ++i) radices[i] = e.r[i];
-      *nthreads = e.nthreads;
-      return e.id;
-    }
+    if (e.r[0] * e.r[1] * e.r[2] * e.r[3] != N) continue;
+    if (forced_id >= 0 ? (e.id != forced_id || e.nseq != nseq) : (e.nseq != nseq)) continue;
+    for (int i = 0; i < 4; ++i) radices[i] = e.r[i];
+    *nthreads = e.nthreads;
+    return e.id;
+  }
+  if (forced_id >= 0) {
+    // a forced variant with the other sequence count must win over the default of this count
+    for (const auto& e : kStaticTable)
+      if (e.id == forced_id && e.r[0] * e.r[1] * e.r[2] * e.r[3] == N) return -2;
   }
   return -1;
 }
@@ -55,16 +67,24 @@ cudaError_t launch_rowpass(const LinePlan& lp, const RowLaunch& a, int num_sms, 
   P.inter_pitch = a.inter_pitch;
   const long long L = 2 * lp.nseq;
   P.nunits = (int)((P.nreal + L - 1) / L);
-  const bool rgba = lp.nseq == 2 && a.C == 4 && a.Cp == 4 && (a.in_pitch % 4) == 0 && (a.inter_pitch % 4) == 0 &&
-                    (reinterpret_cast<uintptr_t>(a.in) % 4) == 0 && (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0;
+  const bool blocked = a.blk.enabled != 0;
+  P.rows_per_frame = blocked ? a.blk.rows_per_frame : 1;
+  P.blk_L = a.blk.L;
+  P.blk_np = a.blk.np;
+  P.blk_padq = a.blk.padq;
+  P.blk_frame_stride = a.blk.frame_stride;
+  // uchar4/float4 (two sequences) or u16/float2 (one sequence, static shapes only) fast path
+  const bool rgba = (lp.nseq == 2 || lp.static_id >= 0) && a.C == 4 && a.Cp == 4 && (a.in_pitch % 4) == 0 &&
+                    (reinterpret_cast<uintptr_t>(a.in) % 4) == 0 && (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0 &&
+                    (blocked ? a.blk.L == 4 : (a.inter_pitch % 4) == 0);
   switch (lp.static_id) {
 #define X(ID, NSEQ, R0, R1, R2, R3, NT, MINB) \
   case ID:                                    \
-    return launch_row_static<ID>(lp, P, rgba, num_sms, stream);
+    return launch_row_static<ID>(lp, P, rgba, blocked, num_sms, stream);
     GBLUR_STATIC_SHAPES(X)
 #undef X
     default:
-      return launch_row_generic(lp, P, rgba, num_sms, stream);
+      return launch_row_generic(lp, P, rgba, blocked, num_sms, stream);
   }
 }
 
@@ -84,16 +104,20 @@ cudaError_t launch_colpass(const LinePlan& lp, const ColLaunch& a, int num_sms, 
   P.out_frame_stride = a.out_frame_stride;
   P.C = a.C;
   P.Cp = a.Cp;
+  const bool blocked = a.blk.enabled != 0;
+  P.unit_stride = (long long)a.blk.np * a.blk.L;
+  P.unit_bytes = (unsigned)(P.unit_stride * 4);
+  if (blocked) P.frame_stride = a.blk.frame_stride;
   const bool packed = a.C == a.Cp && (a.W % L) == 0 && (a.out_pitch % L) == 0 && (a.out_frame_stride % L) == 0 &&
                       (reinterpret_cast<uintptr_t>(a.out) % L) == 0;
   switch (lp.static_id) {
 #define X(ID, NSEQ, R0, R1, R2, R3, NT, MINB) \
   case ID:                                    \
-    return launch_col_static<ID>(lp, P, packed, num_sms, stream);
+    return launch_col_static<ID>(lp, P, packed, blocked, num_sms, stream);
     GBLUR_STATIC_SHAPES(X)
 #undef X
     default:
-      return launch_col_generic(lp, P, packed, num_sms, stream);
+      return launch_col_generic(lp, P, packed, blocked, num_sms, stream);
   }
 }
 

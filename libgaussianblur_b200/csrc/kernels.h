@@ -24,6 +24,17 @@ struct LinePlan {
   size_t smem_bytes = 0; // dynamic shared memory per CTA
 };
 
+// Blocked intermediate [frame][group][np slots][L floats] (see problems.cuh): written by the row
+// pass, bulk-copied unit by unit by the column pass. enabled == 0: row-major [rows][pitch].
+struct BlockedLayout {
+  int enabled = 0;
+  int L = 4;                   // floats per column group = 2 * column nseq
+  int np = 0;                  // slots per unit (column FFT length + bank padding slots)
+  int padq = 0;                // column plan's padq
+  int rows_per_frame = 0;
+  long long frame_stride = 0;  // floats per frame = groups * np * L
+};
+
 struct RowLaunch {
   const uint8_t* in;
   long long in_pitch;
@@ -32,6 +43,7 @@ struct RowLaunch {
   long long rows_total;
   float* inter;
   long long inter_pitch;
+  BlockedLayout blk;
 };
 
 struct ColLaunch {
@@ -45,6 +57,7 @@ struct ColLaunch {
   long long out_pitch;
   long long out_frame_stride;
   int C, Cp;
+  BlockedLayout blk;
 };
 
 // Returns the static shape id for (N, nseq) or -1; fills radices when found.

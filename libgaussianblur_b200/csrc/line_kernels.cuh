@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include "async_copy.cuh"
 #include "fftconv.cuh"
 #include "kernels.h"
 #include "problems.cuh"
@@ -11,29 +12,59 @@ namespace gblur {
 
 void count_launch();  // kernels.cu
 
+// Stage one unit into shared memory with a single bulk copy (BULK problems). The exchange buffer
+// was last touched through the generic proxy, hence the proxy fence before the async write.
+template <class Problem, class Params>
+__device__ __forceinline__ void bulk_stage_unit(const Params& P, int unit, void* sm, uint64_t* bar,
+                                                uint32_t& parity) {
+  if (threadIdx.x == 0) {
+    fence_proxy_async();
+    mbar_expect_tx(bar, P.unit_bytes);
+    bulk_g2s(sm, Problem::bulk_src(P, unit), P.unit_bytes, bar);
+  }
+  mbar_wait(bar, parity);
+  parity ^= 1u;
+}
+
 template <int NSEQ, class Problem, class Params>
 __global__ void __launch_bounds__(512, 1)
     line_kernel_generic(const __grid_constant__ LineShape sh, const __grid_constant__ Params P) {
   extern __shared__ float4 smem_raw[];
   auto* sm = reinterpret_cast<typename SmemElem<NSEQ>::type*>(smem_raw);
+  __shared__ uint64_t bar;
+  uint32_t parity = 0;
+  if constexpr (Problem::kBulkIn) {
+    if (threadIdx.x == 0) mbar_init(&bar, 1);
+    __syncthreads();
+  }
   for (int unit = blockIdx.x; unit < P.nunits; unit += gridDim.x) {
     typename Problem::Loader ld;
     typename Problem::Storer st;
     Problem::make(P, unit, ld, st);
-    run_line_generic<NSEQ>(sh, ld, st, sm, (int)threadIdx.x, (int)blockDim.x);
+    if constexpr (Problem::kBulkIn) bulk_stage_unit<Problem>(P, unit, sm, &bar, parity);
+    run_line_generic<NSEQ, Problem::kBulkIn>(sh, ld, st, sm, (int)threadIdx.x, (int)blockDim.x);
   }
 }
 
-template <int NSEQ, class SS, int NT, int MINB, class Problem, class Params>
-__global__ void __launch_bounds__(NT, MINB)
+// MAXREG is given to ptxas directly: with __launch_bounds__ it rounds the CTA size up (400 -> 512
+// threads) and caps at 128 registers, which spills the radix-20 butterflies.
+template <int NSEQ, class SS, int NT, int MAXREG, class Problem, class Params>
+__global__ void __maxnreg__(MAXREG)
     line_kernel_static(const __grid_constant__ LineShape sh, const __grid_constant__ Params P) {
   extern __shared__ float4 smem_raw[];
   auto* sm = reinterpret_cast<typename SmemElem<NSEQ>::type*>(smem_raw);
+  __shared__ uint64_t bar;
+  uint32_t parity = 0;
+  if constexpr (Problem::kBulkIn) {
+    if (threadIdx.x == 0) mbar_init(&bar, 1);
+    __syncthreads();
+  }
   for (int unit = blockIdx.x; unit < P.nunits; unit += gridDim.x) {
     typename Problem::Loader ld;
     typename Problem::Storer st;
     Problem::make(P, unit, ld, st);
-    run_line_static<NSEQ, SS>(sh, ld, st, sm, (int)threadIdx.x, NT);
+    if constexpr (Problem::kBulkIn) bulk_stage_unit<Problem>(P, unit, sm, &bar, parity);
+    run_line_static<NSEQ, SS, Problem::kBulkIn>(sh, ld, st, sm, (int)threadIdx.x, NT);
   }
 }
 
@@ -63,7 +94,8 @@ cudaError_t launch_line(const LinePlan& lp, const Params& P, int nthreads, int n
   int device = 0;
   cudaGetDevice(&device);
   if (cached_smem != lp.smem_bytes || cached_threads != nthreads || cached_device != device) {
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)(lp.smem_bytes > 48 * 1024 ? lp.smem_bytes : 48 * 1024));
     if (e != cudaSuccess) return e;
     int per_sm = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, nthreads, lp.smem_bytes);
@@ -83,11 +115,14 @@ cudaError_t launch_line(const LinePlan& lp, const Params& P, int nthreads, int n
 }
 
 // entry points implemented one per translation unit
+// rgba: uchar4/float4 fast path; blocked: blocked intermediate; packed: aligned u16/u32 output stores
 template <int ID>
-cudaError_t launch_row_static(const LinePlan&, const RowParams&, bool rgba, int num_sms, cudaStream_t);
+cudaError_t launch_row_static(const LinePlan&, const RowParams&, bool rgba, bool blocked, int num_sms, cudaStream_t);
 template <int ID>
-cudaError_t launch_col_static(const LinePlan&, const ColParams&, bool packed, int num_sms, cudaStream_t);
-cudaError_t launch_row_generic(const LinePlan&, const RowParams&, bool rgba, int num_sms, cudaStream_t);
-cudaError_t launch_col_generic(const LinePlan&, const ColParams&, bool packed, int num_sms, cudaStream_t);
+cudaError_t launch_col_static(const LinePlan&, const ColParams&, bool packed, bool blocked, int num_sms,
+                              cudaStream_t);
+cudaError_t launch_row_generic(const LinePlan&, const RowParams&, bool rgba, bool blocked, int num_sms, cudaStream_t);
+cudaError_t launch_col_generic(const LinePlan&, const ColParams&, bool packed, bool blocked, int num_sms,
+                               cudaStream_t);
 
 }  // namespace gblur

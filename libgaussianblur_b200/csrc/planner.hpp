@@ -12,7 +12,7 @@
 namespace gblur {
 namespace host {
 
-constexpr size_t kMaxSmemBytes = 227 * 1024;
+constexpr size_t kMaxSmemBytes = 227 * 1024 - 64;  // 64 bytes left for static shared (mbarrier)
 constexpr double kTwoPi = 6.28318530717958647692528676655900577;
 
 struct Factorization {
@@ -80,6 +80,7 @@ inline bool plan_line(int N, LinePlan& lp) {
     Factorization f;
     int st_r[4], st_threads = 0;
     const int sid = find_static_shape(N, nseq, st_r, &st_threads);
+    if (sid == -2) continue;  // a tuning variant with the other sequence count was forced
     if (sid >= 0) {
       f.nstages = 0;
       for (int i = 0; i < 4; ++i)

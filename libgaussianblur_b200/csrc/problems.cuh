@@ -46,12 +46,43 @@ struct RowParams {
   float* inter;           // [rows_total][inter_pitch] fp32, element (r, x*Cp + ch)
   long long inter_pitch;  // floats per row
   int nunits;
+  // blocked intermediate (BLOCKED problems): [frame][group g][slot physc(n)][L floats], written so
+  // that the column pass can bulk-copy one whole padded unit; see BlockedDst below
+  int rows_per_frame;          // column-pass line length (rows of one frame)
+  int blk_L;                   // floats per column group = 2 * (column plan's NSEQ)
+  int blk_np;                  // slots per column unit (N_col + padding slots)
+  int blk_padq;                // column plan's padq
+  long long blk_frame_stride;  // floats per frame
 };
 
+// Where one image row lands in the blocked intermediate: slot n = pad + r plus, for rows inside
+// the reflect_101 border, the mirrored slots (the row pass writes the column pass's padding, so
+// the column pass needs no index arithmetic at all; the zero tail is never written).
+struct BlockedDst {
+  float* base;      // inter + frame offset + physc(pad + r) * L
+  long long dl, dr; // float offsets of the left / right mirror slot relative to base, 0 = none
+  long long gstride;  // floats between consecutive groups = np * L
+};
+
+__device__ __forceinline__ BlockedDst make_blocked_dst(const RowParams& P, long long r_global) {
+  BlockedDst d;
+  const long long f = r_global / P.rows_per_frame;
+  const int r = (int)(r_global - f * P.rows_per_frame);
+  const int Tc = P.rows_per_frame, pad = P.pad, L = P.blk_L;
+  const int p1 = phys(pad + r, P.blk_padq);
+  d.base = P.inter + f * P.blk_frame_stride + (long long)p1 * L;
+  d.gstride = (long long)P.blk_np * L;
+  d.dl = (r >= 1 && r <= pad) ? (long long)(phys(pad - r, P.blk_padq) - p1) * L : 0;
+  d.dr = (r >= Tc - 1 - pad && r <= Tc - 2) ? (long long)(phys(pad + 2 * Tc - 2 - r, P.blk_padq) - p1) * L : 0;
+  return d;
+}
+
 // Any C, Cp: real line sigma = r*Cp + ch; a unit takes 2*NSEQ consecutive lines.
-template <int NSEQ>
+// BLOCKED selects the blocked intermediate (scalar scattered stores) instead of row-major.
+template <int NSEQ, bool BLOCKED = false>
 struct RowProblemGeneric {
   static constexpr int L = 2 * NSEQ;
+  static constexpr bool kBulkIn = false;
   struct Loader {
     const uint8_t* p[L];
     int C, pad, T;
@@ -69,16 +100,29 @@ struct RowProblemGeneric {
     }
   };
   struct Storer {
-    float* q[L];  // nullptr: line does not exist (tail unit)
-    int Cp, pad, T;
+    float* q[L];  // nullptr: line does not exist (tail unit); BLOCKED: BlockedDst::base
+    long long dl[L], dr[L], gstride;
+    int ch[L];
+    int Cp, pad, T, lshift;
+    __device__ __forceinline__ void put(int k, int x, float v) const {
+      if (!q[k]) return;
+      if constexpr (!BLOCKED) {
+        q[k][(long long)x * Cp] = v;
+      } else {
+        const int w = x * Cp + ch[k];
+        float* d = q[k] + (long long)(w >> lshift) * gstride + (w & ((1 << lshift) - 1));
+        *d = v;
+        if (dl[k]) d[dl[k]] = v;
+        if (dr[k]) d[dr[k]] = v;
+      }
+    }
     __device__ __forceinline__ void store(int n, const Pt<NSEQ>& v) const {
       const int x = n - pad;
       if (x < 0 || x >= T) return;
-      const long long off = (long long)x * Cp;
 #pragma unroll
       for (int s = 0; s < NSEQ; ++s) {
-        if (q[2 * s]) q[2 * s][off] = v.v[s].x;
-        if (q[2 * s + 1]) q[2 * s + 1][off] = v.v[s].y;
+        put(2 * s, x, v.v[s].x);
+        put(2 * s + 1, x, v.v[s].y);
       }
     }
   };
@@ -87,6 +131,8 @@ struct RowProblemGeneric {
     ld.pad = st.pad = P.pad;
     ld.T = st.T = P.T;
     st.Cp = P.Cp;
+    st.lshift = (P.blk_L == 4) ? 2 : 1;
+    st.gstride = 0;
 #pragma unroll
     for (int k = 0; k < L; ++k) {
       long long sig = (long long)unit * L + k;
@@ -95,13 +141,26 @@ struct RowProblemGeneric {
       const long long r = sig / P.Cp;
       const int ch = (int)(sig - r * P.Cp);
       ld.p[k] = P.in + r * P.in_pitch + ch;
-      st.q[k] = ok ? P.inter + r * P.inter_pitch + ch : nullptr;
+      st.ch[k] = ch;
+      st.dl[k] = st.dr[k] = 0;
+      if constexpr (!BLOCKED) {
+        st.q[k] = ok ? P.inter + r * P.inter_pitch + ch : nullptr;
+      } else {
+        const BlockedDst d = make_blocked_dst(P, r);
+        st.q[k] = ok ? d.base : nullptr;
+        st.dl[k] = d.dl;
+        st.dr[k] = d.dr;
+        st.gstride = d.gstride;
+      }
     }
   }
 };
 
-// C == Cp == 4, two sequences: one uchar4 load feeds (R + iG, B + iA), one float4 store per pixel
+// C == Cp == 4, two sequences: one uchar4 load feeds (R + iG, B + iA), one float4 store per pixel.
+// BLOCKED (needs a column plan with two sequences, L = 4): pixel x is column group x.
+template <bool BLOCKED = false>
 struct RowProblemRGBA {
+  static constexpr bool kBulkIn = false;
   struct Loader {
     const uint32_t* row;
     int pad, T;
@@ -116,19 +175,88 @@ struct RowProblemRGBA {
     }
   };
   struct Storer {
-    float4* row;
+    float* row;  // row-major: start of the row; blocked: BlockedDst::base
+    long long dl, dr, gstride;
     int pad, T;
     __device__ __forceinline__ void store(int n, const Pt<2>& v) const {
       const int x = n - pad;
       if (x < 0 || x >= T) return;
-      row[x] = make_float4(v.v[0].x, v.v[0].y, v.v[1].x, v.v[1].y);
+      const float4 o = make_float4(v.v[0].x, v.v[0].y, v.v[1].x, v.v[1].y);
+      if constexpr (!BLOCKED) {
+        reinterpret_cast<float4*>(row)[x] = o;
+      } else {
+        float* d = row + (long long)x * gstride;
+        *reinterpret_cast<float4*>(d) = o;
+        if (dl) *reinterpret_cast<float4*>(d + dl) = o;
+        if (dr) *reinterpret_cast<float4*>(d + dr) = o;
+      }
     }
   };
   static __device__ __forceinline__ void make(const RowParams& P, int unit, Loader& ld, Storer& st) {
     ld.pad = st.pad = P.pad;
     ld.T = st.T = P.T;
     ld.row = reinterpret_cast<const uint32_t*>(P.in + (long long)unit * P.in_pitch);
-    st.row = reinterpret_cast<float4*>(P.inter + (long long)unit * P.inter_pitch);
+    st.dl = st.dr = st.gstride = 0;
+    if constexpr (!BLOCKED) {
+      st.row = P.inter + (long long)unit * P.inter_pitch;
+    } else {
+      const BlockedDst d = make_blocked_dst(P, unit);
+      st.row = d.base;
+      st.dl = d.dl;
+      st.dr = d.dr;
+      st.gstride = d.gstride;
+    }
+  }
+};
+
+// C == Cp == 4, ONE sequence per unit: unit = (row, channel pair p), (R + iG) for p = 0 and
+// (B + iA) for p = 1. 16-bit loads, float2 stores (row-major: at 16-byte stride; blocked with
+// L = 4: the half of group x that belongs to pair p).
+template <bool BLOCKED = false>
+struct RowProblemRGBA1 {
+  static constexpr bool kBulkIn = false;
+  struct Loader {
+    const uint16_t* row;  // already offset by the pair
+    int pad, T;
+    __device__ __forceinline__ Pt<1> load(int n) const {
+      const int x = reflect101(n, pad, T);
+      const uint32_t w = __ldg(row + 2 * (x < 0 ? 0 : x));
+      Pt<1> r;
+      r.v[0] = (x < 0) ? make_float2(0.f, 0.f) : make_float2(u8_to_f32(w, 0), u8_to_f32(w, 1));
+      return r;
+    }
+  };
+  struct Storer {
+    float* row;
+    long long dl, dr, gstride;
+    int pad, T;
+    __device__ __forceinline__ void store(int n, const Pt<1>& v) const {
+      const int x = n - pad;
+      if (x < 0 || x >= T) return;
+      float* d = row + (long long)x * gstride;
+      *reinterpret_cast<float2*>(d) = v.v[0];
+      if constexpr (BLOCKED) {
+        if (dl) *reinterpret_cast<float2*>(d + dl) = v.v[0];
+        if (dr) *reinterpret_cast<float2*>(d + dr) = v.v[0];
+      }
+    }
+  };
+  static __device__ __forceinline__ void make(const RowParams& P, int unit, Loader& ld, Storer& st) {
+    const int r = unit >> 1, p = unit & 1;
+    ld.pad = st.pad = P.pad;
+    ld.T = st.T = P.T;
+    ld.row = reinterpret_cast<const uint16_t*>(P.in + (long long)r * P.in_pitch) + p;
+    st.dl = st.dr = 0;
+    if constexpr (!BLOCKED) {
+      st.row = P.inter + (long long)r * P.inter_pitch + 2 * p;
+      st.gstride = 4;
+    } else {
+      const BlockedDst d = make_blocked_dst(P, r);
+      st.row = d.base + 2 * p;
+      st.dl = d.dl;
+      st.dr = d.dr;
+      st.gstride = d.gstride;
+    }
   }
 };
 
@@ -147,13 +275,25 @@ struct ColParams {
   long long out_pitch;     // bytes per image row
   long long out_frame_stride;
   int C, Cp;
+  // BULK problems: inter is the blocked layout [frame][group][np slots][L floats]; one unit is one
+  // contiguous run of unit_bytes that is bulk-copied straight into the exchange buffer
+  long long unit_stride;   // floats between consecutive groups = np * L
+  unsigned unit_bytes;     // np * L * 4 (multiple of 16)
 };
 
 // PACKED: Cp == C and every row/pitch is aligned so that the 2*NSEQ bytes of a unit are one
 // aligned 16/32-bit store; otherwise bytes are scattered individually.
-template <int NSEQ, bool PACKED>
+// BULK: the unit is fetched with one cp.async.bulk from the blocked intermediate (padding and
+// mirrored border rows were already written by the row pass), so the Loader is never called.
+template <int NSEQ, bool PACKED, bool BULK = false>
 struct ColProblem {
   static constexpr int L = 2 * NSEQ;
+  static constexpr bool kBulkIn = BULK;
+  static __device__ __forceinline__ const void* bulk_src(const ColParams& P, int unit) {
+    const int f = unit / P.groups_per_frame;
+    const int g = unit - f * P.groups_per_frame;
+    return P.inter + (long long)f * P.frame_stride + (long long)g * P.unit_stride;
+  }
   struct Loader {
     const float* col;  // inter + frame*frame_stride + w0
     long long pitch;

@@ -10,38 +10,66 @@ namespace gblur {
 
 template <int ID>
 struct ShapeOf;
-#define X(ID, NSEQ_, R0, R1, R2, R3, NT_, MINB_)     \
+#define X(ID, NSEQ_, R0, R1, R2, R3, NT_, MAXREG_)     \
   template <>                                        \
   struct ShapeOf<ID> {                               \
     using SS = StaticShape<R0, R1, R2, R3>;          \
-    static constexpr int NSEQ = NSEQ_, NT = NT_, MINB = MINB_; \
+    static constexpr int NSEQ = NSEQ_, NT = NT_, MAXREG = MAXREG_; \
   };
 GBLUR_STATIC_SHAPES(X)
 #undef X
 
 template <int ID>
-cudaError_t launch_row_static(const LinePlan& lp, const RowParams& P, bool rgba, int num_sms, cudaStream_t s) {
+cudaError_t launch_row_static(const LinePlan& lp, const RowParams& P, bool rgba, bool blocked, int num_sms,
+                              cudaStream_t s) {
   using S = ShapeOf<ID>;
+  using SS = typename S::SS;
   if constexpr (S::NSEQ == 2) {
+    if (rgba && blocked)
+      return launch_line<line_kernel_static<2, SS, S::NT, S::MAXREG, RowProblemRGBA<true>, RowParams>>(lp, P, S::NT,
+                                                                                                       num_sms, s);
     if (rgba)
-      return launch_line<line_kernel_static<2, typename S::SS, S::NT, S::MINB, RowProblemRGBA, RowParams>>(lp, P,
-                         S::NT, num_sms, s);
+      return launch_line<line_kernel_static<2, SS, S::NT, S::MAXREG, RowProblemRGBA<false>, RowParams>>(lp, P, S::NT,
+                                                                                                        num_sms, s);
   }
-  return launch_line<line_kernel_static<S::NSEQ, typename S::SS, S::NT, S::MINB, RowProblemGeneric<S::NSEQ>, RowParams>>(lp, P,
-      S::NT, num_sms, s);
+  if constexpr (S::NSEQ == 1) {
+    if (rgba && blocked)
+      return launch_line<line_kernel_static<1, SS, S::NT, S::MAXREG, RowProblemRGBA1<true>, RowParams>>(lp, P, S::NT,
+                                                                                                        num_sms, s);
+    if (rgba)
+      return launch_line<line_kernel_static<1, SS, S::NT, S::MAXREG, RowProblemRGBA1<false>, RowParams>>(lp, P, S::NT,
+                                                                                                         num_sms, s);
+  }
+  if (blocked)
+    return launch_line<line_kernel_static<S::NSEQ, SS, S::NT, S::MAXREG, RowProblemGeneric<S::NSEQ, true>, RowParams>>(
+        lp, P, S::NT, num_sms, s);
+  return launch_line<line_kernel_static<S::NSEQ, SS, S::NT, S::MAXREG, RowProblemGeneric<S::NSEQ, false>, RowParams>>(
+      lp, P, S::NT, num_sms, s);
 }
 
 template <int ID>
-cudaError_t launch_col_static(const LinePlan& lp, const ColParams& P, bool packed, int num_sms, cudaStream_t s) {
+cudaError_t launch_col_static(const LinePlan& lp, const ColParams& P, bool packed, bool blocked, int num_sms,
+                              cudaStream_t s) {
   using S = ShapeOf<ID>;
+  using SS = typename S::SS;
+  constexpr int Q = S::NSEQ;
+  if (blocked) {
+    if (packed)
+      return launch_line<line_kernel_static<Q, SS, S::NT, S::MAXREG, ColProblem<Q, true, true>, ColParams>>(
+          lp, P, S::NT, num_sms, s);
+    return launch_line<line_kernel_static<Q, SS, S::NT, S::MAXREG, ColProblem<Q, false, true>, ColParams>>(
+        lp, P, S::NT, num_sms, s);
+  }
   if (packed)
-    return launch_line<line_kernel_static<S::NSEQ, typename S::SS, S::NT, S::MINB, ColProblem<S::NSEQ, true>, ColParams>>(lp, P,
-        S::NT, num_sms, s);
-  return launch_line<line_kernel_static<S::NSEQ, typename S::SS, S::NT, S::MINB, ColProblem<S::NSEQ, false>, ColParams>>(lp, P,
-      S::NT, num_sms, s);
+    return launch_line<line_kernel_static<Q, SS, S::NT, S::MAXREG, ColProblem<Q, true, false>, ColParams>>(
+        lp, P, S::NT, num_sms, s);
+  return launch_line<line_kernel_static<Q, SS, S::NT, S::MAXREG, ColProblem<Q, false, false>, ColParams>>(
+      lp, P, S::NT, num_sms, s);
 }
 
-template cudaError_t launch_row_static<GBLUR_TU_SHAPE>(const LinePlan&, const RowParams&, bool, int, cudaStream_t);
-template cudaError_t launch_col_static<GBLUR_TU_SHAPE>(const LinePlan&, const ColParams&, bool, int, cudaStream_t);
+template cudaError_t launch_row_static<GBLUR_TU_SHAPE>(const LinePlan&, const RowParams&, bool, bool, int,
+                                                       cudaStream_t);
+template cudaError_t launch_col_static<GBLUR_TU_SHAPE>(const LinePlan&, const ColParams&, bool, bool, int,
+                                                       cudaStream_t);
 
 }  // namespace gblur

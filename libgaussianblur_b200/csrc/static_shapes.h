@@ -1,13 +1,22 @@
 // static_shapes.h — FFT lengths that get a fully compile-time kernel (all radices, strides and
 // index arithmetic constant-folded). Every other valid length runs the runtime-radix kernel.
-// Columns: id, NSEQ, R0, R1, R2, R3 (1 = stage absent), CTA threads, min CTAs per SM.
+// Columns: id, NSEQ, R0, R1, R2, R3 (1 = stage absent), CTA threads, register cap per thread.
 // libgaussianblur_b200/build.py compiles static_impl.cu once per id (GBLUR_TU_SHAPE=id).
+//
+// Register caps follow the per-scheduler register file (16384 registers per SM sub-partition):
+// cap = floor(16384 / ceil(resident_warps / 4) / 32) rounded down to a multiple of 8.
+// Several entries may share one FFT length: the first one listed is the default, the others are
+// tuning variants selectable with the environment variable GBLUR_VARIANT_<N>=<id>.
 #pragma once
 
-#define GBLUR_STATIC_SHAPES(X)                                                  \
-  X(0, 2, 20, 20, 20, 1, 400, 1) /* N = 8000 : 8K RGBA sigma=20 row pass    */ \
-  X(1, 2, 16, 16, 18, 1, 288, 2) /* N = 4608 : 8K RGBA sigma=20 column pass */ \
-  X(2, 2, 16, 16, 8, 1, 256, 2)  /* N = 2048 : 1080p row pass               */ \
-  X(3, 2, 12, 12, 8, 1, 160, 2)  /* N = 1152 : 1080p column pass            */
-
-#define GBLUR_NUM_STATIC_SHAPES 4
+#define GBLUR_STATIC_SHAPES(X)                                                                     \
+  X(0, 2, 20, 20, 20, 1, 400, 128)  /* N = 8000 : 8K RGBA sigma=20 row pass, 1 CTA/SM (13 warps) */ \
+  X(1, 2, 16, 16, 18, 1, 288, 96)   /* N = 4608 : 8K RGBA sigma=20 column pass, 2 CTAs/SM        */ \
+  X(2, 2, 16, 16, 8, 1, 256, 128)   /* N = 2048 : 1080p row pass                                 */ \
+  X(3, 2, 12, 12, 8, 1, 160, 128)   /* N = 1152 : 1080p column pass                              */ \
+  X(4, 1, 20, 20, 20, 1, 400, 72)   /* N = 8000 : one sequence, 2 CTAs/SM (26 warps)             */ \
+  X(5, 1, 20, 20, 20, 1, 200, 80)   /* N = 8000 : one sequence, 2 butterflies/thread, 3 CTAs/SM  */ \
+  X(6, 2, 8, 10, 10, 10, 1000, 64)  /* N = 8000 : four stages, 1 CTA/SM (32 warps)               */ \
+  X(7, 2, 16, 16, 18, 1, 288, 168)  /* N = 4608 : 1 CTA/SM, no register pressure                 */ \
+  X(8, 2, 8, 8, 8, 9, 576, 56)      /* N = 4608 : four stages, 2 CTAs/SM (36 warps)              */ \
+  X(9, 1, 16, 16, 18, 1, 288, 72)   /* N = 4608 : one sequence, 3 CTAs/SM (27 warps)             */
