@@ -5,6 +5,8 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
@@ -117,7 +119,7 @@ BlockedLayout blocked_layout(const gblur_plan* p, int cp) {
   const LinePlan& c = p->col.lp;
   b.enabled = 1;
   b.L = 2 * c.nseq;
-  b.np = (int)(c.smem_bytes / (8 * (size_t)c.nseq));
+  b.np = c.exch_elems;
   b.padq = c.padq;
   b.rows_per_frame = p->full_rows;
   const long long groups = ((long long)p->cols * cp + b.L - 1) / b.L;
@@ -308,16 +310,26 @@ static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_f
   const int cp = processed_channels(p, apply_to_alpha);
   // workspace sized for the widest layout (all channels processed)
   const BlockedLayout widest = blocked_layout(p, p->channels);
-  int rc = ensure_inter(p, (size_t)p->max_frames * (size_t)widest.frame_stride);
+  const size_t rowmajor_floats = (size_t)p->rows * (size_t)default_pitch((long long)p->cols * p->channels);
+  int rc = ensure_inter(p, (size_t)p->max_frames * std::max((size_t)widest.frame_stride, rowmajor_floats));
   if (rc != GBLUR_OK) return rc;
+  // tuning switch: GBLUR_LAYOUT=rowmajor keeps the fp32 intermediate row-major (column pass gathers
+  // 16-byte pieces); default is the blocked layout the column pass bulk-copies
+  static const bool rowmajor = [] {
+    const char* e = getenv("GBLUR_LAYOUT");
+    return e && std::strcmp(e, "rowmajor") == 0;
+  }();
   const BlockedLayout blk = blocked_layout(p, cp);
-  if (p->inter_cp != 0 && p->inter_cp != cp) {
+  const BlockedLayout* bp = rowmajor ? nullptr : &blk;
+  const long long pitch = default_pitch((long long)p->cols * cp);
+  const int layout_tag = rowmajor ? -cp : cp;
+  if (p->inter_cp != 0 && p->inter_cp != layout_tag) {
     // the zero tail / padding slots of the new layout may hold samples of the old one
     CU(cudaMemsetAsync(p->d_inter, 0, p->inter_floats * sizeof(float), s));
   }
-  p->inter_cp = cp;
+  p->inter_cp = layout_tag;
   if (stages & 1) {
-    rc = run_rowpass(p, d_in, p->d_inter, 0, n_frames, apply_to_alpha, s, &blk);
+    rc = run_rowpass(p, d_in, p->d_inter, pitch, n_frames, apply_to_alpha, s, bp);
     if (rc != GBLUR_OK) return rc;
   }
   p->last_cp = cp;
@@ -325,7 +337,7 @@ static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_f
   if (!(stages & 2)) return GBLUR_OK;
   if (d_in != d_out && cp < p->channels)
     CU(launch_copy_channel(d_in, d_out, (long long)p->rows * p->cols * n_frames, p->channels, 3, s));
-  return run_colpass(p, p->d_inter, 0, d_out, (long long)p->cols * p->channels, n_frames, apply_to_alpha, s, &blk);
+  return run_colpass(p, p->d_inter, pitch, d_out, (long long)p->cols * p->channels, n_frames, apply_to_alpha, s, bp);
 }
 
 int gblur_run_batch_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
@@ -394,7 +406,14 @@ int gblur_dump_intermediate(gblur_plan* p, float* host_out, int apply_to_alpha) 
   if (!p->d_inter || p->inter_cp == 0) return fail(GBLUR_E_INVALID, "no run has happened on this plan");
   DeviceGuard guard(p->device);
   const int cp = processed_channels(p, apply_to_alpha);
-  if (cp != p->inter_cp) return fail(GBLUR_E_INVALID, "last run used a different apply_to_alpha");
+  if (cp != p->inter_cp && -cp != p->inter_cp) return fail(GBLUR_E_INVALID, "last run used a different apply_to_alpha");
+  if (p->inter_cp < 0) {  // row-major layout
+    const long long w = (long long)p->cols * cp, pitch = default_pitch(w);
+    CU(cudaDeviceSynchronize());
+    CU(cudaMemcpy2D(host_out, (size_t)w * sizeof(float), p->d_inter, (size_t)pitch * sizeof(float),
+                    (size_t)w * sizeof(float), (size_t)p->rows, cudaMemcpyDeviceToHost));
+    return GBLUR_OK;
+  }
   const BlockedLayout b = blocked_layout(p, cp);
   std::vector<float> blk((size_t)b.frame_stride);
   CU(cudaDeviceSynchronize());

@@ -68,15 +68,49 @@ struct LineShape {
   int radix[kMaxStages];
   int M[kMaxStages];  // M[s] = N / (radix[0] * ... * radix[s]); M[nstages-1] == 1
   int padq;           // radix[nstages-1] if that radix is even, else 0
-  const float2* tw[kMaxStages];  // tw[s][(j-1)*M[s] + m] = exp(-2 pi i m j / (radix[s]*M[s])), s < nstages-1
+  const float2* tw[kMaxStages];  // factored stage tables (TwSplit), s < nstages-1; contiguous in stage order
   const float* kperm;            // spectrum gains * 1/N in digit-reversed position order
+};
+
+// Stage twiddles are stored factored: for radix R = A*B only the B-1 "fine" powers w^1..w^(B-1)
+// and the A-1 "coarse" powers w^B, w^2B, .. of w = exp(-2 pi i m / (R*M)) are tabulated
+// (A+B-2 entries per butterfly column m instead of R-1); the rest are one complex product each.
+// The tables are then small enough to sit in shared memory next to the exchange buffer, which
+// keeps them out of the L1 that the streaming loads/stores thrash.
+//   layout: tw[e*M + m], e < B-1 -> j = e+1 ; e >= B-1 -> j = (e-(B-1)+1)*B
+template <int R>
+struct TwSplit {
+  static constexpr int B = (R % 4 == 0) ? 4 : (R % 5 == 0) ? 5 : (R % 3 == 0) ? 3 : (R % 2 == 0) ? 2 : R;
+  static constexpr int A = R / B;
+  static constexpr int NBASE = (B - 1) + (A - 1);
+};
+
+template <int R, bool TSM>
+struct StageTwiddles {
+  using S = TwSplit<R>;
+  float2 fine[S::B > 1 ? S::B - 1 : 1];
+  float2 coarse[S::A > 1 ? S::A - 1 : 1];
+  __device__ __forceinline__ void load(const float2* __restrict__ tw, int M, int m) {
+#pragma unroll
+    for (int b = 1; b < S::B; ++b) fine[b - 1] = TSM ? tw[(b - 1) * M + m] : __ldg(tw + (b - 1) * M + m);
+#pragma unroll
+    for (int a = 1; a < S::A; ++a)
+      coarse[a - 1] = TSM ? tw[(S::B - 2 + a) * M + m] : __ldg(tw + (S::B - 2 + a) * M + m);
+  }
+  // w^j, j compile-time after unrolling
+  __device__ __forceinline__ float2 get(int j) const {
+    const int a = j / S::B, b = j % S::B;
+    if (a == 0) return fine[b - 1];
+    if (b == 0) return coarse[a - 1];
+    return cmul(coarse[a - 1], fine[b - 1]);
+  }
 };
 
 // --------------------------------------------------------------------------------------------
 // stages
 // --------------------------------------------------------------------------------------------
 // forward stage s < last: (loader | smem) -> radix-R DFT -> twiddle -> smem
-template <int R, int NSEQ, bool FIRST, class Loader>
+template <int R, int NSEQ, bool FIRST, bool TSM, class Loader>
 __device__ __forceinline__ void fwd_stage(const Loader& ld, typename SmemElem<NSEQ>::type* sm,
                                           const float2* __restrict__ tw, int N, int M, int padq,
                                           int tid, int nthreads) {
@@ -98,6 +132,8 @@ __device__ __forceinline__ void fwd_stage(const Loader& ld, typename SmemElem<NS
 #pragma unroll
       for (int q = 0; q < NSEQ; ++q) c[q][j] = p.v[q];
     }
+    StageTwiddles<R, TSM> tws;
+    tws.load(tw, M, m);
 #pragma unroll
     for (int q = 0; q < NSEQ; ++q) dft<R, false>(c[q]);
 #pragma unroll
@@ -107,7 +143,7 @@ __device__ __forceinline__ void fwd_stage(const Loader& ld, typename SmemElem<NS
 #pragma unroll
         for (int q = 0; q < NSEQ; ++q) p.v[q] = c[q][0];
       } else {
-        const float2 w = __ldg(tw + (j - 1) * M + m);
+        const float2 w = tws.get(j);
 #pragma unroll
         for (int q = 0; q < NSEQ; ++q) p.v[q] = cmul(c[q][j], w);
       }
@@ -117,7 +153,7 @@ __device__ __forceinline__ void fwd_stage(const Loader& ld, typename SmemElem<NS
 }
 
 // last forward stage + spectrum multiply + first inverse stage, all on one register set
-template <int R, int NSEQ>
+template <int R, int NSEQ, bool TSM>
 __device__ __forceinline__ void fused_last_stage(typename SmemElem<NSEQ>::type* sm,
                                                  const float* __restrict__ kperm, int N, int padq,
                                                  int tid, int nthreads) {
@@ -137,7 +173,7 @@ __device__ __forceinline__ void fused_last_stage(typename SmemElem<NSEQ>::type* 
     const float* kp = kperm + u * R;
 #pragma unroll
     for (int j = 0; j < R; ++j) {
-      const float g = __ldg(kp + j);
+      const float g = TSM ? kp[j] : __ldg(kp + j);
 #pragma unroll
       for (int q = 0; q < NSEQ; ++q) {
         c[q][j].x *= g;
@@ -157,7 +193,7 @@ __device__ __forceinline__ void fused_last_stage(typename SmemElem<NSEQ>::type* 
 }
 
 // inverse stage s < last: smem -> conj twiddle -> inverse radix-R DFT -> (smem | storer)
-template <int R, int NSEQ, bool FINAL, class Storer>
+template <int R, int NSEQ, bool FINAL, bool TSM, class Storer>
 __device__ __forceinline__ void inv_stage(const Storer& st, typename SmemElem<NSEQ>::type* sm,
                                           const float2* __restrict__ tw, int N, int M, int padq,
                                           int tid, int nthreads) {
@@ -169,6 +205,8 @@ __device__ __forceinline__ void inv_stage(const Storer& st, typename SmemElem<NS
     const int base = b * (R * M) + m;
     const int pb = phys(base, padq);
     float2 c[NSEQ][R];
+    StageTwiddles<R, TSM> tws;
+    tws.load(tw, M, m);
 #pragma unroll
     for (int j = 0; j < R; ++j) {
       Pt<NSEQ> p = SE::ld(sm + pb + j * pstep);
@@ -176,7 +214,7 @@ __device__ __forceinline__ void inv_stage(const Storer& st, typename SmemElem<NS
 #pragma unroll
         for (int q = 0; q < NSEQ; ++q) c[q][0] = p.v[q];
       } else {
-        const float2 w = __ldg(tw + (j - 1) * M + m);
+        const float2 w = tws.get(j);
 #pragma unroll
         for (int q = 0; q < NSEQ; ++q) c[q][j] = cmulc(p.v[q], w);
       }
@@ -214,9 +252,9 @@ __device__ __forceinline__ void run_line_generic(const LineShape& sh, const Load
 #define X(R_)                                                                                        \
   case R_:                                                                                           \
     if (s == 0 && !SMEM_IN)                                                                          \
-      fwd_stage<R_, NSEQ, true>(ld, sm, sh.tw[s], sh.N, sh.M[s], sh.padq, tid, nthreads);            \
+      fwd_stage<R_, NSEQ, true, false>(ld, sm, sh.tw[s], sh.N, sh.M[s], sh.padq, tid, nthreads);            \
     else                                                                                             \
-      fwd_stage<R_, NSEQ, false>(ld, sm, sh.tw[s], sh.N, sh.M[s], sh.padq, tid, nthreads);           \
+      fwd_stage<R_, NSEQ, false, false>(ld, sm, sh.tw[s], sh.N, sh.M[s], sh.padq, tid, nthreads);           \
     break;
       GBLUR_FOR_EACH_GENERIC_RADIX(X)
 #undef X
@@ -226,7 +264,7 @@ __device__ __forceinline__ void run_line_generic(const LineShape& sh, const Load
   switch (sh.radix[S - 1]) {
 #define X(R_)                                                             \
   case R_:                                                                \
-    fused_last_stage<R_, NSEQ>(sm, sh.kperm, sh.N, sh.padq, tid, nthreads); \
+    fused_last_stage<R_, NSEQ, false>(sm, sh.kperm, sh.N, sh.padq, tid, nthreads); \
     break;
     GBLUR_FOR_EACH_GENERIC_RADIX(X)
 #undef X
@@ -237,9 +275,9 @@ __device__ __forceinline__ void run_line_generic(const LineShape& sh, const Load
 #define X(R_)                                                                                        \
   case R_:                                                                                           \
     if (s == 0)                                                                                      \
-      inv_stage<R_, NSEQ, true>(st, sm, sh.tw[s], sh.N, sh.M[s], sh.padq, tid, nthreads);            \
+      inv_stage<R_, NSEQ, true, false>(st, sm, sh.tw[s], sh.N, sh.M[s], sh.padq, tid, nthreads);            \
     else                                                                                             \
-      inv_stage<R_, NSEQ, false>(st, sm, sh.tw[s], sh.N, sh.M[s], sh.padq, tid, nthreads);           \
+      inv_stage<R_, NSEQ, false, false>(st, sm, sh.tw[s], sh.N, sh.M[s], sh.padq, tid, nthreads);           \
     break;
       GBLUR_FOR_EACH_GENERIC_RADIX(X)
 #undef X
@@ -256,33 +294,44 @@ struct StaticShape {
   static constexpr int RL = (S == 4) ? R3 : (S == 3) ? R2 : R1;
   static constexpr int PADQ = (RL % 2 == 0) ? RL : 0;
   static constexpr int M0 = N / R0, M1 = M0 / R1, M2 = M1 / R2;
+  static constexpr int EXCH = N + (PADQ ? N / PADQ : 0);  // exchange-buffer slots
+  // factored twiddle tables of the non-last stages (float2 entries), kept in shared memory
+  static constexpr int TW0 = TwSplit<R0>::NBASE * M0;
+  static constexpr int TW1 = (S >= 3) ? TwSplit<R1>::NBASE * M1 : 0;
+  static constexpr int TW2 = (S >= 4) ? TwSplit<R2>::NBASE * M2 : 0;
+  static constexpr int TWTOT = TW0 + TW1 + TW2;
 };
 
+// twsm / kpsm: the stage tables and the permuted spectrum, already copied to shared memory
 template <int NSEQ, class SS, bool SMEM_IN, class Loader, class Storer>
-__device__ __forceinline__ void run_line_static(const LineShape& sh, const Loader& ld, const Storer& st,
-                                                typename SmemElem<NSEQ>::type* sm, int tid, int nthreads) {
+__device__ __forceinline__ void run_line_static(const float2* twsm, const float* kpsm, const Loader& ld,
+                                                const Storer& st, typename SmemElem<NSEQ>::type* sm, int tid,
+                                                int nthreads) {
   constexpr int N = SS::N, PQ = SS::PADQ;
-  fwd_stage<N / SS::M0, NSEQ, !SMEM_IN>(ld, sm, sh.tw[0], N, SS::M0, PQ, tid, nthreads);
+  const float2* tw0 = twsm;
+  const float2* tw1 = twsm + SS::TW0;
+  const float2* tw2 = twsm + SS::TW0 + SS::TW1;
+  fwd_stage<N / SS::M0, NSEQ, !SMEM_IN, true>(ld, sm, tw0, N, SS::M0, PQ, tid, nthreads);
   __syncthreads();
   if constexpr (SS::S >= 3) {
-    fwd_stage<SS::M0 / SS::M1, NSEQ, false>(ld, sm, sh.tw[1], N, SS::M1, PQ, tid, nthreads);
+    fwd_stage<SS::M0 / SS::M1, NSEQ, false, true>(ld, sm, tw1, N, SS::M1, PQ, tid, nthreads);
     __syncthreads();
   }
   if constexpr (SS::S >= 4) {
-    fwd_stage<SS::M1 / SS::M2, NSEQ, false>(ld, sm, sh.tw[2], N, SS::M2, PQ, tid, nthreads);
+    fwd_stage<SS::M1 / SS::M2, NSEQ, false, true>(ld, sm, tw2, N, SS::M2, PQ, tid, nthreads);
     __syncthreads();
   }
-  fused_last_stage<SS::RL, NSEQ>(sm, sh.kperm, N, PQ, tid, nthreads);
+  fused_last_stage<SS::RL, NSEQ, true>(sm, kpsm, N, PQ, tid, nthreads);
   __syncthreads();
   if constexpr (SS::S >= 4) {
-    inv_stage<SS::M1 / SS::M2, NSEQ, false>(st, sm, sh.tw[2], N, SS::M2, PQ, tid, nthreads);
+    inv_stage<SS::M1 / SS::M2, NSEQ, false, true>(st, sm, tw2, N, SS::M2, PQ, tid, nthreads);
     __syncthreads();
   }
   if constexpr (SS::S >= 3) {
-    inv_stage<SS::M0 / SS::M1, NSEQ, false>(st, sm, sh.tw[1], N, SS::M1, PQ, tid, nthreads);
+    inv_stage<SS::M0 / SS::M1, NSEQ, false, true>(st, sm, tw1, N, SS::M1, PQ, tid, nthreads);
     __syncthreads();
   }
-  inv_stage<N / SS::M0, NSEQ, true>(st, sm, sh.tw[0], N, SS::M0, PQ, tid, nthreads);
+  inv_stage<N / SS::M0, NSEQ, true, true>(st, sm, tw0, N, SS::M0, PQ, tid, nthreads);
   __syncthreads();
 }
 

@@ -21,7 +21,8 @@ struct LinePlan {
   int nseq = 2;          // complex sequences per line unit (1 or 2)
   int nthreads = 0;      // CTA size for the runtime-radix kernel
   int static_id = -1;    // index into the compile-time shape table, -1 = runtime-radix kernel
-  size_t smem_bytes = 0; // dynamic shared memory per CTA
+  size_t smem_bytes = 0; // dynamic shared memory per CTA (exchange buffer + in-smem tables)
+  int exch_elems = 0;    // exchange-buffer slots (N + bank-padding slots)
 };
 
 // Blocked intermediate [frame][group][np slots][L floats] (see problems.cuh): written by the row

@@ -47,24 +47,31 @@ __global__ void __launch_bounds__(512, 1)
 }
 
 // MAXREG is given to ptxas directly: with __launch_bounds__ it rounds the CTA size up (400 -> 512
-// threads) and caps at 128 registers, which spills the radix-20 butterflies.
+// threads) and caps at 128 registers with a worse allocation.
+// Shared memory: [exchange buffer][factored twiddle tables][permuted spectrum]; the tables are
+// copied once per (persistent) CTA and then read with LDS — they never compete for L1.
 template <int NSEQ, class SS, int NT, int MAXREG, class Problem, class Params>
 __global__ void __maxnreg__(MAXREG)
     line_kernel_static(const __grid_constant__ LineShape sh, const __grid_constant__ Params P) {
   extern __shared__ float4 smem_raw[];
-  auto* sm = reinterpret_cast<typename SmemElem<NSEQ>::type*>(smem_raw);
+  using Elem = typename SmemElem<NSEQ>::type;
+  auto* sm = reinterpret_cast<Elem*>(smem_raw);
+  float2* twsm = reinterpret_cast<float2*>(sm + SS::EXCH);
+  float* kpsm = reinterpret_cast<float*>(twsm + SS::TWTOT);
+  for (int i = threadIdx.x; i < SS::TWTOT; i += NT) twsm[i] = __ldg(sh.tw[0] + i);
+  for (int i = threadIdx.x; i < SS::N; i += NT) kpsm[i] = __ldg(sh.kperm + i);
   __shared__ uint64_t bar;
   uint32_t parity = 0;
   if constexpr (Problem::kBulkIn) {
     if (threadIdx.x == 0) mbar_init(&bar, 1);
-    __syncthreads();
   }
+  __syncthreads();
   for (int unit = blockIdx.x; unit < P.nunits; unit += gridDim.x) {
     typename Problem::Loader ld;
     typename Problem::Storer st;
     Problem::make(P, unit, ld, st);
     if constexpr (Problem::kBulkIn) bulk_stage_unit<Problem>(P, unit, sm, &bar, parity);
-    run_line_static<NSEQ, SS, Problem::kBulkIn>(sh, ld, st, sm, (int)threadIdx.x, NT);
+    run_line_static<NSEQ, SS, Problem::kBulkIn>(twsm, kpsm, ld, st, sm, (int)threadIdx.x, NT);
   }
 }
 

@@ -65,10 +65,20 @@ inline bool factorize_generic(int N, Factorization& f) {
   return true;
 }
 
-inline size_t smem_bytes_for(int N, int rlast, int nseq) {
+inline int exch_elems_for(int N, int rlast) {
   const int padq = (rlast % 2 == 0) ? rlast : 0;
-  const size_t elems = (size_t)N + (padq ? (size_t)N / padq : 0);
-  return elems * 8 * (size_t)nseq;
+  return N + (padq ? N / padq : 0);
+}
+
+// factored twiddle table of a radix-R stage: (B-1) fine + (A-1) coarse powers (fftconv.cuh TwSplit)
+inline void tw_split(int R, int& A, int& B) {
+  B = (R % 4 == 0) ? 4 : (R % 5 == 0) ? 5 : (R % 3 == 0) ? 3 : (R % 2 == 0) ? 2 : R;
+  A = R / B;
+}
+inline int tw_nbase(int R) {
+  int A, B;
+  tw_split(R, A, B);
+  return (B - 1) + (A - 1);
 }
 
 // Fill everything of a LinePlan that does not live on the device. Returns false when the length
@@ -89,8 +99,18 @@ inline bool plan_line(int N, LinePlan& lp) {
       return false;
     }
     const int rlast = f.radix[f.nstages - 1];
-    const size_t smem = smem_bytes_for(N, rlast, nseq);
+    const int exch = exch_elems_for(N, rlast);
+    size_t smem = (size_t)exch * 8 * (size_t)nseq;
+    if (sid >= 0) {  // compile-time kernels keep the stage tables and the spectrum in shared memory
+      int m = N;
+      for (int s = 0; s < f.nstages - 1; ++s) {
+        m /= f.radix[s];
+        smem += (size_t)tw_nbase(f.radix[s]) * (size_t)m * 8;
+      }
+      smem += (size_t)N * 4;
+    }
     if (smem > kMaxSmemBytes) continue;
+    lp.exch_elems = exch;
     lp.nseq = nseq;
     lp.nstages = f.nstages;
     int m = N, max_nb = 1;
@@ -109,20 +129,25 @@ inline bool plan_line(int N, LinePlan& lp) {
   return false;
 }
 
-// tw[s][(j-1)*M + m] = exp(-2 pi i m j / (R*M)) as (cos, -sin) pairs, concatenated over s < S-1.
+// Factored stage tables, concatenated over s < S-1: tw[s][e*M + m] = exp(-2 pi i m j_e / (R*M))
+// with j_e = e+1 for e < B-1 (fine powers) and j_e = (e-(B-1)+1)*B after that (coarse powers).
 inline void build_twiddles(const LinePlan& lp, std::vector<float>& flat, size_t offsets[kHostMaxStages]) {
   flat.clear();
   for (int s = 0; s < lp.nstages - 1; ++s) {
     const int R = lp.radix[s], M = lp.M[s];
-    const long long B = (long long)R * M;
+    const long long BM = (long long)R * M;
+    int A, B;
+    tw_split(R, A, B);
     offsets[s] = flat.size() / 2;
-    for (int j = 1; j < R; ++j)
+    for (int e = 0; e < (B - 1) + (A - 1); ++e) {
+      const int j = e < B - 1 ? e + 1 : (e - (B - 1) + 1) * B;
       for (int m = 0; m < M; ++m) {
-        const long long e = ((long long)m * j) % B;
-        const double a = kTwoPi * (double)e / (double)B;
+        const long long k = ((long long)m * j) % BM;
+        const double a = kTwoPi * (double)k / (double)BM;
         flat.push_back((float)std::cos(a));
         flat.push_back((float)(-std::sin(a)));
       }
+    }
   }
 }
 
