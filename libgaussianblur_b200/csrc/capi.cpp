@@ -113,7 +113,7 @@ int processed_channels(const gblur_plan* p, int apply_to_alpha) {
 
 long long default_pitch(long long w) { return (w + 3) / 4 * 4; }
 
-// Blocked intermediate of the fused run: one contiguous unit of np slots x L floats per column group.
+// Panel intermediate of the fused run: [panel of 32 float columns][np slots][32 floats].
 BlockedLayout blocked_layout(const gblur_plan* p, int cp) {
   BlockedLayout b;
   const LinePlan& c = p->col.lp;
@@ -122,8 +122,8 @@ BlockedLayout blocked_layout(const gblur_plan* p, int cp) {
   b.np = c.exch_elems;
   b.padq = c.padq;
   b.rows_per_frame = p->full_rows;
-  const long long groups = ((long long)p->cols * cp + b.L - 1) / b.L;
-  b.frame_stride = groups * b.np * b.L;
+  const long long panels = ((long long)p->cols * cp + 31) / 32;
+  b.frame_stride = panels * b.np * 32;
   return b;
 }
 
@@ -423,7 +423,7 @@ int gblur_dump_intermediate(gblur_plan* p, float* host_out, int apply_to_alpha) 
     const int n = p->sz.pad + r;
     const long long slot = b.padq ? n + n / b.padq : n;
     for (long long x = 0; x < w; ++x)
-      host_out[(size_t)r * w + x] = blk[(size_t)((x / b.L) * b.np + slot) * b.L + (size_t)(x % b.L)];
+      host_out[(size_t)r * w + x] = blk[(size_t)((x / 32) * b.np + slot) * 32 + (size_t)(x % 32)];
   }
   return GBLUR_OK;
 }

@@ -219,6 +219,12 @@ __device__ __forceinline__ void inv_stage(const Storer& st, typename SmemElem<NS
         for (int q = 0; q < NSEQ; ++q) c[q][j] = cmulc(p.v[q], w);
       }
     }
+    if constexpr (FINAL && Storer::kPrefetch) {
+      // the slots this thread just read are dead for the current unit: refill them, asynchronously,
+      // with the next unit's samples while the last butterflies and the global stores run
+#pragma unroll
+      for (int j = 0; j < R; ++j) st.prefetch(sm + pb + j * pstep, pb + j * pstep);
+    }
 #pragma unroll
     for (int q = 0; q < NSEQ; ++q) dft<R, true>(c[q]);
 #pragma unroll

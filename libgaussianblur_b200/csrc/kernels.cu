@@ -76,7 +76,7 @@ cudaError_t launch_rowpass(const LinePlan& lp, const RowLaunch& a, int num_sms, 
   // uchar4/float4 (two sequences) or u16/float2 (one sequence, static shapes only) fast path
   const bool rgba = (lp.nseq == 2 || lp.static_id >= 0) && a.C == 4 && a.Cp == 4 && (a.in_pitch % 4) == 0 &&
                     (reinterpret_cast<uintptr_t>(a.in) % 4) == 0 && (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0 &&
-                    (blocked ? a.blk.L == 4 : (a.inter_pitch % 4) == 0);
+                    (blocked || (a.inter_pitch % 4) == 0);
   switch (lp.static_id) {
 #define X(ID, NSEQ, R0, R1, R2, R3, NT, MINB) \
   case ID:                                    \
@@ -105,8 +105,8 @@ cudaError_t launch_colpass(const LinePlan& lp, const ColLaunch& a, int num_sms, 
   P.C = a.C;
   P.Cp = a.Cp;
   const bool blocked = a.blk.enabled != 0;
-  P.unit_stride = (long long)a.blk.np * a.blk.L;
-  P.unit_bytes = (unsigned)(P.unit_stride * 4);
+  P.panel_stride = (long long)a.blk.np * 32;
+  P.np = a.blk.np;
   if (blocked) P.frame_stride = a.blk.frame_stride;
   const bool packed = a.C == a.Cp && (a.W % L) == 0 && (a.out_pitch % L) == 0 && (a.out_frame_stride % L) == 0 &&
                       (reinterpret_cast<uintptr_t>(a.out) % L) == 0;

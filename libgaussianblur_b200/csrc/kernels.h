@@ -25,15 +25,16 @@ struct LinePlan {
   int exch_elems = 0;    // exchange-buffer slots (N + bank-padding slots)
 };
 
-// Blocked intermediate [frame][group][np slots][L floats] (see problems.cuh): written by the row
-// pass, bulk-copied unit by unit by the column pass. enabled == 0: row-major [rows][pitch].
+// Panel intermediate [frame][panel = w/32][np slots][32 floats] (see problems.cuh): the row pass
+// writes whole 128-byte lines, the column pass gathers its L floats per slot with cp.async.
+// enabled == 0: row-major [rows][pitch].
 struct BlockedLayout {
   int enabled = 0;
   int L = 4;                   // floats per column group = 2 * column nseq
   int np = 0;                  // slots per unit (column FFT length + bank padding slots)
   int padq = 0;                // column plan's padq
   int rows_per_frame = 0;
-  long long frame_stride = 0;  // floats per frame = groups * np * L
+  long long frame_stride = 0;  // floats per frame = panels * np * 32
 };
 
 struct RowLaunch {

@@ -12,18 +12,22 @@ namespace gblur {
 
 void count_launch();  // kernels.cu
 
-// Stage one unit into shared memory with a single bulk copy (BULK problems). The exchange buffer
-// was last touched through the generic proxy, hence the proxy fence before the async write.
-template <class Problem, class Params>
-__device__ __forceinline__ void bulk_stage_unit(const Params& P, int unit, void* sm, uint64_t* bar,
-                                                uint32_t& parity) {
-  if (threadIdx.x == 0) {
-    fence_proxy_async();
-    mbar_expect_tx(bar, P.unit_bytes);
-    bulk_g2s(sm, Problem::bulk_src(P, unit), P.unit_bytes, bar);
-  }
-  mbar_wait(bar, parity);
-  parity ^= 1u;
+// Stage one unit into shared memory (BULK problems): np pieces of one exchange-buffer element each,
+// 128 bytes apart in the panel intermediate, gathered with cp.async (no registers, all in flight
+// at once). Every thread waits for its own copies; the caller's barrier publishes them.
+template <int NSEQ, class Problem, class Params>
+__device__ __forceinline__ void gather_stage_unit(const Params& P, int unit, typename SmemElem<NSEQ>::type* sm,
+                                                  int tid, int nthreads) {
+  const float* src = Problem::bulk_src(P, unit);
+  for (int s = tid; s < P.np; s += nthreads) cp_async<8 * NSEQ>(sm + s, src + (long long)s * kPanelFloats);
+  cp_async_commit();
+}
+// The copies of this thread (issued by gather_stage_unit or by the previous unit's last stage) have
+// landed; the barrier makes everybody's visible.
+__device__ __forceinline__ void gather_wait() {
+  cp_async_commit();
+  cp_async_wait<0>();
+  __syncthreads();
 }
 
 template <int NSEQ, class Problem, class Params>
@@ -31,17 +35,15 @@ __global__ void __launch_bounds__(512, 1)
     line_kernel_generic(const __grid_constant__ LineShape sh, const __grid_constant__ Params P) {
   extern __shared__ float4 smem_raw[];
   auto* sm = reinterpret_cast<typename SmemElem<NSEQ>::type*>(smem_raw);
-  __shared__ uint64_t bar;
-  uint32_t parity = 0;
   if constexpr (Problem::kBulkIn) {
-    if (threadIdx.x == 0) mbar_init(&bar, 1);
-    __syncthreads();
+    if ((int)blockIdx.x < P.nunits)
+      gather_stage_unit<NSEQ, Problem>(P, (int)blockIdx.x, sm, (int)threadIdx.x, (int)blockDim.x);
   }
   for (int unit = blockIdx.x; unit < P.nunits; unit += gridDim.x) {
     typename Problem::Loader ld;
     typename Problem::Storer st;
     Problem::make(P, unit, ld, st);
-    if constexpr (Problem::kBulkIn) bulk_stage_unit<Problem>(P, unit, sm, &bar, parity);
+    if constexpr (Problem::kBulkIn) gather_wait();
     run_line_generic<NSEQ, Problem::kBulkIn>(sh, ld, st, sm, (int)threadIdx.x, (int)blockDim.x);
   }
 }
@@ -60,17 +62,15 @@ __global__ void __maxnreg__(MAXREG)
   float* kpsm = reinterpret_cast<float*>(twsm + SS::TWTOT);
   for (int i = threadIdx.x; i < SS::TWTOT; i += NT) twsm[i] = __ldg(sh.tw[0] + i);
   for (int i = threadIdx.x; i < SS::N; i += NT) kpsm[i] = __ldg(sh.kperm + i);
-  __shared__ uint64_t bar;
-  uint32_t parity = 0;
   if constexpr (Problem::kBulkIn) {
-    if (threadIdx.x == 0) mbar_init(&bar, 1);
+    if ((int)blockIdx.x < P.nunits) gather_stage_unit<NSEQ, Problem>(P, (int)blockIdx.x, sm, (int)threadIdx.x, NT);
   }
   __syncthreads();
   for (int unit = blockIdx.x; unit < P.nunits; unit += gridDim.x) {
     typename Problem::Loader ld;
     typename Problem::Storer st;
     Problem::make(P, unit, ld, st);
-    if constexpr (Problem::kBulkIn) bulk_stage_unit<Problem>(P, unit, sm, &bar, parity);
+    if constexpr (Problem::kBulkIn) gather_wait();
     run_line_static<NSEQ, SS, Problem::kBulkIn>(twsm, kpsm, ld, st, sm, (int)threadIdx.x, NT);
   }
 }

@@ -11,6 +11,7 @@
 #pragma once
 #include <cstdint>
 
+#include "async_copy.cuh"
 #include "fftconv.cuh"
 
 namespace gblur {
@@ -46,29 +47,32 @@ struct RowParams {
   float* inter;           // [rows_total][inter_pitch] fp32, element (r, x*Cp + ch)
   long long inter_pitch;  // floats per row
   int nunits;
-  // blocked intermediate (BLOCKED problems): [frame][group g][slot physc(n)][L floats], written so
-  // that the column pass can bulk-copy one whole padded unit; see BlockedDst below
+  // panel intermediate (BLOCKED problems): [frame][panel = w/32][slot physc(n)][32 floats] with
+  // w = x*Cp + ch the float column: every row writes whole 128-byte lines, and a column unit
+  // (L adjacent float columns) finds its padded line at a fixed 128-byte stride; see BlockedDst
   int rows_per_frame;          // column-pass line length (rows of one frame)
   int blk_L;                   // floats per column group = 2 * (column plan's NSEQ)
-  int blk_np;                  // slots per column unit (N_col + padding slots)
+  int blk_np;                  // slots per panel (N_col + padding slots)
   int blk_padq;                // column plan's padq
-  long long blk_frame_stride;  // floats per frame
+  long long blk_frame_stride;  // floats per frame = panels * np * 32
 };
 
 // Where one image row lands in the blocked intermediate: slot n = pad + r plus, for rows inside
 // the reflect_101 border, the mirrored slots (the row pass writes the column pass's padding, so
 // the column pass needs no index arithmetic at all; the zero tail is never written).
+constexpr int kPanelFloats = 32;  // one 128-byte line per (panel, slot)
+
 struct BlockedDst {
-  float* base;      // inter + frame offset + physc(pad + r) * L
+  float* base;      // inter + frame offset + physc(pad + r) * 32
   long long dl, dr; // float offsets of the left / right mirror slot relative to base, 0 = none
-  long long gstride;  // floats between consecutive groups = np * L
+  long long gstride;  // floats between consecutive panels = np * 32
 };
 
 __device__ __forceinline__ BlockedDst make_blocked_dst(const RowParams& P, long long r_global) {
   BlockedDst d;
   const long long f = r_global / P.rows_per_frame;
   const int r = (int)(r_global - f * P.rows_per_frame);
-  const int Tc = P.rows_per_frame, pad = P.pad, L = P.blk_L;
+  const int Tc = P.rows_per_frame, pad = P.pad, L = kPanelFloats;
   const int p1 = phys(pad + r, P.blk_padq);
   d.base = P.inter + f * P.blk_frame_stride + (long long)p1 * L;
   d.gstride = (long long)P.blk_np * L;
@@ -100,17 +104,18 @@ struct RowProblemGeneric {
     }
   };
   struct Storer {
+    static constexpr bool kPrefetch = false;
     float* q[L];  // nullptr: line does not exist (tail unit); BLOCKED: BlockedDst::base
     long long dl[L], dr[L], gstride;
     int ch[L];
-    int Cp, pad, T, lshift;
+    int Cp, pad, T;
     __device__ __forceinline__ void put(int k, int x, float v) const {
       if (!q[k]) return;
       if constexpr (!BLOCKED) {
         q[k][(long long)x * Cp] = v;
       } else {
         const int w = x * Cp + ch[k];
-        float* d = q[k] + (long long)(w >> lshift) * gstride + (w & ((1 << lshift) - 1));
+        float* d = q[k] + (long long)(w >> 5) * gstride + (w & 31);
         *d = v;
         if (dl[k]) d[dl[k]] = v;
         if (dr[k]) d[dr[k]] = v;
@@ -131,7 +136,6 @@ struct RowProblemGeneric {
     ld.pad = st.pad = P.pad;
     ld.T = st.T = P.T;
     st.Cp = P.Cp;
-    st.lshift = (P.blk_L == 4) ? 2 : 1;
     st.gstride = 0;
 #pragma unroll
     for (int k = 0; k < L; ++k) {
@@ -175,6 +179,7 @@ struct RowProblemRGBA {
     }
   };
   struct Storer {
+    static constexpr bool kPrefetch = false;
     float* row;  // row-major: start of the row; blocked: BlockedDst::base
     long long dl, dr, gstride;
     int pad, T;
@@ -185,7 +190,7 @@ struct RowProblemRGBA {
       if constexpr (!BLOCKED) {
         reinterpret_cast<float4*>(row)[x] = o;
       } else {
-        float* d = row + (long long)x * gstride;
+        float* d = row + (long long)(x >> 3) * gstride + ((x & 7) << 2);
         *reinterpret_cast<float4*>(d) = o;
         if (dl) *reinterpret_cast<float4*>(d + dl) = o;
         if (dr) *reinterpret_cast<float4*>(d + dr) = o;
@@ -227,15 +232,18 @@ struct RowProblemRGBA1 {
     }
   };
   struct Storer {
+    static constexpr bool kPrefetch = false;
     float* row;
     long long dl, dr, gstride;
     int pad, T;
     __device__ __forceinline__ void store(int n, const Pt<1>& v) const {
       const int x = n - pad;
       if (x < 0 || x >= T) return;
-      float* d = row + (long long)x * gstride;
-      *reinterpret_cast<float2*>(d) = v.v[0];
-      if constexpr (BLOCKED) {
+      if constexpr (!BLOCKED) {
+        *reinterpret_cast<float2*>(row + (long long)x * 4) = v.v[0];
+      } else {
+        float* d = row + (long long)(x >> 3) * gstride + ((x & 7) << 2);
+        *reinterpret_cast<float2*>(d) = v.v[0];
         if (dl) *reinterpret_cast<float2*>(d + dl) = v.v[0];
         if (dr) *reinterpret_cast<float2*>(d + dr) = v.v[0];
       }
@@ -249,7 +257,7 @@ struct RowProblemRGBA1 {
     st.dl = st.dr = 0;
     if constexpr (!BLOCKED) {
       st.row = P.inter + (long long)r * P.inter_pitch + 2 * p;
-      st.gstride = 4;
+      st.gstride = 0;
     } else {
       const BlockedDst d = make_blocked_dst(P, r);
       st.row = d.base + 2 * p;
@@ -275,24 +283,25 @@ struct ColParams {
   long long out_pitch;     // bytes per image row
   long long out_frame_stride;
   int C, Cp;
-  // BULK problems: inter is the blocked layout [frame][group][np slots][L floats]; one unit is one
-  // contiguous run of unit_bytes that is bulk-copied straight into the exchange buffer
-  long long unit_stride;   // floats between consecutive groups = np * L
-  unsigned unit_bytes;     // np * L * 4 (multiple of 16)
+  // BULK problems: inter is the panel layout [frame][panel][np slots][32 floats]; a unit's padded
+  // line is np pieces of L floats at a 128-byte stride, gathered with cp.async into the exchange buffer
+  long long panel_stride;  // floats between consecutive panels = np * 32
+  int np;                  // slots per unit
 };
 
 // PACKED: Cp == C and every row/pitch is aligned so that the 2*NSEQ bytes of a unit are one
 // aligned 16/32-bit store; otherwise bytes are scattered individually.
-// BULK: the unit is fetched with one cp.async.bulk from the blocked intermediate (padding and
-// mirrored border rows were already written by the row pass), so the Loader is never called.
+// BULK: the unit is gathered with cp.async from the panel intermediate (padding and mirrored
+// border rows were already written by the row pass), so the Loader is never called.
 template <int NSEQ, bool PACKED, bool BULK = false>
 struct ColProblem {
   static constexpr int L = 2 * NSEQ;
   static constexpr bool kBulkIn = BULK;
-  static __device__ __forceinline__ const void* bulk_src(const ColParams& P, int unit) {
+  static __device__ __forceinline__ const float* bulk_src(const ColParams& P, int unit) {
     const int f = unit / P.groups_per_frame;
     const int g = unit - f * P.groups_per_frame;
-    return P.inter + (long long)f * P.frame_stride + (long long)g * P.unit_stride;
+    const int w0 = g * L;
+    return P.inter + (long long)f * P.frame_stride + (long long)(w0 >> 5) * P.panel_stride + (w0 & 31);
   }
   struct Loader {
     const float* col;  // inter + frame*frame_stride + w0
@@ -317,10 +326,15 @@ struct ColProblem {
     }
   };
   struct Storer {
+    static constexpr bool kPrefetch = BULK;
     uint8_t* base;  // out + frame*out_frame_stride (+ w0 when PACKED)
     long long pitch;
     int off[L];     // byte offset of each line inside a row, -1 = not stored (generic path)
     int pad, T;
+    const float* next_src;  // BULK: padded line of the unit this CTA processes next, or nullptr
+    __device__ __forceinline__ void prefetch(typename SmemElem<NSEQ>::type* dst, int phys_slot) const {
+      if (next_src) cp_async<8 * NSEQ>(dst, next_src + (long long)phys_slot * kPanelFloats);
+    }
     __device__ __forceinline__ void store(int n, const Pt<NSEQ>& v) const {
       const int r = n - pad;
       if (r < 0 || r >= T) return;
@@ -353,6 +367,11 @@ struct ColProblem {
     ld.col = P.inter + (long long)f * P.frame_stride + w0;
     st.pitch = P.out_pitch;
     st.base = P.out + (long long)f * P.out_frame_stride + (PACKED ? w0 : 0);
+    st.next_src = nullptr;
+    if constexpr (BULK) {
+      const int next = unit + (int)gridDim.x;
+      if (next < P.nunits) st.next_src = bulk_src(P, next);
+    }
 #pragma unroll
     for (int k = 0; k < L; ++k) {
       const int w = w0 + k;
