@@ -80,7 +80,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError(f"nvcc not found at {NVCC}; cannot build the sm_100a library")
 
     jobs = []  # (name, cmd)
-    for name in ("kernels.cu", "generic_row.cu", "generic_col.cu"):
+    for name in ("kernels.cu", "generic_row.cu", "generic_col.cu", "cluster_kernels.cu"):
         o = os.path.join(OBJ, name.replace(".cu", ".o"))
         jobs.append((o, [NVCC, *ARCH, *COMMON, "-c", os.path.join(CSRC, name), "-o", o]))
     for sid in _static_ids():

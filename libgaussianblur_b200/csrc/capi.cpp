@@ -320,9 +320,11 @@ static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_f
     return e && std::strcmp(e, "rowmajor") == 0;
   }();
   const BlockedLayout blk = blocked_layout(p, cp);
-  const BlockedLayout* bp = rowmajor ? nullptr : &blk;
+  // a column pass that runs on a cluster reads the row-major intermediate
+  const bool use_rowmajor = rowmajor || p->col.lp.cluster > 1;
+  const BlockedLayout* bp = use_rowmajor ? nullptr : &blk;
   const long long pitch = default_pitch((long long)p->cols * cp);
-  const int layout_tag = rowmajor ? -cp : cp;
+  const int layout_tag = use_rowmajor ? -cp : cp;
   if (p->inter_cp != 0 && p->inter_cp != layout_tag) {
     // the zero tail / padding slots of the new layout may hold samples of the old one
     CU(cudaMemsetAsync(p->d_inter, 0, p->inter_floats * sizeof(float), s));

@@ -292,6 +292,48 @@ __device__ __forceinline__ void run_line_generic(const LineShape& sh, const Load
   }
 }
 
+// Stages 1 .. S-1 forward, the fused last stage and the inverse stages S-2 .. 1 on a buffer that
+// holds `nloc` consecutive positions of the line (cluster kernels: stage 0 crosses CTAs and is
+// done by the caller; after it the positions [c*nloc, (c+1)*nloc) are self-contained).
+// `kperm` already points at this range's gains.
+template <int NSEQ, class Loader, class Storer>
+__device__ __forceinline__ void run_local_stages(const LineShape& sh, int nloc, const float* kperm, const Loader& ld,
+                                                 const Storer& st, typename SmemElem<NSEQ>::type* sm, int tid,
+                                                 int nthreads) {
+  const int S = sh.nstages;
+  for (int s = 1; s < S - 1; ++s) {
+    switch (sh.radix[s]) {
+#define X(R_)                                                                                  \
+  case R_:                                                                                     \
+    fwd_stage<R_, NSEQ, false, false>(ld, sm, sh.tw[s], nloc, sh.M[s], sh.padq, tid, nthreads); \
+    break;
+      GBLUR_FOR_EACH_GENERIC_RADIX(X)
+#undef X
+    }
+    __syncthreads();
+  }
+  switch (sh.radix[S - 1]) {
+#define X(R_)                                                                \
+  case R_:                                                                   \
+    fused_last_stage<R_, NSEQ, false>(sm, kperm, nloc, sh.padq, tid, nthreads); \
+    break;
+    GBLUR_FOR_EACH_GENERIC_RADIX(X)
+#undef X
+  }
+  __syncthreads();
+  for (int s = S - 2; s >= 1; --s) {
+    switch (sh.radix[s]) {
+#define X(R_)                                                                                  \
+  case R_:                                                                                     \
+    inv_stage<R_, NSEQ, false, false>(st, sm, sh.tw[s], nloc, sh.M[s], sh.padq, tid, nthreads); \
+    break;
+      GBLUR_FOR_EACH_GENERIC_RADIX(X)
+#undef X
+    }
+    __syncthreads();
+  }
+}
+
 // compile-time shapes: R3 == 1 -> three stages, R2 == R3 == 1 -> two stages
 template <int R0, int R1, int R2, int R3>
 struct StaticShape {

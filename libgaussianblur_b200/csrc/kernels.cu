@@ -77,6 +77,7 @@ cudaError_t launch_rowpass(const LinePlan& lp, const RowLaunch& a, int num_sms, 
   const bool rgba = (lp.nseq == 2 || lp.static_id >= 0) && a.C == 4 && a.Cp == 4 && (a.in_pitch % 4) == 0 &&
                     (reinterpret_cast<uintptr_t>(a.in) % 4) == 0 && (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0 &&
                     (blocked || (a.inter_pitch % 4) == 0);
+  if (lp.cluster > 1) return launch_row_cluster(lp, P, blocked, stream);
   switch (lp.static_id) {
 #define X(ID, NSEQ, R0, R1, R2, R3, NT, MINB) \
   case ID:                                    \
@@ -110,6 +111,7 @@ cudaError_t launch_colpass(const LinePlan& lp, const ColLaunch& a, int num_sms, 
   if (blocked) P.frame_stride = a.blk.frame_stride;
   const bool packed = a.C == a.Cp && (a.W % L) == 0 && (a.out_pitch % L) == 0 && (a.out_frame_stride % L) == 0 &&
                       (reinterpret_cast<uintptr_t>(a.out) % L) == 0;
+  if (lp.cluster > 1) return blocked ? cudaErrorInvalidValue : launch_col_cluster(lp, P, packed, stream);
   switch (lp.static_id) {
 #define X(ID, NSEQ, R0, R1, R2, R3, NT, MINB) \
   case ID:                                    \

@@ -22,7 +22,8 @@ struct LinePlan {
   int nthreads = 0;      // CTA size for the runtime-radix kernel
   int static_id = -1;    // index into the compile-time shape table, -1 = runtime-radix kernel
   size_t smem_bytes = 0; // dynamic shared memory per CTA (exchange buffer + in-smem tables)
-  int exch_elems = 0;    // exchange-buffer slots (N + bank-padding slots)
+  int exch_elems = 0;    // exchange-buffer slots (N + bank-padding slots); per CTA for cluster plans
+  int cluster = 1;       // CTAs per line unit: > 1 = thread-block cluster, the line is split over their shared memories
 };
 
 // Panel intermediate [frame][panel = w/32][np slots][32 floats] (see problems.cuh): the row pass

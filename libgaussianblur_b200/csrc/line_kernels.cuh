@@ -131,5 +131,8 @@ cudaError_t launch_col_static(const LinePlan&, const ColParams&, bool packed, bo
 cudaError_t launch_row_generic(const LinePlan&, const RowParams&, bool rgba, bool blocked, int num_sms, cudaStream_t);
 cudaError_t launch_col_generic(const LinePlan&, const ColParams&, bool packed, bool blocked, int num_sms,
                                cudaStream_t);
+// cluster_kernels.cu: lines split over the shared memories of a thread-block cluster
+cudaError_t launch_row_cluster(const LinePlan&, const RowParams&, bool blocked, cudaStream_t);
+cudaError_t launch_col_cluster(const LinePlan&, const ColParams&, bool packed, cudaStream_t);
 
 }  // namespace gblur

@@ -126,6 +126,68 @@ inline bool plan_line(int N, LinePlan& lp) {
     lp.nthreads = sid >= 0 ? st_threads : std::min(512, std::max(32, ((max_nb + 31) / 32) * 32));
     return true;
   }
+  // Too long for one CTA: split the line over a thread-block cluster of G CTAs (distributed
+  // shared memory). Stage 0 is radix 16 and crosses CTAs; after it the line falls apart into 16
+  // independent sub-transforms of length N/16, 16/G of them per CTA, which run locally.
+  for (int G = 2; G <= 8; G *= 2) {
+    if (N % (16 * G)) continue;
+    Factorization rest;
+    int cur[kHostMaxStages];
+    long long best_cost = 1LL << 60;
+    // at most kHostMaxStages - 1 further stages
+    struct Local {
+      static void go(int rem, int max_r, int depth, int* cur, Factorization& best, long long& best_cost) {
+        if (rem == 1) {
+          if (depth < 1) return;
+          long long sum = 0;
+          for (int i = 0; i < depth; ++i) sum += cur[i];
+          const long long cost = (long long)depth * 1000 + sum;
+          if (cost < best_cost) {
+            best_cost = cost;
+            best.nstages = depth;
+            for (int i = 0; i < kHostMaxStages; ++i) best.radix[i] = i < depth ? cur[i] : 1;
+          }
+          return;
+        }
+        if (depth == kHostMaxStages - 1) return;
+        for (int r : generic_radices()) {
+          if (r > max_r || rem % r) continue;
+          cur[depth] = r;
+          go(rem / r, r, depth + 1, cur, best, best_cost);
+        }
+      }
+    };
+    Local::go(N / 16, 16, 0, cur, rest, best_cost);
+    if (rest.nstages == 0) continue;
+    for (int i = rest.nstages - 1; i >= 0; --i) {
+      if (rest.radix[i] % 4 == 0) {
+        std::swap(rest.radix[i], rest.radix[rest.nstages - 1]);
+        break;
+      }
+    }
+    const int rlast = rest.radix[rest.nstages - 1];
+    const int nloc = N / G;
+    const int exch = exch_elems_for(nloc, rlast);
+    const size_t smem = (size_t)exch * 8;
+    if (smem > kMaxSmemBytes) continue;
+    lp.cluster = G;
+    lp.nseq = 1;
+    lp.exch_elems = exch;
+    lp.nstages = rest.nstages + 1;
+    lp.radix[0] = 16;
+    lp.M[0] = N / 16;
+    int m = N / 16;
+    for (int s = 0; s < rest.nstages; ++s) {
+      lp.radix[s + 1] = rest.radix[s];
+      m /= rest.radix[s];
+      lp.M[s + 1] = m;
+    }
+    lp.padq = (rlast % 2 == 0) ? rlast : 0;
+    lp.smem_bytes = smem;
+    lp.static_id = -1;
+    lp.nthreads = 512;
+    return true;
+  }
   return false;
 }
 

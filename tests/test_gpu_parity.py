@@ -216,3 +216,42 @@ def test_band_passes_equal_whole_image(gb):
         out[:, k * bc:(k + 1) * bc] = band_out
         p.close()
     assert np.array_equal(out.cpu().numpy(), whole)
+
+
+@pytest.mark.parametrize("n_target,ch", [(34560, 1), (34560, 3), (69120, 3), (69120, 4)])
+def test_cluster_kernel_long_rows(gb, refcheck, n_target, ch):
+    """Row FFT lengths of BASELINE.json configs 4 and 5 (34560, 69120) do not fit one CTA: the line is
+    split over a thread-block cluster (distributed shared memory)."""
+    sigma = 3.0
+    pad = (go.gaussian_window(sigma, 100000) - 1) // 2
+    cols = n_target - 2 * pad
+    rows = 20
+    assert gb.host_plan_sizes(rows, cols, sigma)["n_rowpass"] == n_target
+    shape = (rows, cols) if ch == 1 else (rows, cols, ch)
+    img = go.synth_u8(shape, n_target + ch)
+    out, _, _ = _blur_gpu(gb, img, sigma, True)
+    _assert_close_u8(out, refcheck.blur(img, sigma, True), f"N={n_target} ch={ch}")
+
+
+@pytest.mark.parametrize("ch", [1, 3])
+def test_cluster_kernel_long_columns(gb, refcheck, ch):
+    """Column FFT length 34560 (configs 4 and 5): cluster kernel on the column pass."""
+    sigma = 3.0
+    pad = (go.gaussian_window(sigma, 100000) - 1) // 2
+    rows = 34560 - 2 * pad
+    cols = 24
+    assert gb.host_plan_sizes(rows, cols, sigma)["n_colpass"] == 34560
+    shape = (rows, cols) if ch == 1 else (rows, cols, ch)
+    img = go.synth_u8(shape, 77 + ch)
+    out, _, _ = _blur_gpu(gb, img, sigma, True)
+    _assert_close_u8(out, refcheck.blur(img, sigma, True), f"N_col=34560 ch={ch}")
+
+
+def test_large_sigma_long_line(gb, refcheck):
+    """sigma=50 on a 33000-wide single plane (config 4's kernel: 331 taps, N=34560 on rows)."""
+    sigma = 50.0
+    sz = gb.host_plan_sizes(400, 34000, sigma)
+    assert sz["n_rowpass"] == 34560
+    img = go.synth_u8((400, 34000), 4)
+    out, _, _ = _blur_gpu(gb, img, sigma, False)
+    _assert_close_u8(out, refcheck.blur(img, sigma, False), "sigma=50 N=34560")
