@@ -30,11 +30,20 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 WORKLOADS = {
-    # name: (rows, cols, channels, sigma, apply_to_alpha)
+    # name: (rows, cols, channels, sigma, apply_to_alpha)   one image per GPU per step (weak scaling)
     "8k_rgba_sigma20": (4320, 7680, 4, 20.0, True),
     "1080p_rgb_sigma5": (1080, 1920, 3, 5.0, False),
     "1080p_rgb_sigma10": (1080, 1920, 3, 10.0, False),
+    # BASELINE.json config 3: 512 frames sharded by frame over the ranks, no collective (strong scaling)
+    "video_1080p_x512_sigma10": (1080, 1920, 3, 10.0, False),
+    # BASELINE.json config 4: one 32768^2 single-channel image, row bands + all-to-all (strong scaling)
+    "band_32k_gray_sigma50": (32768, 32768, 1, 50.0, False),
+    # BASELINE.json config 5: 65536 x 32768 RGB, sigma=150 (FFT lengths 69120 / 34560), row bands + all-to-all
+    "band_64kx32k_rgb_sigma150": (32768, 65536, 3, 150.0, False),
+    # a 4x smaller band-sharded case for quick checks
+    "band_16k_gray_sigma50": (16384, 16384, 1, 50.0, False),
 }
+VIDEO_FRAMES = 512
 METRIC = "Mpixel/s 8K RGBA sigma=20"
 UNIT = "Mpixel/s"
 
@@ -157,6 +166,168 @@ def run_reference_arm(args, wl):
     return 0
 
 
+def _events(torch):
+    return torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+
+def bench_video(args, wl, torch, dist, gb, world, rank, local, barrier):
+    """Config 3: VIDEO_FRAMES frames of 1080p RGB sharded by frame (contiguous blocks), one plan per rank,
+    no collective. value = all frames' pixels / max-over-ranks time."""
+    from libgaussianblur_b200.multi import FrameShardedBlur
+    from libgaussianblur_b200.synth import synth_u8
+
+    rows, cols, ch, sigma, alpha = WORKLOADS[wl]
+    fs = FrameShardedBlur(VIDEO_FRAMES, rows, cols, ch, sigma, device=local, chunk_frames=args.chunk_frames)
+    f0, f1 = fs.frames
+    n_local = f1 - f0
+    one = synth_u8((rows, cols, ch), 0x1234 + 2)
+    d_in = torch.from_numpy(one).cuda().unsqueeze(0).repeat(n_local, 1, 1, 1).contiguous()
+    d_in[:, 0, 0, 0] = torch.arange(f0, f1, device="cuda").to(torch.uint8)  # frames differ
+    d_out = torch.empty_like(d_in)
+    h_pin = torch.empty((fs.chunk, rows, cols, ch), dtype=torch.uint8).pin_memory()
+    h_pin.copy_(d_in[: fs.chunk].cpu())
+    stream = torch.cuda.current_stream()
+    for _ in range(max(args.warmup, 3)):
+        fs.run(d_in, d_out, alpha)
+    barrier()
+    l0 = gb.launch_count()
+    e0, e1 = _events(torch)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        fs.run(d_in, d_out, alpha)
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = gb.launch_count() - l0
+    # e2e: every chunk goes host -> device -> host through the host-buffer C-ABI call
+    nchunks = (n_local + fs.chunk - 1) // fs.chunk
+    fs.plan.run_host(h_pin, alpha, n_frames=fs.chunk)
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        for _c in range(nchunks):
+            fs.plan.run_host(h_pin, alpha, n_frames=fs.chunk)
+    torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    fs.close()
+    npx_step = VIDEO_FRAMES * rows * cols
+    cp = ch
+    return dict(ms_total=ms, e2e_ms=e2e_ms, npx_step=npx_step, launches=launches, scaling="strong",
+                alg_bytes_step=npx_step * 10 * cp, h2d=nchunks * fs.chunk * rows * cols * ch,
+                d2h=nchunks * fs.chunk * rows * cols * ch,
+                config={"workload": wl, "frames": VIDEO_FRAMES, "rows": rows, "cols": cols, "channels": ch, "sigma": sigma,
+                        "apply_to_alpha": alpha, "parallelism": f"frames sharded x{world}, no collective",
+                        "frames_per_rank": n_local, "chunk_frames": fs.chunk,
+                        "l2": f"{n_local * rows * cols * ch / 1e6:.0f} MB u8 per rank per step, larger than L2"},
+                phases_ms=None)
+
+
+def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier):
+    """Config 4: one big single-channel image. 1 GPU: the fused run. N GPUs: row bands, row pass local,
+    NCCL all-to-all of the fp32 intermediate, column pass local (output stays column-band-owned)."""
+    from libgaussianblur_b200.multi import BandShardedBlur, shard_range
+    from libgaussianblur_b200.synth import synth_u8
+
+    rows, cols, ch, sigma, alpha = WORKLOADS[wl]
+    r0, r1 = shard_range(rows, world, rank)
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(0x1234 + 3 + rank)  # uniform u8 generated on the device (the bands are GBs)
+    band = torch.randint(0, 256, (r1 - r0, cols, ch), dtype=torch.uint8, device="cuda", generator=gen)
+    h_pin = torch.empty_like(band, device="cpu").pin_memory()
+    h_pin.copy_(band.cpu())
+    stream = torch.cuda.current_stream()
+    phases = {}
+    if world == 1:
+        plan = gb.Plan(rows, cols, ch, sigma, device=local)
+        d_out = torch.empty_like(band)
+        step = lambda: plan.run_device(band, d_out, alpha)
+        e2e_step = lambda: plan.run_host(h_pin, alpha)
+        h2d = d2h = band.numel()
+        closer = plan.close
+    else:
+        bs = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, device=local)
+        step = lambda: bs.run(band)
+        h_out = torch.empty((rows, bs.my_cols[1] - bs.my_cols[0], ch), dtype=torch.uint8).pin_memory()
+
+        def e2e_step():
+            d = h_pin.cuda(non_blocking=True)
+            h_out.copy_(bs.run(d), non_blocking=True)
+            torch.cuda.synchronize()
+
+        h2d, d2h = band.numel(), h_out.numel()
+        closer = bs.close
+    for _ in range(max(args.warmup, 3)):
+        step()
+    barrier()
+    l0 = gb.launch_count()
+    e0, e1 = _events(torch)
+    barrier()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = gb.launch_count() - l0
+    if world == 1:
+        for name, st in (("row_pass", 1), ("col_pass", 2)):
+            k0, k1 = _events(torch)
+            torch.cuda.synchronize()
+            k0.record(stream)
+            for _ in range(args.steps):
+                plan.run_stage(st, band, d_out, alpha)
+            k1.record(stream)
+            torch.cuda.synchronize()
+            phases[name] = k0.elapsed_time(k1) / args.steps
+    else:
+        phases["exchanged_bytes_per_rank"] = bs.exchanged_bytes
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_ms = (time.perf_counter() - t0) * 1e3
+    closer()
+    npx_step = rows * cols
+    return dict(ms_total=ms, e2e_ms=e2e_ms, npx_step=npx_step, launches=launches, scaling="strong",
+                alg_bytes_step=npx_step * 10 * ch, h2d=h2d, d2h=d2h,
+                config={"workload": wl, "rows": rows, "cols": cols, "channels": ch, "sigma": sigma,
+                        "apply_to_alpha": alpha,
+                        "parallelism": "single GPU" if world == 1 else f"row bands x{world} + NCCL all-to-all + column bands",
+                        "l2": "inputs larger than L2"},
+                phases_ms=phases)
+
+
+def finish_multi(args, res, torch, dist, world, rank, sampler):
+    t = torch.tensor([res["ms_total"], res["e2e_ms"]], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total, e2e_ms = float(t[0]), float(t[1])
+    clocks = sampler.stop() if rank == 0 else None
+    if rank != 0:
+        return
+    peak, peak_src = load_peaks()
+    per_step_s = ms_total / args.steps * 1e-3
+    value = res["npx_step"] / per_step_s / 1e6
+    achieved = res["alg_bytes_step"] / world / per_step_s / 1e9  # per GPU, whole step
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+        "scaling": res["scaling"], "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": res["config"],
+        "e2e": {"value": res["npx_step"] / (e2e_ms / args.steps * 1e-3) / 1e6, "unit": UNIT,
+                "h2d_bytes_per_step": int(res["h2d"]), "d2h_bytes_per_step": int(res["d2h"]),
+                "ms_per_step": e2e_ms / args.steps},
+        "gpu_launches": int(res["launches"]),
+        "roofline": {"bound": "hbm", "kernel": "whole step (row pass + column pass" + (" + exchange)" if world > 1 and "band" in res["config"]["workload"] else ")"),
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "peak_source": peak_src, "algorithmic_bytes_per_launch": int(res["alg_bytes_step"] // world)},
+        "phases_ms": res["phases_ms"], "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -165,10 +336,17 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="8k_rgba_sigma20", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--chunk-frames", type=int, default=16, help="frames per launch in the video workload")
     args = ap.parse_args()
     wl = args.workload
     if args.impl == "reference":
         return run_reference_arm(args, wl)
+
+    # rank 0 prints ONE JSON line: libraries (NCCL's version banner) write to fd 1, so park the real
+    # stdout and point fd 1 at stderr until the line is ready
+    real_stdout = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    sys.stdout = real_stdout
 
     import torch
     import torch.distributed as dist
@@ -192,6 +370,16 @@ def main():
         torch.cuda.synchronize()
 
     gb.lib()
+    if wl.startswith("video_") or wl.startswith("band_"):
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        fn = bench_video if wl.startswith("video_") else bench_band
+        res = fn(args, wl, torch, dist, gb, world, rank, local, barrier)
+        finish_multi(args, res, torch, dist, world, rank, sampler)
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
     plan = gb.Plan(rows, cols, ch, sigma, device=local)
     npx = rows * cols
     img = synth_u8((rows, cols, ch), 0x1234 + 1 + rank)
@@ -286,7 +474,7 @@ def main():
             else:
                 line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": 0, "kind": "reference",
                                         "sample": "oracle/_ref not built"}
-        print(json.dumps(line))
+        print(json.dumps(line), flush=True)
     plan.close()
     if world > 1:
         dist.destroy_process_group()

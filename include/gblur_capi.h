@@ -16,6 +16,7 @@
  *                            :246-287, process_channel_tiles :202-244, interleave :289-305)
  *   gblur_run_batch_device   a loop of the above over frames with ONE kernel spectrum (additive)
  *   gblur_rowpass_device     process_channel_tiles, first call  src/gaussianblur.cpp:268-272
+ *   gblur_rowpass_split_device  the same first call, output laid out per destination rank (additive)
  *   gblur_colpass_device     process_channel_tiles, second call src/gaussianblur.cpp:275-279
  *   gblur_dump_intermediate  (test hook) the fp32 plane after pass 1
  */
@@ -80,6 +81,12 @@ int gblur_run_stage_device(gblur_plan* plan, const uint8_t* d_in, uint8_t* d_out
  * [full_rows][out_pitch bytes] with band_cols*channels valid bytes per row. */
 int gblur_rowpass_device(gblur_plan* plan, const uint8_t* d_in, float* d_inter, long long inter_pitch_floats,
                          int apply_to_alpha, void* cuda_stream);
+/* Row pass that writes the send buffer of the band-sharded all-to-all directly: pixel columns are cut in
+ * bands of split_cols; element (r, x, ch) lands at
+ *   d_inter[(x / split_cols) * split_stride_floats + r * split_cols * Cp + (x % split_cols) * Cp + ch],
+ * i.e. one contiguous [band_rows][split_cols * Cp] block per destination rank. */
+int gblur_rowpass_split_device(gblur_plan* plan, const uint8_t* d_in, float* d_inter, int split_cols,
+                               long long split_stride_floats, int apply_to_alpha, void* cuda_stream);
 int gblur_colpass_device(gblur_plan* plan, const float* d_inter, long long inter_pitch_floats, uint8_t* d_out,
                          long long out_pitch_bytes, int apply_to_alpha, void* cuda_stream);
 

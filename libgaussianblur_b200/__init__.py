@@ -27,7 +27,7 @@ __all__ = ["Plan", "GblurError", "lib", "gaussianblur", "gaussianblur_module", "
 EXPORTED_SYMBOLS = [
     "gblur_plan_create", "gblur_plan_create_batch", "gblur_plan_create_band", "gblur_plan_destroy",
     "gblur_plan_info", "gblur_plan_spectrum", "gblur_plan_radices", "gblur_run_host", "gblur_run_batch_host",
-    "gblur_run_device", "gblur_run_batch_device", "gblur_run_stage_device", "gblur_rowpass_device", "gblur_colpass_device",
+    "gblur_run_device", "gblur_run_batch_device", "gblur_run_stage_device", "gblur_rowpass_device", "gblur_rowpass_split_device", "gblur_colpass_device",
     "gblur_dump_intermediate", "gblur_launch_count", "gblur_last_error", "gblur_device_count",
     "gblur_host_plan_sizes", "gblur_host_taps", "gblur_host_spectrum", "gblur_host_line_plan", "gblur_host_kperm",
 ]
@@ -68,6 +68,7 @@ def lib():
         "gblur_run_batch_device": (C.c_int, [vp, u8p, u8p, C.c_int, C.c_int, vp]),
         "gblur_run_stage_device": (C.c_int, [vp, u8p, u8p, C.c_int, C.c_int, vp, C.c_int]),
         "gblur_rowpass_device": (C.c_int, [vp, u8p, vp, ll, C.c_int, vp]),
+        "gblur_rowpass_split_device": (C.c_int, [vp, u8p, vp, C.c_int, ll, C.c_int, vp]),
         "gblur_colpass_device": (C.c_int, [vp, vp, ll, u8p, ll, C.c_int, vp]),
         "gblur_dump_intermediate": (C.c_int, [vp, fp, C.c_int]),
         "gblur_launch_count": (C.c_ulonglong, []),
@@ -225,6 +226,12 @@ class Plan:
     def rowpass(self, d_in, d_inter, inter_pitch_floats: int, apply_to_alpha: bool = False, stream=None):
         _check(lib().gblur_rowpass_device(self._h, _ptr(d_in), _ptr(d_inter), inter_pitch_floats,
                                           int(bool(apply_to_alpha)), _stream_ptr(stream)))
+
+    def rowpass_split(self, d_in, d_inter, split_cols: int, split_stride_floats: int, apply_to_alpha: bool = False,
+                      stream=None):
+        """Row pass writing one contiguous [band_rows, split_cols*Cp] block per column band (all-to-all send buffer)."""
+        _check(lib().gblur_rowpass_split_device(self._h, _ptr(d_in), _ptr(d_inter), split_cols, split_stride_floats,
+                                                int(bool(apply_to_alpha)), _stream_ptr(stream)))
 
     def colpass(self, d_inter, inter_pitch_floats: int, d_out, out_pitch_bytes: int, apply_to_alpha: bool = False,
                 stream=None):

@@ -187,7 +187,7 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
 }
 
 int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pitch, int frames, int alpha,
-                cudaStream_t s, const BlockedLayout* blk = nullptr) {
+                cudaStream_t s, const BlockedLayout* blk = nullptr, int split_cols = 0, long long split_stride = 0) {
   const int cp = processed_channels(p, alpha);
   RowLaunch a{};
   a.in = d_in;
@@ -200,6 +200,8 @@ int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pi
   a.inter = d_inter;
   a.inter_pitch = pitch;
   if (blk) a.blk = *blk;
+  a.split_cols = split_cols;
+  a.split_stride = split_stride;
   CU(launch_rowpass(p->row.lp, a, p->num_sms, s));
   return GBLUR_OK;
 }
@@ -389,6 +391,18 @@ int gblur_rowpass_device(gblur_plan* p, const uint8_t* d_in, float* d_inter, lon
   if (inter_pitch_floats < (long long)p->full_cols * cp) return fail(GBLUR_E_INVALID, "intermediate pitch too small");
   DeviceGuard guard(p->device);
   return run_rowpass(p, d_in, d_inter, inter_pitch_floats, 1, apply_to_alpha, static_cast<cudaStream_t>(cuda_stream));
+}
+
+int gblur_rowpass_split_device(gblur_plan* p, const uint8_t* d_in, float* d_inter, int split_cols,
+                               long long split_stride_floats, int apply_to_alpha, void* cuda_stream) {
+  if (!p || !d_in || !d_inter) return fail(GBLUR_E_INVALID, "null argument");
+  if (split_cols < 1 || split_cols > p->full_cols) return fail(GBLUR_E_INVALID, "split_cols outside [1, cols]");
+  const int cp = processed_channels(p, apply_to_alpha);
+  if (split_stride_floats < (long long)p->rows * split_cols * cp)
+    return fail(GBLUR_E_INVALID, "split stride smaller than one band block");
+  DeviceGuard guard(p->device);
+  return run_rowpass(p, d_in, d_inter, (long long)split_cols * cp, 1, apply_to_alpha,
+                     static_cast<cudaStream_t>(cuda_stream), nullptr, split_cols, split_stride_floats);
 }
 
 int gblur_colpass_device(gblur_plan* p, const float* d_inter, long long inter_pitch_floats, uint8_t* d_out,

@@ -68,13 +68,15 @@ cudaError_t launch_rowpass(const LinePlan& lp, const RowLaunch& a, int num_sms, 
   const long long L = 2 * lp.nseq;
   P.nunits = (int)((P.nreal + L - 1) / L);
   const bool blocked = a.blk.enabled != 0;
+  P.split_cols = blocked ? 0 : a.split_cols;
+  P.split_stride = a.split_stride;
   P.rows_per_frame = blocked ? a.blk.rows_per_frame : 1;
   P.blk_L = a.blk.L;
   P.blk_np = a.blk.np;
   P.blk_padq = a.blk.padq;
   P.blk_frame_stride = a.blk.frame_stride;
   // uchar4/float4 (two sequences) or u16/float2 (one sequence, static shapes only) fast path
-  const bool rgba = (lp.nseq == 2 || lp.static_id >= 0) && a.C == 4 && a.Cp == 4 && (a.in_pitch % 4) == 0 &&
+  const bool rgba = P.split_cols == 0 && (lp.nseq == 2 || lp.static_id >= 0) && a.C == 4 && a.Cp == 4 && (a.in_pitch % 4) == 0 &&
                     (reinterpret_cast<uintptr_t>(a.in) % 4) == 0 && (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0 &&
                     (blocked || (a.inter_pitch % 4) == 0);
   if (lp.cluster > 1) return launch_row_cluster(lp, P, blocked, stream);

@@ -47,6 +47,8 @@ struct RowLaunch {
   float* inter;
   long long inter_pitch;
   BlockedLayout blk;
+  int split_cols = 0;          // row-major only: see RowParams::split_cols
+  long long split_stride = 0;
 };
 
 struct ColLaunch {

@@ -47,6 +47,10 @@ struct RowParams {
   float* inter;           // [rows_total][inter_pitch] fp32, element (r, x*Cp + ch)
   long long inter_pitch;  // floats per row
   int nunits;
+  // row-major only: pixel columns split in bands of split_cols (0 = off); band h of every row lives at
+  // inter + h * split_stride with row pitch split_cols * Cp (send buffer of the band-sharded all-to-all)
+  int split_cols;
+  long long split_stride;
   // panel intermediate (BLOCKED problems): [frame][panel = w/32][slot physc(n)][32 floats] with
   // w = x*Cp + ch the float column: every row writes whole 128-byte lines, and a column unit
   // (L adjacent float columns) finds its padded line at a fixed 128-byte stride; see BlockedDst
@@ -109,10 +113,17 @@ struct RowProblemGeneric {
     long long dl[L], dr[L], gstride;
     int ch[L];
     int Cp, pad, T;
+    int split_cols;
+    long long split_stride;
     __device__ __forceinline__ void put(int k, int x, float v) const {
       if (!q[k]) return;
       if constexpr (!BLOCKED) {
-        q[k][(long long)x * Cp] = v;
+        if (split_cols) {
+          const int h = x / split_cols;
+          q[k][(long long)h * split_stride + (long long)(x - h * split_cols) * Cp] = v;
+        } else {
+          q[k][(long long)x * Cp] = v;
+        }
       } else {
         const int w = x * Cp + ch[k];
         float* d = q[k] + (long long)(w >> 5) * gstride + (w & 31);
@@ -137,6 +148,8 @@ struct RowProblemGeneric {
     ld.T = st.T = P.T;
     st.Cp = P.Cp;
     st.gstride = 0;
+    st.split_cols = P.split_cols;
+    st.split_stride = P.split_stride;
 #pragma unroll
     for (int k = 0; k < L; ++k) {
       long long sig = (long long)unit * L + k;

@@ -1,0 +1,194 @@
+"""Multi-GPU host layer (one process per GPU, torch.distributed for the plumbing).
+
+Two partitionings of the hot path (the reference itself is single-process, its only
+parallelism is hybrid_loop's std::thread fan-out, /root/reference/include/gaussianblur/helpers.hpp:134-172):
+
+* frames  -> ranks, contiguous blocks, NO collective (video batches; every rank holds the same plan);
+* row bands of one image -> ranks: row pass local, ONE all-to-all of the fp32 intermediate so that every
+  rank then owns a band of pixel columns for all rows, column pass local. The all-to-all is NCCL
+  (`dist.all_to_all`) on GPUs; on backends without it (gloo, used by the CPU tests of this plumbing) the
+  same exchange is done with point-to-point sends.
+
+The compute is injected (`rowpass` / `colpass` callables): the product binds them to the CUDA plans
+(`BandShardedBlur.cuda`), the CPU tests bind them to the test oracle to check partitioning, packing and
+exchange without a GPU. There is no CPU compute path in this module.
+"""
+from __future__ import annotations
+
+from typing import Callable, List, Sequence, Tuple
+
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n: int, world: int, rank: int) -> Tuple[int, int]:
+    """Contiguous block [start, stop) of n items owned by `rank`; the first n % world ranks get one extra."""
+    base, rem = divmod(n, world)
+    start = rank * base + min(rank, rem)
+    return start, start + base + (1 if rank < rem else 0)
+
+
+def shard_ranges(n: int, world: int) -> List[Tuple[int, int]]:
+    return [shard_range(n, world, r) for r in range(world)]
+
+
+def exchange(send: Sequence[torch.Tensor], recv: Sequence[torch.Tensor], group=None) -> None:
+    """all-to-all of per-peer tensors (send[h] goes to rank h, recv[g] comes from rank g)."""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        recv[0].copy_(send[0])
+        return
+    world = dist.get_world_size(group)
+    rank = dist.get_rank(group)
+    if dist.get_backend(group) == "nccl":
+        dist.all_to_all(list(recv), list(send), group=group)
+        return
+    # gloo & co.: pairwise exchange, lower rank sends first (deadlock-free for blocking send/recv)
+    recv[rank].copy_(send[rank])
+    for peer in range(world):
+        if peer == rank:
+            continue
+        src = dist.get_global_rank(group, peer) if group is not None else peer
+        if rank < peer:
+            dist.send(send[peer].contiguous(), src, group=group)
+            dist.recv(recv[peer], src, group=group)
+        else:
+            dist.recv(recv[peer], src, group=group)
+            dist.send(send[peer].contiguous(), src, group=group)
+
+
+class BandShardedBlur:
+    """One (rows x cols x channels) image sharded by row bands over the ranks of `group`.
+
+    rowpass(band_u8[band_rows, cols, C]) -> fp32 [band_rows, cols * Cp]          (local rows, all columns)
+    colpass(inter[rows, band_cols * Cp], alpha_src) -> u8 [rows, band_cols, C]   (all rows, local columns)
+    run() returns the rank's band of pixel COLUMNS of the blurred image (all rows); `gather_rows=True`
+    adds a second (4x smaller, u8) all-to-all that returns to row-band ownership.
+    """
+
+    def __init__(self, rows: int, cols: int, channels: int, processed_channels: int,
+                 rowpass: Callable[[torch.Tensor], torch.Tensor],
+                 colpass: Callable[[torch.Tensor, torch.Tensor], torch.Tensor], group=None):
+        self.rows, self.cols, self.C, self.Cp = rows, cols, channels, processed_channels
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.row_ranges = shard_ranges(rows, self.world)
+        self.col_ranges = shard_ranges(cols, self.world)
+        self.rowpass, self.colpass = rowpass, colpass
+        self.rowpass_split = None  # optional: band -> [world, band_rows, cols/world, Cp] written in place
+        self.exchanged_bytes = 0  # bytes this rank sent to OTHER ranks in the last run
+
+    @property
+    def my_rows(self) -> Tuple[int, int]:
+        return self.row_ranges[self.rank]
+
+    @property
+    def my_cols(self) -> Tuple[int, int]:
+        return self.col_ranges[self.rank]
+
+    def run(self, band: torch.Tensor, gather_rows: bool = False) -> torch.Tensor:
+        r0, r1 = self.my_rows
+        c0, c1 = self.my_cols
+        Cp, C = self.Cp, self.C
+        assert band.shape[0] == r1 - r0 and band.shape[1] == self.cols
+        if self.rowpass_split is not None and self.cols % self.world == 0:
+            # the row pass writes the per-destination blocks itself: no packing copy
+            send = list(self.rowpass_split(band).unbind(0))
+            inter = send[0]
+        else:
+            inter = self.rowpass(band).view(r1 - r0, self.cols, Cp)
+            # pack: one contiguous block per destination rank (its pixel columns of my rows)
+            send = [inter[:, a:b, :].contiguous() for a, b in self.col_ranges]
+        recv_buf = torch.empty((self.rows, c1 - c0, Cp), dtype=inter.dtype, device=inter.device)
+        recv = [recv_buf[a:b] for a, b in self.row_ranges]  # row blocks of a row-major buffer: contiguous
+        self.exchanged_bytes = sum(t.numel() * t.element_size() for h, t in enumerate(send) if h != self.rank)
+        exchange(send, recv, self.group)
+        # the un-blurred alpha bytes (C == 4, Cp == 3) travel as u8 beside the intermediate
+        alpha_src = None
+        if Cp < C:
+            a_send = [band[:, a:b, C - 1].contiguous() for a, b in self.col_ranges]
+            alpha_src = torch.empty((self.rows, c1 - c0), dtype=band.dtype, device=band.device)
+            exchange(a_send, [alpha_src[a:b] for a, b in self.row_ranges], self.group)
+        out_cols = self.colpass(recv_buf.view(self.rows, (c1 - c0) * Cp), alpha_src)
+        if not gather_rows:
+            return out_cols
+        back_send = [out_cols[a:b].contiguous() for a, b in self.row_ranges]
+        parts = [torch.empty((r1 - r0, b - a, C), dtype=out_cols.dtype, device=out_cols.device)
+                 for a, b in self.col_ranges]
+        exchange(back_send, parts, self.group)
+        return torch.cat(parts, dim=1)
+
+    # ---- product binding: CUDA plans through the C ABI ----
+    @classmethod
+    def cuda(cls, rows: int, cols: int, channels: int, sigma: float, apply_to_alpha: bool = False, device: int = 0,
+             group=None) -> "BandShardedBlur":
+        import libgaussianblur_b200 as gb
+
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        rank = dist.get_rank(group) if dist.is_initialized() else 0
+        r0, r1 = shard_range(rows, world, rank)
+        c0, c1 = shard_range(cols, world, rank)
+        cp = 3 if (channels == 4 and not apply_to_alpha) else channels
+        p_row = gb.Plan(rows, cols, channels, sigma, device=device, band_rows=r1 - r0, band_cols=cols)
+        p_col = gb.Plan(rows, cols, channels, sigma, device=device, band_rows=rows, band_cols=c1 - c0)
+        dev = torch.device("cuda", device)
+        wb = (c1 - c0) * cp
+
+        def rowpass(band: torch.Tensor) -> torch.Tensor:
+            inter = torch.empty((r1 - r0, cols * cp), dtype=torch.float32, device=dev)
+            p_row.rowpass(band, inter, cols * cp, apply_to_alpha)
+            return inter
+
+        def colpass(inter: torch.Tensor, alpha_src) -> torch.Tensor:
+            pitch = (wb + 3) // 4 * 4
+            if pitch != wb:  # the kernels read 16-byte pieces: pad the pitch
+                padded = torch.zeros((rows, pitch), dtype=torch.float32, device=dev)
+                padded[:, :wb] = inter
+                inter = padded
+            out = torch.empty((rows, c1 - c0, channels), dtype=torch.uint8, device=dev)
+            if alpha_src is not None:
+                out[..., channels - 1] = alpha_src
+            p_col.colpass(inter, pitch, out, (c1 - c0) * channels, apply_to_alpha)
+            return out
+
+        def rowpass_split(band: torch.Tensor) -> torch.Tensor:
+            bc = cols // world
+            out = torch.empty((world, r1 - r0, bc, cp), dtype=torch.float32, device=dev)
+            p_row.rowpass_split(band, out, bc, (r1 - r0) * bc * cp, apply_to_alpha)
+            return out
+
+        self = cls(rows, cols, channels, cp, rowpass, colpass, group)
+        self.rowpass_split = rowpass_split
+        self.plans = (p_row, p_col)
+        return self
+
+    def close(self):
+        for p in getattr(self, "plans", ()):
+            p.close()
+
+
+class FrameShardedBlur:
+    """A batch of equal-geometry frames sharded by contiguous frame blocks; no collective. Every rank
+    builds the same plan once (kernel spectrum and twiddles reused for all its frames)."""
+
+    def __init__(self, n_frames: int, rows: int, cols: int, channels: int, sigma: float, device: int = 0,
+                 chunk_frames: int = 16, group=None):
+        import libgaussianblur_b200 as gb
+
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.frames = shard_range(n_frames, self.world, self.rank)
+        self.chunk = max(1, min(chunk_frames, self.frames[1] - self.frames[0]))
+        self.plan = gb.Plan(rows, cols, channels, sigma, device=device, max_frames=self.chunk)
+
+    def run(self, d_frames: torch.Tensor, d_out: torch.Tensor | None = None, apply_to_alpha: bool = False):
+        """d_frames: this rank's frames [n_local, rows, cols, C] u8 on the device."""
+        d_out = d_frames if d_out is None else d_out
+        n = d_frames.shape[0]
+        for f in range(0, n, self.chunk):
+            k = min(self.chunk, n - f)
+            self.plan.run_device(d_frames[f:f + k], d_out[f:f + k], apply_to_alpha, n_frames=k)
+        return d_out
+
+    def close(self):
+        self.plan.close()

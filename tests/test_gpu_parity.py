@@ -255,3 +255,31 @@ def test_large_sigma_long_line(gb, refcheck):
     img = go.synth_u8((400, 34000), 4)
     out, _, _ = _blur_gpu(gb, img, sigma, False)
     _assert_close_u8(out, refcheck.blur(img, sigma, False), "sigma=50 N=34560")
+
+
+def test_band_sharded_binding_single_rank(gb, refcheck):
+    """libgaussianblur_b200.multi.BandShardedBlur bound to the CUDA band plans, world size 1."""
+    import torch
+
+    from libgaussianblur_b200.multi import BandShardedBlur
+
+    for ch, alpha in ((1, False), (3, False), (4, False), (4, True)):
+        rows, cols, sigma = 96, 160, 4.0
+        img = go.synth_u8((rows, cols, ch) if ch > 1 else (rows, cols), 31 + ch)
+        b = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha)
+        out = b.run(torch.from_numpy(img).cuda().view(rows, cols, ch))
+        torch.cuda.synchronize()
+        b.close()
+        want = refcheck.blur(img, sigma, alpha)
+        _assert_close_u8(out.cpu().numpy().reshape(want.shape), want, f"band binding ch={ch} alpha={alpha}")
+
+
+def test_sigma150_rows_69120(gb, refcheck):
+    """Config 5's row pass: sigma=150 (997 taps, pad 498) on 68124-wide RGB rows -> FFT length 69120."""
+    sigma = 150.0
+    rows, cols = 600, 69120 - 2 * 498
+    sz = gb.host_plan_sizes(rows, cols, sigma)
+    assert sz["pad"] == 498 and sz["n_rowpass"] == 69120
+    img = go.synth_u8((rows, cols, 3), 150)
+    out, _, _ = _blur_gpu(gb, img, sigma, False)
+    _assert_close_u8(out, refcheck.blur(img, sigma, False), "sigma=150 N=69120")

@@ -1,0 +1,100 @@
+"""Multi-rank host logic on CPU (gloo, world_size 2 and 3): sharding, packing, the all-to-all exchange and
+re-assembly of the band-sharded path (libgaussianblur_b200/multi.py). The compute callables are bound to
+the test oracle here — this checks the plumbing, not the kernels; the GPU tests check the kernels."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from libgaussianblur_b200 import multi
+from oracle import gblur_oracle as go
+
+
+def test_shard_ranges_cover_everything():
+    for n in (1, 7, 8, 512, 32768, 4321):
+        for w in (1, 2, 3, 4, 8):
+            r = multi.shard_ranges(n, w)
+            assert r[0][0] == 0 and r[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(r, r[1:]))
+            sizes = [b - a for a, b in r]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _oracle_passes(rows, cols, ch, cp, sigma):
+    ksize, pad, n_rp, n_cp, _, _ = go.plan_sizes(rows, cols, sigma)
+
+    def rowpass(band):  # [band_rows, cols, C] u8 -> [band_rows, cols*cp] f32
+        x = band.numpy().astype(np.float64)
+        out = np.empty((x.shape[0], cols, cp), dtype=np.float32)
+        for c in range(cp):
+            out[..., c] = go.conv_lines(np.ascontiguousarray(x[..., c]), sigma, ksize, pad, n_rp)
+        return torch.from_numpy(out.reshape(x.shape[0], cols * cp))
+
+    def colpass(inter, alpha_src):  # [rows, bc*cp] f32 -> [rows, bc, C] u8
+        bc = inter.shape[1] // cp
+        v = inter.numpy().reshape(rows, bc, cp)
+        out = np.empty((rows, bc, ch), dtype=np.uint8)
+        for c in range(cp):
+            y = go.conv_lines(np.ascontiguousarray(v[..., c].T), sigma, ksize, pad, n_cp).T
+            out[..., c] = go.to_u8(y)
+        if alpha_src is not None:
+            out[..., ch - 1] = alpha_src.numpy()
+        return torch.from_numpy(out)
+
+    return rowpass, colpass
+
+
+def _worker(rank, world, port, rows, cols, ch, alpha, sigma, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        img = go.synth_u8((rows, cols, ch), 0x77)
+        cp = 3 if (ch == 4 and not alpha) else ch
+        rp, cpass = _oracle_passes(rows, cols, ch, cp, sigma)
+        b = multi.BandShardedBlur(rows, cols, ch, cp, rp, cpass)
+        r0, r1 = b.my_rows
+        out_cols = b.run(torch.from_numpy(img[r0:r1].copy()))
+        out_rows = b.run(torch.from_numpy(img[r0:r1].copy()), gather_rows=True)
+        q.put((rank, b.my_cols, out_cols.numpy(), b.my_rows, out_rows.numpy(), b.exchanged_bytes))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,ch,alpha", [(2, 3, False), (2, 4, False), (3, 4, True)])
+def test_band_sharded_exchange_matches_single_process(world, ch, alpha):
+    rows, cols, sigma = 37, 50, 2.0
+    img = go.synth_u8((rows, cols, ch), 0x77)
+    want = go.gaussianblur(img, sigma, alpha)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, rows, cols, ch, alpha, sigma, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    by_cols = np.empty_like(img)
+    by_rows = np.empty_like(img)
+    cp = 3 if (ch == 4 and not alpha) else ch
+    for rank, (c0, c1), oc, (r0, r1), orow, sent in got:
+        by_cols[:, c0:c1] = oc
+        by_rows[r0:r1] = orow
+        assert sent == (r1 - r0) * (cols - (c1 - c0)) * cp * 4  # fp32 bytes that left this rank
+    assert np.array_equal(by_cols, want)
+    assert np.array_equal(by_rows, want)
