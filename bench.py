@@ -246,7 +246,7 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier):
         h2d = d2h = band.numel()
         closer = plan.close
     else:
-        bs = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, device=local)
+        bs = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, device=local, fused=(args.exchange == "fused"))
         step = lambda: bs.run(band)
         h_out = torch.empty((rows, bs.my_cols[1] - bs.my_cols[0], ch), dtype=torch.uint8).pin_memory()
 
@@ -281,7 +281,14 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier):
             torch.cuda.synchronize()
             phases[name] = k0.elapsed_time(k1) / args.steps
     else:
-        phases["exchanged_bytes_per_rank"] = bs.exchanged_bytes
+        if bs.fused_run is not None:
+            bs.profile = True
+            step()
+            torch.cuda.synchronize()
+            phases.update(bs.phase_ms())
+            bs.profile = False
+        phases["exchange"] = bs.exchange_kind
+        phases["exchanged_bytes_per_rank"] = (r1 - r0) * (cols - cols // world) * ch * 4
     e2e_step()
     barrier()
     t0 = time.perf_counter()
@@ -295,7 +302,7 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier):
                 alg_bytes_step=npx_step * 10 * ch, h2d=h2d, d2h=d2h,
                 config={"workload": wl, "rows": rows, "cols": cols, "channels": ch, "sigma": sigma,
                         "apply_to_alpha": alpha,
-                        "parallelism": "single GPU" if world == 1 else f"row bands x{world} + NCCL all-to-all + column bands",
+                        "parallelism": "single GPU" if world == 1 else f"row bands x{world} + {args.exchange} exchange + column bands",
                         "l2": "inputs larger than L2"},
                 phases_ms=phases)
 
@@ -337,6 +344,8 @@ def main():
     ap.add_argument("--workload", default="8k_rgba_sigma20", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--chunk-frames", type=int, default=16, help="frames per launch in the video workload")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="band workloads: row pass stores into peer memory (fused) or NCCL all-to-all")
     args = ap.parse_args()
     wl = args.workload
     if args.impl == "reference":

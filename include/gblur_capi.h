@@ -90,6 +90,24 @@ int gblur_rowpass_split_device(gblur_plan* plan, const uint8_t* d_in, float* d_i
 int gblur_colpass_device(gblur_plan* plan, const float* d_inter, long long inter_pitch_floats, uint8_t* d_out,
                          long long out_pitch_bytes, int apply_to_alpha, void* cuda_stream);
 
+/* ---- band sharding with the exchange fused into the row pass (NVLink peer stores, no collective) ----
+ * Every rank owns a band of pixel columns and a PANEL buffer for it ([panel of 32 float columns][np slots]
+ * [32 floats]), allocated by gblur_band_panel_alloc on its column-band plan and exported to
+ * the other processes with gblur_ipc_export / gblur_ipc_open (CUDA IPC). gblur_rowpass_peer_device runs a row
+ * band and stores each 128-byte line (and the mirrored reflect_101 border rows) straight into the panel buffer
+ * of the rank that owns those columns — peer_panels[h] is rank h's buffer as mapped in THIS process. After a
+ * cross-rank barrier, gblur_colpass_panel_device blurs the columns out of the local panel buffer.
+ * cols*Cp must be a multiple of 32*n_peers. */
+int gblur_plan_panel_geometry(const gblur_plan* col_plan, int* np, int* padq);
+int gblur_band_panel_alloc(gblur_plan* col_plan, int apply_to_alpha, float** d_panel, long long* n_floats);
+int gblur_ipc_export(const void* d_ptr, unsigned char handle[64]);
+int gblur_ipc_open(const unsigned char handle[64], void** d_ptr);
+int gblur_ipc_close(void* d_ptr);
+int gblur_rowpass_peer_device(gblur_plan* row_plan, const uint8_t* d_in, float* const* peer_panels, int n_peers,
+                              int row_offset, int apply_to_alpha, void* cuda_stream);
+int gblur_colpass_panel_device(gblur_plan* col_plan, const float* d_panel, uint8_t* d_out, long long out_pitch_bytes,
+                               int apply_to_alpha, void* cuda_stream);
+
 /* Test hook: fp32 row-pass output of the last gblur_run_* call on this plan (frame 0), copied to
  * host as [rows][cols*Cp]. */
 int gblur_dump_intermediate(gblur_plan* plan, float* host_out, int apply_to_alpha);

@@ -28,6 +28,8 @@ EXPORTED_SYMBOLS = [
     "gblur_plan_create", "gblur_plan_create_batch", "gblur_plan_create_band", "gblur_plan_destroy",
     "gblur_plan_info", "gblur_plan_spectrum", "gblur_plan_radices", "gblur_run_host", "gblur_run_batch_host",
     "gblur_run_device", "gblur_run_batch_device", "gblur_run_stage_device", "gblur_rowpass_device", "gblur_rowpass_split_device", "gblur_colpass_device",
+    "gblur_plan_panel_geometry", "gblur_band_panel_alloc", "gblur_ipc_export", "gblur_ipc_open", "gblur_ipc_close",
+    "gblur_rowpass_peer_device", "gblur_colpass_panel_device",
     "gblur_dump_intermediate", "gblur_launch_count", "gblur_last_error", "gblur_device_count",
     "gblur_host_plan_sizes", "gblur_host_taps", "gblur_host_spectrum", "gblur_host_line_plan", "gblur_host_kperm",
 ]
@@ -70,6 +72,13 @@ def lib():
         "gblur_rowpass_device": (C.c_int, [vp, u8p, vp, ll, C.c_int, vp]),
         "gblur_rowpass_split_device": (C.c_int, [vp, u8p, vp, C.c_int, ll, C.c_int, vp]),
         "gblur_colpass_device": (C.c_int, [vp, vp, ll, u8p, ll, C.c_int, vp]),
+        "gblur_plan_panel_geometry": (C.c_int, [vp, ip, ip]),
+        "gblur_band_panel_alloc": (C.c_int, [vp, C.c_int, pp, C.POINTER(C.c_longlong)]),
+        "gblur_ipc_export": (C.c_int, [vp, C.c_char_p]),
+        "gblur_ipc_open": (C.c_int, [C.c_char_p, pp]),
+        "gblur_ipc_close": (C.c_int, [vp]),
+        "gblur_rowpass_peer_device": (C.c_int, [vp, u8p, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, vp]),
+        "gblur_colpass_panel_device": (C.c_int, [vp, vp, u8p, ll, C.c_int, vp]),
         "gblur_dump_intermediate": (C.c_int, [vp, fp, C.c_int]),
         "gblur_launch_count": (C.c_ulonglong, []),
         "gblur_last_error": (C.c_char_p, []),
@@ -233,6 +242,22 @@ class Plan:
         _check(lib().gblur_rowpass_split_device(self._h, _ptr(d_in), _ptr(d_inter), split_cols, split_stride_floats,
                                                 int(bool(apply_to_alpha)), _stream_ptr(stream)))
 
+    # -- fused exchange: panel buffers written by the peers' row passes --
+    def panel_alloc(self, apply_to_alpha: bool = False):
+        """(device pointer, floats) of a zeroed panel buffer for this column-band plan (owned by the plan)."""
+        ptr, n = C.c_void_p(), C.c_longlong()
+        _check(lib().gblur_band_panel_alloc(self._h, int(bool(apply_to_alpha)), C.byref(ptr), C.byref(n)))
+        return ptr.value, n.value
+
+    def rowpass_peer(self, d_in, peer_ptrs, row_offset: int, apply_to_alpha: bool = False, stream=None):
+        arr = (C.c_void_p * len(peer_ptrs))(*peer_ptrs)
+        _check(lib().gblur_rowpass_peer_device(self._h, _ptr(d_in), arr, len(peer_ptrs), row_offset,
+                                               int(bool(apply_to_alpha)), _stream_ptr(stream)))
+
+    def colpass_panel(self, d_panel: int, d_out, out_pitch_bytes: int, apply_to_alpha: bool = False, stream=None):
+        _check(lib().gblur_colpass_panel_device(self._h, C.c_void_p(d_panel), _ptr(d_out), out_pitch_bytes,
+                                                int(bool(apply_to_alpha)), _stream_ptr(stream)))
+
     def colpass(self, d_inter, inter_pitch_floats: int, d_out, out_pitch_bytes: int, apply_to_alpha: bool = False,
                 stream=None):
         _check(lib().gblur_colpass_device(self._h, _ptr(d_inter), inter_pitch_floats, _ptr(d_out), out_pitch_bytes,
@@ -244,6 +269,22 @@ class Plan:
         _check(lib().gblur_dump_intermediate(self._h, out.ctypes.data_as(C.POINTER(C.c_float)),
                                              int(bool(apply_to_alpha))))
         return out
+
+
+def ipc_export(d_ptr: int) -> bytes:
+    buf = C.create_string_buffer(64)
+    _check(lib().gblur_ipc_export(C.c_void_p(d_ptr), buf))
+    return buf.raw
+
+
+def ipc_open(handle: bytes) -> int:
+    out = C.c_void_p()
+    _check(lib().gblur_ipc_open(C.create_string_buffer(handle, 64), C.byref(out)))
+    return out.value
+
+
+def ipc_close(d_ptr: int) -> None:
+    _check(lib().gblur_ipc_close(C.c_void_p(d_ptr)))
 
 
 def gaussianblur(img: np.ndarray, sigma: float, apply_to_alpha: bool = False, device: int = 0) -> np.ndarray:

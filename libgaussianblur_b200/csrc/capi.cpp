@@ -71,6 +71,7 @@ struct gblur_plan {
   LineTables row, col;  // row pass (N = n_rowpass), column pass (N = n_colpass)
   float* d_inter = nullptr;
   size_t inter_floats = 0;
+  std::vector<void*> owned;    // device buffers handed out by gblur_band_panel_alloc
   uint8_t* d_stage = nullptr;  // device image for gblur_run_host
   size_t stage_bytes = 0;
   cudaStream_t stream = nullptr;
@@ -268,6 +269,7 @@ void gblur_plan_destroy(gblur_plan* p) {
   free_tables(p->col);
   if (p->d_inter) cudaFree(p->d_inter);
   if (p->d_stage) cudaFree(p->d_stage);
+  for (void* q : p->owned) cudaFree(q);
   if (p->stream) cudaStreamDestroy(p->stream);
   delete p;
 }
@@ -415,6 +417,142 @@ int gblur_colpass_device(gblur_plan* p, const float* d_inter, long long inter_pi
   DeviceGuard guard(p->device);
   return run_colpass(p, d_inter, inter_pitch_floats, d_out, out_pitch_bytes, 1, apply_to_alpha,
                      static_cast<cudaStream_t>(cuda_stream));
+}
+
+/* ---- band-sharded fused exchange: the row pass stores straight into the column owners' panel buffers ---- */
+
+namespace {
+// Panel geometry every rank derives from the (identical) column plan: slots per panel and the
+// bank-padding period. Cluster column plans read the panel through their loader: no padding holes.
+void panel_geometry(const gblur_plan* p, int* np, int* padq) {
+  const LinePlan& c = p->col.lp;
+  *np = c.cluster > 1 ? c.N : c.exch_elems;
+  *padq = c.cluster > 1 ? 0 : c.padq;
+}
+}  // namespace
+
+int gblur_plan_panel_geometry(const gblur_plan* p, int* np, int* padq) {
+  if (!p) return fail(GBLUR_E_INVALID, "null plan");
+  int a, b;
+  panel_geometry(p, &a, &b);
+  if (np) *np = a;
+  if (padq) *padq = b;
+  return GBLUR_OK;
+}
+
+int gblur_band_panel_alloc(gblur_plan* p, int apply_to_alpha, float** d_panel, long long* n_floats) {
+  if (!p || !d_panel) return fail(GBLUR_E_INVALID, "null argument");
+  DeviceGuard guard(p->device);
+  const int cp = processed_channels(p, apply_to_alpha);
+  int np, padq;
+  panel_geometry(p, &np, &padq);
+  const long long panels = ((long long)p->cols * cp + 31) / 32;
+  const long long floats = panels * np * 32;
+  void* q = nullptr;
+  CU(cudaMalloc(&q, (size_t)floats * sizeof(float)));
+  CU(cudaMemset(q, 0, (size_t)floats * sizeof(float)));  // padding holes and the zero tail stay zero for ever
+  CU(cudaDeviceSynchronize());
+  p->owned.push_back(q);
+  *d_panel = static_cast<float*>(q);
+  if (n_floats) *n_floats = floats;
+  return GBLUR_OK;
+}
+
+int gblur_ipc_export(const void* d_ptr, unsigned char handle[64]) {
+  if (!d_ptr || !handle) return fail(GBLUR_E_INVALID, "null argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "CUDA IPC handle size");
+  cudaIpcMemHandle_t h;
+  CU(cudaIpcGetMemHandle(&h, const_cast<void*>(d_ptr)));
+  std::memcpy(handle, &h, 64);
+  return GBLUR_OK;
+}
+
+int gblur_ipc_open(const unsigned char handle[64], void** d_ptr) {
+  if (!handle || !d_ptr) return fail(GBLUR_E_INVALID, "null argument");
+  cudaIpcMemHandle_t h;
+  std::memcpy(&h, handle, 64);
+  CU(cudaIpcOpenMemHandle(d_ptr, h, cudaIpcMemLazyEnablePeerAccess));
+  return GBLUR_OK;
+}
+
+int gblur_ipc_close(void* d_ptr) {
+  if (!d_ptr) return GBLUR_OK;
+  CU(cudaIpcCloseMemHandle(d_ptr));
+  return GBLUR_OK;
+}
+
+int gblur_rowpass_peer_device(gblur_plan* p, const uint8_t* d_in, float* const* peer_panels, int n_peers,
+                              int row_offset, int apply_to_alpha, void* cuda_stream) {
+  if (!p || !d_in || !peer_panels) return fail(GBLUR_E_INVALID, "null argument");
+  if (n_peers < 1 || n_peers > 8) return fail(GBLUR_E_INVALID, "n_peers outside [1, 8]");
+  const int cp = processed_channels(p, apply_to_alpha);
+  const long long w = (long long)p->full_cols * cp;
+  if (w % (32LL * n_peers)) return fail(GBLUR_E_INVALID, "cols*Cp must be a multiple of 32*n_peers for the fused exchange");
+  if (row_offset < 0 || row_offset + p->rows > p->full_rows) return fail(GBLUR_E_INVALID, "row band outside the image");
+  DeviceGuard guard(p->device);
+  int np, padq;
+  panel_geometry(p, &np, &padq);
+  BlockedLayout b;
+  b.enabled = 1;
+  b.L = 2 * p->col.lp.nseq;
+  b.np = np;
+  b.padq = padq;
+  b.rows_per_frame = p->full_rows;
+  b.frame_stride = 0;
+  RowLaunch a{};
+  a.in = d_in;
+  a.in_pitch = (long long)p->full_cols * p->channels;
+  a.C = p->channels;
+  a.Cp = cp;
+  a.T = p->full_cols;
+  a.pad = p->sz.pad;
+  a.rows_total = p->rows;
+  a.inter = nullptr;
+  a.inter_pitch = 0;
+  a.blk = b;
+  a.npeers = n_peers;
+  a.peer_panels = (int)(w / 32 / n_peers);
+  a.row_offset = row_offset;
+  for (int i = 0; i < n_peers; ++i) {
+    if (!peer_panels[i]) return fail(GBLUR_E_INVALID, "null peer panel pointer");
+    a.peer[i] = peer_panels[i];
+  }
+  CU(launch_rowpass(p->row.lp, a, p->num_sms, static_cast<cudaStream_t>(cuda_stream)));
+  return GBLUR_OK;
+}
+
+int gblur_colpass_panel_device(gblur_plan* p, const float* d_panel, uint8_t* d_out, long long out_pitch_bytes,
+                               int apply_to_alpha, void* cuda_stream) {
+  if (!p || !d_panel || !d_out) return fail(GBLUR_E_INVALID, "null argument");
+  if (out_pitch_bytes < (long long)p->cols * p->channels) return fail(GBLUR_E_INVALID, "output pitch too small");
+  DeviceGuard guard(p->device);
+  const int cp = processed_channels(p, apply_to_alpha);
+  int np, padq;
+  panel_geometry(p, &np, &padq);
+  BlockedLayout b;
+  b.enabled = 1;
+  b.L = 2 * p->col.lp.nseq;
+  b.np = np;
+  b.padq = padq;
+  b.rows_per_frame = p->full_rows;
+  b.frame_stride = (((long long)p->cols * cp + 31) / 32) * np * 32;
+  ColLaunch a{};
+  a.inter = d_panel;
+  a.pitch = 0;
+  a.frame_stride = b.frame_stride;
+  a.frames = 1;
+  a.T = p->full_rows;
+  a.pad = p->sz.pad;
+  a.W = p->cols * cp;
+  a.out = d_out;
+  a.out_pitch = out_pitch_bytes;
+  a.out_frame_stride = (long long)p->full_rows * out_pitch_bytes;
+  a.C = p->channels;
+  a.Cp = cp;
+  a.blk = b;
+  a.panel_in = p->col.lp.cluster > 1 ? 1 : 0;
+  CU(launch_colpass(p->col.lp, a, p->num_sms, static_cast<cudaStream_t>(cuda_stream)));
+  return GBLUR_OK;
 }
 
 int gblur_dump_intermediate(gblur_plan* p, float* host_out, int apply_to_alpha) {

@@ -70,13 +70,18 @@ cudaError_t launch_rowpass(const LinePlan& lp, const RowLaunch& a, int num_sms, 
   const bool blocked = a.blk.enabled != 0;
   P.split_cols = blocked ? 0 : a.split_cols;
   P.split_stride = a.split_stride;
+  P.npeers = blocked ? a.npeers : 0;
+  P.peer_panels = a.peer_panels;
+  P.row_offset = a.row_offset;
+  for (int i = 0; i < 8; ++i) P.peer[i] = a.peer[i];
+  if (P.npeers) P.inter = reinterpret_cast<float*>(kPeerFakeBase);
   P.rows_per_frame = blocked ? a.blk.rows_per_frame : 1;
   P.blk_L = a.blk.L;
   P.blk_np = a.blk.np;
   P.blk_padq = a.blk.padq;
   P.blk_frame_stride = a.blk.frame_stride;
   // uchar4/float4 (two sequences) or u16/float2 (one sequence, static shapes only) fast path
-  const bool rgba = P.split_cols == 0 && (lp.nseq == 2 || lp.static_id >= 0) && a.C == 4 && a.Cp == 4 && (a.in_pitch % 4) == 0 &&
+  const bool rgba = P.split_cols == 0 && P.npeers == 0 && (lp.nseq == 2 || lp.static_id >= 0) && a.C == 4 && a.Cp == 4 && (a.in_pitch % 4) == 0 &&
                     (reinterpret_cast<uintptr_t>(a.in) % 4) == 0 && (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0 &&
                     (blocked || (a.inter_pitch % 4) == 0);
   if (lp.cluster > 1) return launch_row_cluster(lp, P, blocked, stream);
@@ -110,10 +115,11 @@ cudaError_t launch_colpass(const LinePlan& lp, const ColLaunch& a, int num_sms, 
   const bool blocked = a.blk.enabled != 0;
   P.panel_stride = (long long)a.blk.np * 32;
   P.np = a.blk.np;
+  P.panel_in = a.panel_in;
   if (blocked) P.frame_stride = a.blk.frame_stride;
   const bool packed = a.C == a.Cp && (a.W % L) == 0 && (a.out_pitch % L) == 0 && (a.out_frame_stride % L) == 0 &&
                       (reinterpret_cast<uintptr_t>(a.out) % L) == 0;
-  if (lp.cluster > 1) return blocked ? cudaErrorInvalidValue : launch_col_cluster(lp, P, packed, stream);
+  if (lp.cluster > 1) return (blocked && !a.panel_in) ? cudaErrorInvalidValue : launch_col_cluster(lp, P, packed, stream);
   switch (lp.static_id) {
 #define X(ID, NSEQ, R0, R1, R2, R3, NT, MINB) \
   case ID:                                    \

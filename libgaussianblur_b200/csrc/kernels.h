@@ -49,6 +49,10 @@ struct RowLaunch {
   BlockedLayout blk;
   int split_cols = 0;          // row-major only: see RowParams::split_cols
   long long split_stride = 0;
+  float* peer[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  int npeers = 0;              // panel layout only: see RowParams::peer
+  int peer_panels = 0;
+  int row_offset = 0;
 };
 
 struct ColLaunch {
@@ -63,6 +67,7 @@ struct ColLaunch {
   long long out_frame_stride;
   int C, Cp;
   BlockedLayout blk;
+  int panel_in = 0;  // the column pass of a cluster plan reads the panel layout through its loader
 };
 
 // Returns the static shape id for (N, nseq) or -1; fills radices when found.

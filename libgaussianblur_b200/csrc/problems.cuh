@@ -51,6 +51,12 @@ struct RowParams {
   // inter + h * split_stride with row pitch split_cols * Cp (send buffer of the band-sharded all-to-all)
   int split_cols;
   long long split_stride;
+  // band-sharded fused exchange (BLOCKED problems): panel h*peer_panels .. of every row goes to the panel
+  // buffer of rank h, peer[h] (NVLink peer memory; peer[own rank] is local). npeers == 0: off, `inter` is used.
+  float* peer[8];
+  int npeers;
+  int peer_panels;
+  int row_offset;  // first image row of this band (slot = pad + row_offset + r)
   // panel intermediate (BLOCKED problems): [frame][panel = w/32][slot physc(n)][32 floats] with
   // w = x*Cp + ch the float column: every row writes whole 128-byte lines, and a column unit
   // (L adjacent float columns) finds its padded line at a fixed 128-byte stride; see BlockedDst
@@ -65,6 +71,8 @@ struct RowParams {
 // the reflect_101 border, the mirrored slots (the row pass writes the column pass's padding, so
 // the column pass needs no index arithmetic at all; the zero tail is never written).
 constexpr int kPanelFloats = 32;  // one 128-byte line per (panel, slot)
+// peer mode: RowParams::inter is this fake base, so Storer::q[] carries a non-null offset into every rank's panel buffer
+constexpr unsigned long long kPeerFakeBase = 4096;
 
 struct BlockedDst {
   float* base;      // inter + frame offset + physc(pad + r) * 32
@@ -74,8 +82,8 @@ struct BlockedDst {
 
 __device__ __forceinline__ BlockedDst make_blocked_dst(const RowParams& P, long long r_global) {
   BlockedDst d;
-  const long long f = r_global / P.rows_per_frame;
-  const int r = (int)(r_global - f * P.rows_per_frame);
+  const long long f = (r_global + P.row_offset) / P.rows_per_frame;
+  const int r = (int)(r_global + P.row_offset - f * P.rows_per_frame);
   const int Tc = P.rows_per_frame, pad = P.pad, L = kPanelFloats;
   const int p1 = phys(pad + r, P.blk_padq);
   d.base = P.inter + f * P.blk_frame_stride + (long long)p1 * L;
@@ -115,6 +123,8 @@ struct RowProblemGeneric {
     int Cp, pad, T;
     int split_cols;
     long long split_stride;
+    float* const* peers;  // BLOCKED: panel buffers of the ranks (nullptr: q[k] points into the local buffer)
+    int peer_panels;
     __device__ __forceinline__ void put(int k, int x, float v) const {
       if (!q[k]) return;
       if constexpr (!BLOCKED) {
@@ -126,7 +136,14 @@ struct RowProblemGeneric {
         }
       } else {
         const int w = x * Cp + ch[k];
-        float* d = q[k] + (long long)(w >> 5) * gstride + (w & 31);
+        int panel = w >> 5;
+        float* d = q[k];
+        if (peers) {  // q[k] holds the offset inside a panel buffer; pick the owner of this panel
+          const int h = panel / peer_panels;
+          panel -= h * peer_panels;
+          d = peers[h] + ((reinterpret_cast<uintptr_t>(q[k]) - kPeerFakeBase) >> 2);
+        }
+        d += (long long)panel * gstride + (w & 31);
         *d = v;
         if (dl[k]) d[dl[k]] = v;
         if (dr[k]) d[dr[k]] = v;
@@ -150,6 +167,8 @@ struct RowProblemGeneric {
     st.gstride = 0;
     st.split_cols = P.split_cols;
     st.split_stride = P.split_stride;
+    st.peers = (BLOCKED && P.npeers) ? P.peer : nullptr;
+    st.peer_panels = P.peer_panels;
 #pragma unroll
     for (int k = 0; k < L; ++k) {
       long long sig = (long long)unit * L + k;
@@ -300,6 +319,7 @@ struct ColParams {
   // line is np pieces of L floats at a 128-byte stride, gathered with cp.async into the exchange buffer
   long long panel_stride;  // floats between consecutive panels = np * 32
   int np;                  // slots per unit
+  int panel_in;            // non-BULK problems: inter is the panel layout too (cluster column pass)
 };
 
 // PACKED: Cp == C and every row/pitch is aligned so that the 2*NSEQ bytes of a unit are one
@@ -378,6 +398,12 @@ struct ColProblem {
     ld.T = st.T = P.T;
     ld.pitch = P.pitch;
     ld.col = P.inter + (long long)f * P.frame_stride + w0;
+    if (!BULK && P.panel_in) {  // slot n of the padded line sits at n * 128 bytes; borders are already mirrored
+      ld.pad = 0;
+      ld.T = P.np;
+      ld.pitch = kPanelFloats;
+      ld.col = bulk_src(P, unit);
+    }
     st.pitch = P.out_pitch;
     st.base = P.out + (long long)f * P.out_frame_stride + (PACKED ? w0 : 0);
     st.next_src = nullptr;

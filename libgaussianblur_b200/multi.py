@@ -76,6 +76,9 @@ class BandShardedBlur:
         self.col_ranges = shard_ranges(cols, self.world)
         self.rowpass, self.colpass = rowpass, colpass
         self.rowpass_split = None  # optional: band -> [world, band_rows, cols/world, Cp] written in place
+        self.profile = False       # fused path: record CUDA events around fence / row pass / fence / column pass
+        self.marks = []
+        self.fused_run = None      # optional: band -> column band, exchange fused into the row pass (peer stores)
         self.exchanged_bytes = 0  # bytes this rank sent to OTHER ranks in the last run
 
     @property
@@ -87,6 +90,9 @@ class BandShardedBlur:
         return self.col_ranges[self.rank]
 
     def run(self, band: torch.Tensor, gather_rows: bool = False) -> torch.Tensor:
+        if self.fused_run is not None:
+            out_cols = self.fused_run(band)
+            return self._gather_rows(out_cols) if gather_rows else out_cols
         r0, r1 = self.my_rows
         c0, c1 = self.my_cols
         Cp, C = self.Cp, self.C
@@ -110,8 +116,12 @@ class BandShardedBlur:
             alpha_src = torch.empty((self.rows, c1 - c0), dtype=band.dtype, device=band.device)
             exchange(a_send, [alpha_src[a:b] for a, b in self.row_ranges], self.group)
         out_cols = self.colpass(recv_buf.view(self.rows, (c1 - c0) * Cp), alpha_src)
-        if not gather_rows:
-            return out_cols
+        return self._gather_rows(out_cols) if gather_rows else out_cols
+
+    def _gather_rows(self, out_cols: torch.Tensor) -> torch.Tensor:
+        """Second, 4x smaller (u8) all-to-all: from column-band ownership back to row bands."""
+        r0, r1 = self.my_rows
+        C = self.C
         back_send = [out_cols[a:b].contiguous() for a, b in self.row_ranges]
         parts = [torch.empty((r1 - r0, b - a, C), dtype=out_cols.dtype, device=out_cols.device)
                  for a, b in self.col_ranges]
@@ -121,7 +131,7 @@ class BandShardedBlur:
     # ---- product binding: CUDA plans through the C ABI ----
     @classmethod
     def cuda(cls, rows: int, cols: int, channels: int, sigma: float, apply_to_alpha: bool = False, device: int = 0,
-             group=None) -> "BandShardedBlur":
+             group=None, fused: bool = True) -> "BandShardedBlur":
         import libgaussianblur_b200 as gb
 
         world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -160,9 +170,83 @@ class BandShardedBlur:
         self = cls(rows, cols, channels, cp, rowpass, colpass, group)
         self.rowpass_split = rowpass_split
         self.plans = (p_row, p_col)
+        self._opened = []
+        if fused and (cols * cp) % (32 * world) == 0 and world <= 8:
+            # Fused exchange: every rank's row pass stores its lines straight into the panel buffer of the rank
+            # that owns those columns (CUDA IPC mapping of the peers' buffers, NVLink stores). Two tiny
+            # all-reduces on the compute stream order the passes across ranks: nobody overwrites a panel that
+            # its owner is still reading, and nobody reads a panel before every row pass has finished.
+            panel_ptr, _ = p_col.panel_alloc(apply_to_alpha)
+            peers = [panel_ptr]
+            if world > 1:
+                handles = [None] * world
+                dist.all_gather_object(handles, gb.ipc_export(panel_ptr), group=group)
+                peers = []
+                for h, hd in enumerate(handles):
+                    if h == rank:
+                        peers.append(panel_ptr)
+                    else:
+                        q = gb.ipc_open(hd)
+                        self._opened.append(q)
+                        peers.append(q)
+            token = torch.zeros(1, dtype=torch.float32, device=dev)
+
+            def fence():
+                if world > 1:
+                    dist.all_reduce(token, group=group)
+
+            def mark():
+                if self.profile:
+                    e = torch.cuda.Event(enable_timing=True)
+                    e.record()
+                    self.marks.append(e)
+
+            def fused_run(band: torch.Tensor) -> torch.Tensor:
+                self.marks = []
+                mark()
+                fence()  # every rank has finished the previous column pass
+                mark()
+                p_row.rowpass_peer(band, peers, r0, apply_to_alpha)
+                mark()
+                fence()  # every rank's row pass (and its peer stores) has completed
+                mark()
+                out = torch.empty((rows, c1 - c0, channels), dtype=torch.uint8, device=dev)
+                if cp < channels:
+                    out[..., channels - 1] = self._exchange_alpha(band)
+                p_col.colpass_panel(panel_ptr, out, (c1 - c0) * channels, apply_to_alpha)
+                mark()
+                return out
+
+            self.fused_run = fused_run
+            self.exchange_kind = "fused peer stores (NVLink), no collective on the data path"
+        else:
+            self.exchange_kind = "NCCL all-to-all"
         return self
 
+    def phase_ms(self):
+        """After a profiled fused run (and a synchronize): ms spent in fence, row pass, fence, column pass."""
+        m = self.marks
+        names = ["fence_before", "row_pass_peer_stores", "fence_after", "col_pass"]
+        return {n: m[i].elapsed_time(m[i + 1]) for i, n in enumerate(names)} if len(m) == 5 else {}
+
+    def _exchange_alpha(self, band: torch.Tensor) -> torch.Tensor:
+        """The un-blurred alpha bytes of all rows for my column band (u8 all-to-all)."""
+        c0, c1 = self.my_cols
+        a_send = [band[:, a:b, self.C - 1].contiguous() for a, b in self.col_ranges]
+        alpha_src = torch.empty((self.rows, c1 - c0), dtype=band.dtype, device=band.device)
+        exchange(a_send, [alpha_src[a:b] for a, b in self.row_ranges], self.group)
+        return alpha_src
+
     def close(self):
+        if getattr(self, "_opened", None):
+            import libgaussianblur_b200 as gb
+
+            torch.cuda.synchronize()
+            if dist.is_initialized():
+                dist.barrier(self.group)
+            for q in self._opened:
+                gb.ipc_close(q)
+            self._opened = []
         for p in getattr(self, "plans", ()):
             p.close()
 

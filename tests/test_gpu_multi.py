@@ -17,16 +17,17 @@ from oracle import ref_lib
 rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local)
 dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-for ch, alpha in ((1, False), (3, False), (4, False)):
+for ch, alpha, fused in ((1, False, True), (3, False, True), (4, False, True), (4, True, True), (1, False, False), (3, False, False), (4, False, False)):
     rows, cols, sigma = 250, 384, 6.0
     img = go.synth_u8((rows, cols, ch) if ch > 1 else (rows, cols), 5 + ch)
     want = (ref_lib.gaussianblur(img, sigma, alpha) if ch > 1 else ref_lib.blur_plane_u8(img, sigma)) if ref_lib.available() else go.gaussianblur(img, sigma, alpha)
-    b = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, device=local)
+    b = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, device=local, fused=fused)
+    assert (b.fused_run is not None) == fused, b.exchange_kind
     r0, r1 = b.my_rows
     out = b.run(torch.from_numpy(img.reshape(rows, cols, ch)[r0:r1].copy()).cuda(), gather_rows=True)
     torch.cuda.synchronize()
     d = np.abs(out.cpu().numpy().astype(int) - want.reshape(rows, cols, ch)[r0:r1].astype(int)).max()
-    assert d <= 1, (ch, alpha, d)
+    assert d <= 1, (ch, alpha, fused, d)
     b.close()
 fs = FrameShardedBlur(6, 135, 240, 3, 5.0, device=local, chunk_frames=2)
 f0, f1 = fs.frames

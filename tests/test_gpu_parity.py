@@ -263,10 +263,12 @@ def test_band_sharded_binding_single_rank(gb, refcheck):
 
     from libgaussianblur_b200.multi import BandShardedBlur
 
-    for ch, alpha in ((1, False), (3, False), (4, False), (4, True)):
+    for ch, alpha, fused in ((1, False, True), (3, False, True), (4, False, True), (4, True, True), (3, False, False),
+                             (4, False, False)):
         rows, cols, sigma = 96, 160, 4.0
         img = go.synth_u8((rows, cols, ch) if ch > 1 else (rows, cols), 31 + ch)
-        b = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha)
+        b = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, fused=fused)
+        assert (b.fused_run is not None) == fused
         out = b.run(torch.from_numpy(img).cuda().view(rows, cols, ch))
         torch.cuda.synchronize()
         b.close()
