@@ -238,7 +238,8 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier):
     h_pin.copy_(band.cpu())
     stream = torch.cuda.current_stream()
     phases = {}
-    if world == 1:
+    single = world == 1 and not args.force_band
+    if single:
         plan = gb.Plan(rows, cols, ch, sigma, device=local)
         d_out = torch.empty_like(band)
         step = lambda: plan.run_device(band, d_out, alpha)
@@ -270,7 +271,7 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier):
     barrier()
     ms = e0.elapsed_time(e1)
     launches = gb.launch_count() - l0
-    if world == 1:
+    if single:
         for name, st in (("row_pass", 1), ("col_pass", 2)):
             k0, k1 = _events(torch)
             torch.cuda.synchronize()
@@ -302,7 +303,7 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier):
                 alg_bytes_step=npx_step * 10 * ch, h2d=h2d, d2h=d2h,
                 config={"workload": wl, "rows": rows, "cols": cols, "channels": ch, "sigma": sigma,
                         "apply_to_alpha": alpha,
-                        "parallelism": "single GPU" if world == 1 else f"row bands x{world} + {args.exchange} exchange + column bands",
+                        "parallelism": "single GPU" if single else f"row bands x{world} + {args.exchange} exchange + column bands",
                         "l2": "inputs larger than L2"},
                 phases_ms=phases)
 
@@ -344,6 +345,7 @@ def main():
     ap.add_argument("--workload", default="8k_rgba_sigma20", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--chunk-frames", type=int, default=16, help="frames per launch in the video workload")
+    ap.add_argument("--force-band", action="store_true", help="band workloads at 1 GPU: run the band-sharded path anyway")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
                     help="band workloads: row pass stores into peer memory (fused) or NCCL all-to-all")
     args = ap.parse_args()

@@ -1,6 +1,7 @@
 // capi.cpp — implementation of include/gblur_capi.h: plans, workspaces and the pass drivers.
 // Host semantics follow the reference (see hostsem.hpp / planner.hpp for file:line citations);
 // all pixel work happens in the sm_100a kernels (kernels.h). No CPU fallback exists.
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <cstdarg>
@@ -72,6 +73,10 @@ struct gblur_plan {
   float* d_inter = nullptr;
   size_t inter_floats = 0;
   std::vector<void*> owned;    // device buffers handed out by gblur_band_panel_alloc
+  CUtensorMap tmap;            // TMA view of the panel intermediate for the column pass
+  const float* tmap_base = nullptr;
+  int tmap_np = 0, tmap_L = 0, tmap_rows = 0;
+  long long tmap_panels = 0;
   uint8_t* d_stage = nullptr;  // device image for gblur_run_host
   size_t stage_bytes = 0;
   cudaStream_t stream = nullptr;
@@ -207,6 +212,24 @@ int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pi
   return GBLUR_OK;
 }
 
+// (Re)build the cached tensor map when the buffer, the layout or the extent changed.
+bool panel_tensor_map(gblur_plan* p, const float* base, const BlockedLayout& b, long long panels) {
+  if (p->tmap_rows && p->tmap_base == base && p->tmap_np == b.np && p->tmap_L == b.L && p->tmap_panels == panels)
+    return true;
+  int rows = 0;
+  if (!make_panel_tensor_map(&p->tmap, base, b.np, panels, b.L, &rows)) {
+    p->tmap_rows = 0;
+    p->tmap_base = nullptr;
+    return false;
+  }
+  p->tmap_base = base;
+  p->tmap_np = b.np;
+  p->tmap_L = b.L;
+  p->tmap_panels = panels;
+  p->tmap_rows = rows;
+  return true;
+}
+
 int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d_out, long long out_pitch, int frames,
                 int alpha, cudaStream_t s, const BlockedLayout* blk = nullptr) {
   const int cp = processed_channels(p, alpha);
@@ -223,7 +246,14 @@ int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d
   a.out_frame_stride = (long long)p->full_rows * out_pitch;
   a.C = p->channels;
   a.Cp = cp;
-  if (blk) a.blk = *blk;
+  if (blk) {
+    a.blk = *blk;
+    const long long panels = ((long long)p->cols * cp + 31) / 32 * frames;
+    if (p->col.lp.cluster == 1 && panel_tensor_map(p, d_inter, *blk, panels)) {
+      a.tmap = &p->tmap;
+      a.tma_rows = p->tmap_rows;
+    }
+  }
   CU(launch_colpass(p->col.lp, a, p->num_sms, s));
   return GBLUR_OK;
 }
@@ -551,6 +581,10 @@ int gblur_colpass_panel_device(gblur_plan* p, const float* d_panel, uint8_t* d_o
   a.Cp = cp;
   a.blk = b;
   a.panel_in = p->col.lp.cluster > 1 ? 1 : 0;
+  if (!a.panel_in && panel_tensor_map(p, d_panel, b, b.frame_stride / ((long long)np * 32))) {
+    a.tmap = &p->tmap;
+    a.tma_rows = p->tmap_rows;
+  }
   CU(launch_colpass(p->col.lp, a, p->num_sms, static_cast<cudaStream_t>(cuda_stream)));
   return GBLUR_OK;
 }

@@ -54,6 +54,38 @@ int find_static_shape(int N, int nseq, int* radices, int* nthreads) {
 
 cudaError_t kernels_init(int) { return cudaSuccess; }
 
+bool make_panel_tensor_map(CUtensorMap* out, const float* base, int np, long long panels, int L, int* box_rows) {
+  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+  static EncodeFn encode = [] {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      fn = nullptr;
+    return reinterpret_cast<EncodeFn>(fn);
+  }();
+  if (!encode || getenv("GBLUR_NO_TMA")) return false;
+  int rows = 0;
+  for (int r = 256; r >= 32; --r)
+    if (np % r == 0) {
+      rows = r;
+      break;
+    }
+  if (!rows || panels < 1) return false;
+  const cuuint64_t dims[3] = {32, (cuuint64_t)np, (cuuint64_t)panels};
+  const cuuint64_t strides[2] = {128, (cuuint64_t)np * 128};  // bytes, dims 1 and 2
+  const cuuint32_t box[3] = {(cuuint32_t)L, (cuuint32_t)rows, 1};
+  const cuuint32_t estr[3] = {1, 1, 1};
+  const CUresult r = encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(base), dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return false;
+  *box_rows = rows;
+  return true;
+}
+
 cudaError_t launch_rowpass(const LinePlan& lp, const RowLaunch& a, int num_sms, cudaStream_t stream) {
   RowParams P{};
   P.in = a.in;
@@ -116,6 +148,13 @@ cudaError_t launch_colpass(const LinePlan& lp, const ColLaunch& a, int num_sms, 
   P.panel_stride = (long long)a.blk.np * 32;
   P.np = a.blk.np;
   P.panel_in = a.panel_in;
+  P.tma_rows = 0;
+  P.panels_per_frame = (a.W + 31) / 32;
+  const bool tma = blocked && a.tmap && a.tma_rows > 0;
+  if (tma) {
+    P.tmap = *a.tmap;
+    P.tma_rows = a.tma_rows;
+  }
   if (blocked) P.frame_stride = a.blk.frame_stride;
   const bool packed = a.C == a.Cp && (a.W % L) == 0 && (a.out_pitch % L) == 0 && (a.out_frame_stride % L) == 0 &&
                       (reinterpret_cast<uintptr_t>(a.out) % L) == 0;
@@ -123,7 +162,7 @@ cudaError_t launch_colpass(const LinePlan& lp, const ColLaunch& a, int num_sms, 
   switch (lp.static_id) {
 #define X(ID, NSEQ, R0, R1, R2, R3, NT, MINB) \
   case ID:                                    \
-    return launch_col_static<ID>(lp, P, packed, blocked, num_sms, stream);
+    return launch_col_static<ID>(lp, P, packed, blocked ? (tma ? 2 : 1) : 0, num_sms, stream);
     GBLUR_STATIC_SHAPES(X)
 #undef X
     default:

@@ -1,5 +1,6 @@
 // kernels.h — host-visible launch interface of the sm_100a line-convolution kernels.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 
 #include <cstddef>
@@ -68,10 +69,16 @@ struct ColLaunch {
   int C, Cp;
   BlockedLayout blk;
   int panel_in = 0;  // the column pass of a cluster plan reads the panel layout through its loader
+  const CUtensorMap* tmap = nullptr;  // host copy of the tensor map over the panel intermediate (TMA gather), or null
+  int tma_rows = 0;
 };
 
 // Returns the static shape id for (N, nseq) or -1; fills radices when found.
 int find_static_shape(int N, int nseq, int* radices /*[4]*/, int* nthreads);
+
+// Tensor map over a panel intermediate for column units of L floats: dims {32, np, panels}, box {L, rows, 1}.
+// Returns false when the driver entry point is missing or np has no usable divisor (then cp.async is used).
+bool make_panel_tensor_map(CUtensorMap* out, const float* base, int np, long long panels, int L, int* box_rows);
 
 // One-time per-process kernel attribute setup (max dynamic smem). Returns cudaSuccess or error.
 cudaError_t kernels_init(int device);

@@ -55,14 +55,24 @@ __global__ void __launch_bounds__(512, 1)
 template <int NSEQ, class SS, int NT, int MAXREG, class Problem, class Params>
 __global__ void __maxnreg__(MAXREG)
     line_kernel_static(const __grid_constant__ LineShape sh, const __grid_constant__ Params P) {
-  extern __shared__ float4 smem_raw[];
+  extern __shared__ __align__(128) float4 smem_raw[];  // TMA destinations need 128-byte alignment
   using Elem = typename SmemElem<NSEQ>::type;
   auto* sm = reinterpret_cast<Elem*>(smem_raw);
   float2* twsm = reinterpret_cast<float2*>(sm + SS::EXCH);
   float* kpsm = reinterpret_cast<float*>(twsm + SS::TWTOT);
   for (int i = threadIdx.x; i < SS::TWTOT; i += NT) twsm[i] = __ldg(sh.tw[0] + i);
   for (int i = threadIdx.x; i < SS::N; i += NT) kpsm[i] = __ldg(sh.kperm + i);
-  if constexpr (Problem::kBulkIn) {
+  // the mbarrier lives behind the tables in dynamic shared memory (a static __shared__ would shift the base)
+  uint64_t& tma_bar = *reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(kpsm + SS::N) + ((SS::N & 1) ? 4 : 0));
+  uint32_t tma_parity = 0;
+  if constexpr (Problem::kTmaIn) {
+    static_assert(SS::M0 == NT, "TMA prefetch needs one last-stage butterfly per thread");
+    if (threadIdx.x == 0) {
+      mbar_init(&tma_bar, 1);
+      fence_proxy_async();
+      if ((int)blockIdx.x < P.nunits) Problem::tma_request(P, (int)blockIdx.x, sm, &tma_bar);
+    }
+  } else if constexpr (Problem::kBulkIn) {
     if ((int)blockIdx.x < P.nunits) gather_stage_unit<NSEQ, Problem>(P, (int)blockIdx.x, sm, (int)threadIdx.x, NT);
   }
   __syncthreads();
@@ -70,7 +80,14 @@ __global__ void __maxnreg__(MAXREG)
     typename Problem::Loader ld;
     typename Problem::Storer st;
     Problem::make(P, unit, ld, st);
-    if constexpr (Problem::kBulkIn) gather_wait();
+    if constexpr (Problem::kTmaIn) {
+      st.smbase = sm;
+      st.bar = &tma_bar;
+      mbar_wait(&tma_bar, tma_parity);  // this unit's tiles have landed
+      tma_parity ^= 1u;
+    } else if constexpr (Problem::kBulkIn) {
+      gather_wait();
+    }
     run_line_static<NSEQ, SS, Problem::kBulkIn>(twsm, kpsm, ld, st, sm, (int)threadIdx.x, NT);
   }
 }
@@ -125,9 +142,9 @@ cudaError_t launch_line(const LinePlan& lp, const Params& P, int nthreads, int n
 // rgba: uchar4/float4 fast path; blocked: blocked intermediate; packed: aligned u16/u32 output stores
 template <int ID>
 cudaError_t launch_row_static(const LinePlan&, const RowParams&, bool rgba, bool blocked, int num_sms, cudaStream_t);
+// input: 0 = row-major loader, 1 = panel layout gathered with cp.async, 2 = panel layout through TMA tiles
 template <int ID>
-cudaError_t launch_col_static(const LinePlan&, const ColParams&, bool packed, bool blocked, int num_sms,
-                              cudaStream_t);
+cudaError_t launch_col_static(const LinePlan&, const ColParams&, bool packed, int input, int num_sms, cudaStream_t);
 cudaError_t launch_row_generic(const LinePlan&, const RowParams&, bool rgba, bool blocked, int num_sms, cudaStream_t);
 cudaError_t launch_col_generic(const LinePlan&, const ColParams&, bool packed, bool blocked, int num_sms,
                                cudaStream_t);

@@ -9,6 +9,8 @@
 //              interleave_channels' uint8_t(v + 0.5f) (helpers.hpp:251-252,270) with a clamp.
 // All citations are under /root/reference/.
 #pragma once
+#include <cuda.h>
+
 #include <cstdint>
 
 #include "async_copy.cuh"
@@ -99,6 +101,7 @@ template <int NSEQ, bool BLOCKED = false>
 struct RowProblemGeneric {
   static constexpr int L = 2 * NSEQ;
   static constexpr bool kBulkIn = false;
+  static constexpr bool kTmaIn = false;
   struct Loader {
     const uint8_t* p[L];
     int C, pad, T;
@@ -117,6 +120,7 @@ struct RowProblemGeneric {
   };
   struct Storer {
     static constexpr bool kPrefetch = false;
+    static constexpr bool kTmaNext = false;
     float* q[L];  // nullptr: line does not exist (tail unit); BLOCKED: BlockedDst::base
     long long dl[L], dr[L], gstride;
     int ch[L];
@@ -125,7 +129,8 @@ struct RowProblemGeneric {
     long long split_stride;
     float* const* peers;  // BLOCKED: panel buffers of the ranks (nullptr: q[k] points into the local buffer)
     int peer_panels;
-    __device__ __forceinline__ void put(int k, int x, float v) const {
+    unsigned peer_magic;  // floor(2^32 / peer_panels) + 1: panel / peer_panels == umulhi(panel, magic) for panel < 2^16
+    __device__ __forceinline__ void put(int k, int x, int w0, float v) const {
       if (!q[k]) return;
       if constexpr (!BLOCKED) {
         if (split_cols) {
@@ -135,15 +140,15 @@ struct RowProblemGeneric {
           q[k][(long long)x * Cp] = v;
         }
       } else {
-        const int w = x * Cp + ch[k];
+        const int w = w0 + ch[k];
         int panel = w >> 5;
         float* d = q[k];
         if (peers) {  // q[k] holds the offset inside a panel buffer; pick the owner of this panel
-          const int h = panel / peer_panels;
+          const int h = peer_panels == 1 ? panel : (int)__umulhi((unsigned)panel, peer_magic);
           panel -= h * peer_panels;
           d = peers[h] + ((reinterpret_cast<uintptr_t>(q[k]) - kPeerFakeBase) >> 2);
         }
-        d += (long long)panel * gstride + (w & 31);
+        d += (long long)panel * (int)gstride + (w & 31);
         *d = v;
         if (dl[k]) d[dl[k]] = v;
         if (dr[k]) d[dr[k]] = v;
@@ -152,10 +157,11 @@ struct RowProblemGeneric {
     __device__ __forceinline__ void store(int n, const Pt<NSEQ>& v) const {
       const int x = n - pad;
       if (x < 0 || x >= T) return;
+      const int w0 = x * Cp;
 #pragma unroll
       for (int s = 0; s < NSEQ; ++s) {
-        put(2 * s, x, v.v[s].x);
-        put(2 * s + 1, x, v.v[s].y);
+        put(2 * s, x, w0, v.v[s].x);
+        put(2 * s + 1, x, w0, v.v[s].y);
       }
     }
   };
@@ -169,6 +175,7 @@ struct RowProblemGeneric {
     st.split_stride = P.split_stride;
     st.peers = (BLOCKED && P.npeers) ? P.peer : nullptr;
     st.peer_panels = P.peer_panels;
+    st.peer_magic = P.peer_panels > 0 ? (unsigned)(0x100000000ULL / (unsigned)P.peer_panels) + 1u : 0u;
 #pragma unroll
     for (int k = 0; k < L; ++k) {
       long long sig = (long long)unit * L + k;
@@ -197,6 +204,7 @@ struct RowProblemGeneric {
 template <bool BLOCKED = false>
 struct RowProblemRGBA {
   static constexpr bool kBulkIn = false;
+  static constexpr bool kTmaIn = false;
   struct Loader {
     const uint32_t* row;
     int pad, T;
@@ -212,6 +220,7 @@ struct RowProblemRGBA {
   };
   struct Storer {
     static constexpr bool kPrefetch = false;
+    static constexpr bool kTmaNext = false;
     float* row;  // row-major: start of the row; blocked: BlockedDst::base
     long long dl, dr, gstride;
     int pad, T;
@@ -252,6 +261,7 @@ struct RowProblemRGBA {
 template <bool BLOCKED = false>
 struct RowProblemRGBA1 {
   static constexpr bool kBulkIn = false;
+  static constexpr bool kTmaIn = false;
   struct Loader {
     const uint16_t* row;  // already offset by the pair
     int pad, T;
@@ -265,6 +275,7 @@ struct RowProblemRGBA1 {
   };
   struct Storer {
     static constexpr bool kPrefetch = false;
+    static constexpr bool kTmaNext = false;
     float* row;
     long long dl, dr, gstride;
     int pad, T;
@@ -320,16 +331,35 @@ struct ColParams {
   long long panel_stride;  // floats between consecutive panels = np * 32
   int np;                  // slots per unit
   int panel_in;            // non-BULK problems: inter is the panel layout too (cluster column pass)
+  // TMA problems: tensor map over the panel intermediate, dims {32 floats, np slots, panels*frames}, box
+  // {L floats, tma_rows slots, 1}: one unit = np / tma_rows strided tiles of 4*L-byte rows
+  CUtensorMap tmap;
+  int tma_rows;
+  int panels_per_frame;
 };
 
 // PACKED: Cp == C and every row/pitch is aligned so that the 2*NSEQ bytes of a unit are one
 // aligned 16/32-bit store; otherwise bytes are scattered individually.
 // BULK: the unit is gathered with cp.async from the panel intermediate (padding and mirrored
 // border rows were already written by the row pass), so the Loader is never called.
-template <int NSEQ, bool PACKED, bool BULK = false>
+// TMA (with BULK): the gather is done by the TMA unit instead — strided tiles through a tensor map —
+// and the next unit's tiles are requested as soon as the last inverse stage has read the buffer.
+template <int NSEQ, bool PACKED, bool BULK = false, bool TMA = false>
 struct ColProblem {
   static constexpr int L = 2 * NSEQ;
   static constexpr bool kBulkIn = BULK;
+  static constexpr bool kTmaIn = BULK && TMA;
+  // request every tile of `unit` (one elected thread); completion is counted in bytes on `bar`
+  static __device__ __forceinline__ void tma_request(const ColParams& P, int unit, void* smbase, uint64_t* bar) {
+    const int f = unit / P.groups_per_frame;
+    const int g = unit - f * P.groups_per_frame;
+    const int w0 = g * L;
+    const int panel = f * P.panels_per_frame + (w0 >> 5);
+    fence_proxy_async();
+    mbar_expect_tx(bar, (uint32_t)P.np * (uint32_t)(4 * L));
+    char* dst = static_cast<char*>(smbase);
+    for (int r = 0; r < P.np; r += P.tma_rows) tma_load_3d(dst + (size_t)r * (4 * L), &P.tmap, w0 & 31, r, panel, bar);
+  }
   static __device__ __forceinline__ const float* bulk_src(const ColParams& P, int unit) {
     const int f = unit / P.groups_per_frame;
     const int g = unit - f * P.groups_per_frame;
@@ -359,7 +389,17 @@ struct ColProblem {
     }
   };
   struct Storer {
-    static constexpr bool kPrefetch = BULK;
+    static constexpr bool kPrefetch = BULK && !TMA;
+    static constexpr bool kTmaNext = BULK && TMA;
+    const ColParams* params;  // TMA: request the next unit's tiles from here
+    void* smbase;
+    uint64_t* bar;
+    int next_unit;            // -1: none
+    // called by every thread once the last inverse stage has read its slots
+    __device__ __forceinline__ void after_reads() const {
+      __syncthreads();
+      if (threadIdx.x == 0 && next_unit >= 0) tma_request(*params, next_unit, smbase, bar);
+    }
     uint8_t* base;  // out + frame*out_frame_stride (+ w0 when PACKED)
     long long pitch;
     int off[L];     // byte offset of each line inside a row, -1 = not stored (generic path)
@@ -407,9 +447,16 @@ struct ColProblem {
     st.pitch = P.out_pitch;
     st.base = P.out + (long long)f * P.out_frame_stride + (PACKED ? w0 : 0);
     st.next_src = nullptr;
+    st.params = &P;
+    st.smbase = nullptr;
+    st.bar = nullptr;
+    st.next_unit = -1;
     if constexpr (BULK) {
       const int next = unit + (int)gridDim.x;
-      if (next < P.nunits) st.next_src = bulk_src(P, next);
+      if (next < P.nunits) {
+        st.next_src = bulk_src(P, next);
+        st.next_unit = next;
+      }
     }
 #pragma unroll
     for (int k = 0; k < L; ++k) {

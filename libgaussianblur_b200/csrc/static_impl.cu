@@ -48,12 +48,21 @@ cudaError_t launch_row_static(const LinePlan& lp, const RowParams& P, bool rgba,
 }
 
 template <int ID>
-cudaError_t launch_col_static(const LinePlan& lp, const ColParams& P, bool packed, bool blocked, int num_sms,
+cudaError_t launch_col_static(const LinePlan& lp, const ColParams& P, bool packed, int input, int num_sms,
                               cudaStream_t s) {
   using S = ShapeOf<ID>;
   using SS = typename S::SS;
   constexpr int Q = S::NSEQ;
-  if (blocked) {
+  if constexpr (SS::M0 == S::NT) {  // one last-stage butterfly per thread: the TMA prefetch protocol applies
+    if (input == 2) {
+      if (packed)
+        return launch_line<line_kernel_static<Q, SS, S::NT, S::MAXREG, ColProblem<Q, true, true, true>, ColParams>>(
+            lp, P, S::NT, num_sms, s);
+      return launch_line<line_kernel_static<Q, SS, S::NT, S::MAXREG, ColProblem<Q, false, true, true>, ColParams>>(
+          lp, P, S::NT, num_sms, s);
+    }
+  }
+  if (input >= 1) {
     if (packed)
       return launch_line<line_kernel_static<Q, SS, S::NT, S::MAXREG, ColProblem<Q, true, true>, ColParams>>(
           lp, P, S::NT, num_sms, s);
@@ -69,7 +78,7 @@ cudaError_t launch_col_static(const LinePlan& lp, const ColParams& P, bool packe
 
 template cudaError_t launch_row_static<GBLUR_TU_SHAPE>(const LinePlan&, const RowParams&, bool, bool, int,
                                                        cudaStream_t);
-template cudaError_t launch_col_static<GBLUR_TU_SHAPE>(const LinePlan&, const ColParams&, bool, bool, int,
+template cudaError_t launch_col_static<GBLUR_TU_SHAPE>(const LinePlan&, const ColParams&, bool, int, int,
                                                        cudaStream_t);
 
 }  // namespace gblur

@@ -285,3 +285,17 @@ def test_sigma150_rows_69120(gb, refcheck):
     img = go.synth_u8((rows, cols, 3), 150)
     out, _, _ = _blur_gpu(gb, img, sigma, False)
     _assert_close_u8(out, refcheck.blur(img, sigma, False), "sigma=150 N=69120")
+
+
+@pytest.mark.parametrize("ch,alpha", [(4, True), (4, False), (3, False)])
+def test_tma_column_gather_n4608(gb, refcheck, ch, alpha):
+    """Column FFT length 4608 (the 8K headline shape): compile-time kernel whose panel input comes through
+    strided TMA tiles, with the next unit requested during the last inverse stage."""
+    rows, cols, sigma = 4320, 200, 20.0
+    sz = gb.host_plan_sizes(rows, cols, sigma)
+    assert sz["n_colpass"] == 4608 and gb.host_line_plan(4608)["static"]
+    img = go.synth_u8((rows, cols, ch), 4608 + ch)
+    out, _, _ = _blur_gpu(gb, img, sigma, alpha)
+    _assert_close_u8(out, refcheck.blur(img, sigma, alpha), f"N_col=4608 ch={ch} alpha={alpha}")
+    if ch == 4 and not alpha:
+        assert np.array_equal(out[..., 3], img[..., 3])
