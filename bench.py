@@ -184,8 +184,8 @@ def bench_video(args, wl, torch, dist, gb, world, rank, local, barrier):
     d_in = torch.from_numpy(one).cuda().unsqueeze(0).repeat(n_local, 1, 1, 1).contiguous()
     d_in[:, 0, 0, 0] = torch.arange(f0, f1, device="cuda").to(torch.uint8)  # frames differ
     d_out = torch.empty_like(d_in)
-    h_pin = torch.empty((fs.chunk, rows, cols, ch), dtype=torch.uint8).pin_memory()
-    h_pin.copy_(d_in[: fs.chunk].cpu())
+    h_pin = torch.empty((n_local, rows, cols, ch), dtype=torch.uint8).pin_memory()
+    h_pin.copy_(d_in.cpu())
     stream = torch.cuda.current_stream()
     for _ in range(max(args.warmup, 3)):
         fs.run(d_in, d_out, alpha)
@@ -200,22 +200,21 @@ def bench_video(args, wl, torch, dist, gb, world, rank, local, barrier):
     barrier()
     ms = e0.elapsed_time(e1)
     launches = gb.launch_count() - l0
-    # e2e: every chunk goes host -> device -> host through the host-buffer C-ABI call
-    nchunks = (n_local + fs.chunk - 1) // fs.chunk
-    fs.plan.run_host(h_pin, alpha, n_frames=fs.chunk)
+    # e2e: the rank's whole frame block goes host -> device -> host through ONE host-buffer C-ABI call, which
+    # streams it in chunks of chunk_frames (H2D || blur || D2H)
+    fs.plan.run_host(h_pin, alpha, n_frames=n_local)
     barrier()
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        for _c in range(nchunks):
-            fs.plan.run_host(h_pin, alpha, n_frames=fs.chunk)
+        fs.plan.run_host(h_pin, alpha, n_frames=n_local)
     torch.cuda.synchronize()
     e2e_ms = (time.perf_counter() - t0) * 1e3
     fs.close()
     npx_step = VIDEO_FRAMES * rows * cols
     cp = ch
     return dict(ms_total=ms, e2e_ms=e2e_ms, npx_step=npx_step, launches=launches, scaling="strong",
-                alg_bytes_step=npx_step * 10 * cp, h2d=nchunks * fs.chunk * rows * cols * ch,
-                d2h=nchunks * fs.chunk * rows * cols * ch,
+                alg_bytes_step=npx_step * 10 * cp, h2d=n_local * rows * cols * ch,
+                d2h=n_local * rows * cols * ch,
                 config={"workload": wl, "frames": VIDEO_FRAMES, "rows": rows, "cols": cols, "channels": ch, "sigma": sigma,
                         "apply_to_alpha": alpha, "parallelism": f"frames sharded x{world}, no collective",
                         "frames_per_rank": n_local, "chunk_frames": fs.chunk,

@@ -62,7 +62,10 @@ int gblur_plan_spectrum(const gblur_plan* plan, int axis, float* host_out);
 /* Stage radices chosen for an axis (for logs/tests): writes up to 5 ints, returns count via *n. */
 int gblur_plan_radices(const gblur_plan* plan, int axis, int* radices, int* n, int* static_kernel);
 
-/* Host buffer in place: H2D, blur, D2H, synchronous. */
+/* Host buffer in place: H2D, blur, D2H, synchronous on return. Large single images are pipelined against
+ * PCIe (row chunks run under the H2D copy, column bands leave under the column pass); a batch longer than the
+ * plan's max_frames is streamed in chunks of max_frames (H2D || blur || D2H). Pinned host memory is needed for
+ * the overlap (pageable memory works but serialises). */
 int gblur_run_host(gblur_plan* plan, uint8_t* hwc_inout, int apply_to_alpha);
 int gblur_run_batch_host(gblur_plan* plan, uint8_t* hwc_inout, int n_frames, int apply_to_alpha);
 /* Device buffers (d_in may equal d_out); asynchronous on `cuda_stream` (a cudaStream_t, may be 0). */

@@ -80,6 +80,10 @@ struct gblur_plan {
   uint8_t* d_stage = nullptr;  // device image for gblur_run_host
   size_t stage_bytes = 0;
   cudaStream_t stream = nullptr;
+  cudaStream_t s_in = nullptr, s_out = nullptr;  // copy streams of the pipelined host path
+  std::vector<cudaEvent_t> events;               // reused by the pipelined host path
+  uint8_t* d_stage2 = nullptr;                   // second staging buffer (batches)
+  size_t stage2_bytes = 0;
   int last_cp = 0;       // processed channels of the last run (layout of d_inter)
   int inter_cp = 0;      // processed-channel count the blocked workspace is currently laid out for
   int last_frames = 0;
@@ -192,8 +196,10 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
   return GBLUR_OK;
 }
 
+// rows_sub > 0: only rows [row0, row0 + rows_sub) of a single frame (d_in / d_inter still point at row 0)
 int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pitch, int frames, int alpha,
-                cudaStream_t s, const BlockedLayout* blk = nullptr, int split_cols = 0, long long split_stride = 0) {
+                cudaStream_t s, const BlockedLayout* blk = nullptr, int split_cols = 0, long long split_stride = 0,
+                int row0 = 0, int rows_sub = 0) {
   const int cp = processed_channels(p, alpha);
   RowLaunch a{};
   a.in = d_in;
@@ -208,6 +214,14 @@ int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pi
   if (blk) a.blk = *blk;
   a.split_cols = split_cols;
   a.split_stride = split_stride;
+  if (rows_sub > 0) {
+    a.in = d_in + (long long)row0 * a.in_pitch;
+    a.rows_total = rows_sub;
+    if (blk)
+      a.row_offset = row0;  // panel layout: the slot index carries the row
+    else
+      a.inter = d_inter + (long long)row0 * pitch;
+  }
   CU(launch_rowpass(p->row.lp, a, p->num_sms, s));
   return GBLUR_OK;
 }
@@ -230,8 +244,9 @@ bool panel_tensor_map(gblur_plan* p, const float* base, const BlockedLayout& b, 
   return true;
 }
 
+// w_end > 0: only the float columns [w_begin, w_end) (w_begin a multiple of 32) of a single frame
 int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d_out, long long out_pitch, int frames,
-                int alpha, cudaStream_t s, const BlockedLayout* blk = nullptr) {
+                int alpha, cudaStream_t s, const BlockedLayout* blk = nullptr, int w_begin = 0, int w_end = 0) {
   const int cp = processed_channels(p, alpha);
   ColLaunch a{};
   a.inter = d_inter;
@@ -246,6 +261,8 @@ int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d
   a.out_frame_stride = (long long)p->full_rows * out_pitch;
   a.C = p->channels;
   a.Cp = cp;
+  a.w_begin = w_begin;
+  a.w_end = w_end;
   if (blk) {
     a.blk = *blk;
     const long long panels = ((long long)p->cols * cp + 31) / 32 * frames;
@@ -299,6 +316,10 @@ void gblur_plan_destroy(gblur_plan* p) {
   free_tables(p->col);
   if (p->d_inter) cudaFree(p->d_inter);
   if (p->d_stage) cudaFree(p->d_stage);
+  if (p->d_stage2) cudaFree(p->d_stage2);
+  for (cudaEvent_t e : p->events) cudaEventDestroy(e);
+  if (p->s_in) cudaStreamDestroy(p->s_in);
+  if (p->s_out) cudaStreamDestroy(p->s_out);
   for (void* q : p->owned) cudaFree(q);
   if (p->stream) cudaStreamDestroy(p->stream);
   delete p;
@@ -333,47 +354,64 @@ int gblur_plan_radices(const gblur_plan* p, int axis, int* radices, int* n, int*
   return GBLUR_OK;
 }
 
-static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
-                     void* cuda_stream, int stages) {
-  if (!p || !d_in || !d_out) return fail(GBLUR_E_INVALID, "null argument");
+namespace {
+struct FusedCtx {
+  BlockedLayout blk;
+  const BlockedLayout* bp = nullptr;  // null: row-major intermediate
+  long long pitch = 0;
+  int cp = 0;
+};
+
+// Workspace, layout choice and (when the layout changes) the zero fill, ordered on stream s.
+int fused_prepare(gblur_plan* p, int n_frames, int apply_to_alpha, cudaStream_t s, FusedCtx& c) {
   if (p->band) return fail(GBLUR_E_INVALID, "band plans run through gblur_rowpass_device / gblur_colpass_device");
   if (n_frames < 1 || n_frames > p->max_frames)
     return fail(GBLUR_E_INVALID, "n_frames %d outside [1, %d]", n_frames, p->max_frames);
-  DeviceGuard guard(p->device);
-  cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
-  const int cp = processed_channels(p, apply_to_alpha);
+  c.cp = processed_channels(p, apply_to_alpha);
   // workspace sized for the widest layout (all channels processed)
   const BlockedLayout widest = blocked_layout(p, p->channels);
   const size_t rowmajor_floats = (size_t)p->rows * (size_t)default_pitch((long long)p->cols * p->channels);
   int rc = ensure_inter(p, (size_t)p->max_frames * std::max((size_t)widest.frame_stride, rowmajor_floats));
   if (rc != GBLUR_OK) return rc;
   // tuning switch: GBLUR_LAYOUT=rowmajor keeps the fp32 intermediate row-major (column pass gathers
-  // 16-byte pieces); default is the blocked layout the column pass bulk-copies
+  // 16-byte pieces); default is the panel layout
   static const bool rowmajor = [] {
     const char* e = getenv("GBLUR_LAYOUT");
     return e && std::strcmp(e, "rowmajor") == 0;
   }();
-  const BlockedLayout blk = blocked_layout(p, cp);
+  c.blk = blocked_layout(p, c.cp);
   // a column pass that runs on a cluster reads the row-major intermediate
   const bool use_rowmajor = rowmajor || p->col.lp.cluster > 1;
-  const BlockedLayout* bp = use_rowmajor ? nullptr : &blk;
-  const long long pitch = default_pitch((long long)p->cols * cp);
-  const int layout_tag = use_rowmajor ? -cp : cp;
+  c.bp = use_rowmajor ? nullptr : &c.blk;
+  c.pitch = default_pitch((long long)p->cols * c.cp);
+  const int layout_tag = use_rowmajor ? -c.cp : c.cp;
   if (p->inter_cp != 0 && p->inter_cp != layout_tag) {
     // the zero tail / padding slots of the new layout may hold samples of the old one
     CU(cudaMemsetAsync(p->d_inter, 0, p->inter_floats * sizeof(float), s));
   }
   p->inter_cp = layout_tag;
+  p->last_cp = c.cp;
+  p->last_frames = n_frames;
+  return GBLUR_OK;
+}
+}  // namespace
+
+static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
+                     void* cuda_stream, int stages) {
+  if (!p || !d_in || !d_out) return fail(GBLUR_E_INVALID, "null argument");
+  DeviceGuard guard(p->device);
+  cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+  FusedCtx c;
+  int rc = fused_prepare(p, n_frames, apply_to_alpha, s, c);
+  if (rc != GBLUR_OK) return rc;
   if (stages & 1) {
-    rc = run_rowpass(p, d_in, p->d_inter, pitch, n_frames, apply_to_alpha, s, bp);
+    rc = run_rowpass(p, d_in, p->d_inter, c.pitch, n_frames, apply_to_alpha, s, c.bp);
     if (rc != GBLUR_OK) return rc;
   }
-  p->last_cp = cp;
-  p->last_frames = n_frames;
   if (!(stages & 2)) return GBLUR_OK;
-  if (d_in != d_out && cp < p->channels)
+  if (d_in != d_out && c.cp < p->channels)
     CU(launch_copy_channel(d_in, d_out, (long long)p->rows * p->cols * n_frames, p->channels, 3, s));
-  return run_colpass(p, p->d_inter, pitch, d_out, (long long)p->cols * p->channels, n_frames, apply_to_alpha, s, bp);
+  return run_colpass(p, p->d_inter, c.pitch, d_out, (long long)p->cols * p->channels, n_frames, apply_to_alpha, s, c.bp);
 }
 
 int gblur_run_batch_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
@@ -391,21 +429,120 @@ int gblur_run_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int app
   return gblur_run_batch_device(p, d_in, d_out, 1, apply_to_alpha, cuda_stream);
 }
 
+namespace {
+int ensure_stage(uint8_t** buf, size_t* have, size_t bytes) {
+  if (*have >= bytes) return GBLUR_OK;
+  if (*buf) cudaFree(*buf);
+  *buf = nullptr;
+  *have = 0;
+  CU(cudaMalloc(buf, bytes));
+  *have = bytes;
+  return GBLUR_OK;
+}
+
+int ensure_pipe(gblur_plan* p, size_t nevents) {
+  if (!p->s_in) CU(cudaStreamCreateWithFlags(&p->s_in, cudaStreamNonBlocking));
+  if (!p->s_out) CU(cudaStreamCreateWithFlags(&p->s_out, cudaStreamNonBlocking));
+  while (p->events.size() < nevents) {
+    cudaEvent_t e;
+    CU(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    p->events.push_back(e);
+  }
+  return GBLUR_OK;
+}
+
+// One image, pipelined against PCIe: the rows arrive in K chunks and each chunk's row pass runs while the
+// next one is still on the bus; the column pass runs in K bands of pixel columns and each band leaves for
+// the host (strided 2-D copy) while the next one is computed.
+int run_host_single_pipelined(gblur_plan* p, uint8_t* hwc, int alpha, int K) {
+  const size_t row_bytes = (size_t)p->cols * p->channels;
+  int rc = ensure_stage(&p->d_stage, &p->stage_bytes, row_bytes * p->rows);
+  if (rc != GBLUR_OK) return rc;
+  rc = ensure_pipe(p, (size_t)2 * K + 1);
+  if (rc != GBLUR_OK) return rc;
+  cudaStream_t sc = p->stream;
+  FusedCtx c;
+  rc = fused_prepare(p, 1, alpha, sc, c);
+  if (rc != GBLUR_OK) return rc;
+  // the copy stream must not run ahead of a previous call's D2H (same staging buffer)
+  for (int k = 0; k < K; ++k) {
+    const int r0 = (int)((long long)p->rows * k / K), r1 = (int)((long long)p->rows * (k + 1) / K);
+    if (r1 <= r0) continue;
+    CU(cudaMemcpyAsync(p->d_stage + r0 * row_bytes, hwc + r0 * row_bytes, (size_t)(r1 - r0) * row_bytes,
+                       cudaMemcpyHostToDevice, p->s_in));
+    CU(cudaEventRecord(p->events[k], p->s_in));
+    CU(cudaStreamWaitEvent(sc, p->events[k], 0));
+    rc = run_rowpass(p, p->d_stage, p->d_inter, c.pitch, 1, alpha, sc, c.bp, 0, 0, r0, r1 - r0);
+    if (rc != GBLUR_OK) return rc;
+  }
+  // column bands on 32-pixel boundaries (=> float-column boundaries on multiples of 32 for any Cp)
+  const int px_per_band = std::max(32, ((p->cols + K - 1) / K + 31) / 32 * 32);
+  int e = K;
+  for (int x0 = 0; x0 < p->cols; x0 += px_per_band, ++e) {
+    const int x1 = std::min(p->cols, x0 + px_per_band);
+    rc = run_colpass(p, p->d_inter, c.pitch, p->d_stage, (long long)row_bytes, 1, alpha, sc, c.bp, x0 * c.cp, x1 * c.cp);
+    if (rc != GBLUR_OK) return rc;
+    CU(cudaEventRecord(p->events[e], sc));
+    CU(cudaStreamWaitEvent(p->s_out, p->events[e], 0));
+    CU(cudaMemcpy2DAsync(hwc + (size_t)x0 * p->channels, row_bytes, p->d_stage + (size_t)x0 * p->channels, row_bytes,
+                         (size_t)(x1 - x0) * p->channels, (size_t)p->rows, cudaMemcpyDeviceToHost, p->s_out));
+  }
+  CU(cudaStreamSynchronize(p->s_out));
+  CU(cudaStreamSynchronize(sc));
+  return GBLUR_OK;
+}
+
+// A batch, pipelined by chunks of max_frames frames through two staging buffers:
+// H2D(chunk k+1) || blur(chunk k) || D2H(chunk k-1).
+int run_host_batch_pipelined(gblur_plan* p, uint8_t* hwc, int n_frames, int alpha) {
+  const size_t frame_bytes = (size_t)p->rows * p->cols * p->channels;
+  const int chunk = p->max_frames;
+  int rc = ensure_stage(&p->d_stage, &p->stage_bytes, frame_bytes * chunk);
+  if (rc == GBLUR_OK) rc = ensure_stage(&p->d_stage2, &p->stage2_bytes, frame_bytes * chunk);
+  if (rc == GBLUR_OK) rc = ensure_pipe(p, 6);
+  if (rc != GBLUR_OK) return rc;
+  uint8_t* buf[2] = {p->d_stage, p->d_stage2};
+  cudaEvent_t *ev_in = &p->events[0], *ev_cmp = &p->events[2], *ev_out = &p->events[4];
+  int k = 0;
+  for (int f = 0; f < n_frames; f += chunk, ++k) {
+    const int b = k & 1, n = std::min(chunk, n_frames - f);
+    if (k >= 2) CU(cudaStreamWaitEvent(p->s_in, ev_out[b], 0));  // the buffer's previous D2H has drained
+    CU(cudaMemcpyAsync(buf[b], hwc + (size_t)f * frame_bytes, frame_bytes * n, cudaMemcpyHostToDevice, p->s_in));
+    CU(cudaEventRecord(ev_in[b], p->s_in));
+    CU(cudaStreamWaitEvent(p->stream, ev_in[b], 0));
+    rc = gblur_run_batch_device(p, buf[b], buf[b], n, alpha, p->stream);
+    if (rc != GBLUR_OK) return rc;
+    CU(cudaEventRecord(ev_cmp[b], p->stream));
+    CU(cudaStreamWaitEvent(p->s_out, ev_cmp[b], 0));
+    CU(cudaMemcpyAsync(hwc + (size_t)f * frame_bytes, buf[b], frame_bytes * n, cudaMemcpyDeviceToHost, p->s_out));
+    CU(cudaEventRecord(ev_out[b], p->s_out));
+  }
+  CU(cudaStreamSynchronize(p->s_out));
+  CU(cudaStreamSynchronize(p->stream));
+  return GBLUR_OK;
+}
+}  // namespace
+
 int gblur_run_batch_host(gblur_plan* p, uint8_t* hwc, int n_frames, int apply_to_alpha) {
   if (!p || !hwc) return fail(GBLUR_E_INVALID, "null argument");
-  if (n_frames < 1 || n_frames > p->max_frames)
-    return fail(GBLUR_E_INVALID, "n_frames %d outside [1, %d]", n_frames, p->max_frames);
+  if (p->band) return fail(GBLUR_E_INVALID, "band plans run through gblur_rowpass_device / gblur_colpass_device");
+  if (n_frames < 1) return fail(GBLUR_E_INVALID, "n_frames %d < 1", n_frames);
   DeviceGuard guard(p->device);
-  const size_t bytes = (size_t)p->rows * p->cols * p->channels * (size_t)n_frames;
-  if (p->stage_bytes < bytes) {
-    if (p->d_stage) cudaFree(p->d_stage);
-    p->d_stage = nullptr;
-    p->stage_bytes = 0;
-    CU(cudaMalloc(&p->d_stage, bytes));
-    p->stage_bytes = bytes;
-  }
+  const size_t frame_bytes = (size_t)p->rows * p->cols * p->channels;
+  static const int pipe_chunks = [] {
+    const char* e = getenv("GBLUR_PIPE_CHUNKS");
+    return e ? atoi(e) : 8;
+  }();
+  if (n_frames > p->max_frames) return run_host_batch_pipelined(p, hwc, n_frames, apply_to_alpha);
+  // a single large image on a panel/row-major single-CTA plan: overlap PCIe with the passes
+  if (n_frames == 1 && pipe_chunks > 1 && frame_bytes >= (8u << 20) && p->cols >= 64 * pipe_chunks &&
+      p->rows >= 8 * pipe_chunks && p->col.lp.cluster == 1)
+    return run_host_single_pipelined(p, hwc, apply_to_alpha, std::min(pipe_chunks, 16));
+  const size_t bytes = frame_bytes * (size_t)n_frames;
+  int rc = ensure_stage(&p->d_stage, &p->stage_bytes, bytes);
+  if (rc != GBLUR_OK) return rc;
   CU(cudaMemcpyAsync(p->d_stage, hwc, bytes, cudaMemcpyHostToDevice, p->stream));
-  int rc = gblur_run_batch_device(p, p->d_stage, p->d_stage, n_frames, apply_to_alpha, p->stream);
+  rc = gblur_run_batch_device(p, p->d_stage, p->d_stage, n_frames, apply_to_alpha, p->stream);
   if (rc != GBLUR_OK) return rc;
   CU(cudaMemcpyAsync(hwc, p->d_stage, bytes, cudaMemcpyDeviceToHost, p->stream));
   CU(cudaStreamSynchronize(p->stream));

@@ -381,7 +381,10 @@ __device__ __forceinline__ void run_line_static(const float2* twsm, const float*
     __syncthreads();
   }
   inv_stage<N / SS::M0, NSEQ, true, true>(st, sm, tw0, N, SS::M0, PQ, tid, nthreads);
-  __syncthreads();
+  // SMEM_IN: the buffer is refilled asynchronously and the caller waits for that (plus a barrier or an
+  // mbarrier) before the next unit; otherwise the next unit's first stage overwrites slots that slower
+  // threads may still be reading
+  if constexpr (!SMEM_IN) __syncthreads();
 }
 
 }  // namespace gblur

@@ -135,9 +135,11 @@ cudaError_t launch_colpass(const LinePlan& lp, const ColLaunch& a, int num_sms, 
   P.frame_stride = a.frame_stride;
   P.T = a.T;
   P.pad = a.pad;
-  P.W = a.W;
+  const int w_end = a.w_end > 0 ? a.w_end : a.W;
+  P.W = w_end;
+  P.w_begin = a.w_begin;
   const int L = 2 * lp.nseq;
-  P.groups_per_frame = (a.W + L - 1) / L;
+  P.groups_per_frame = (w_end - a.w_begin + L - 1) / L;
   P.nunits = a.frames * P.groups_per_frame;
   P.out = a.out;
   P.out_pitch = a.out_pitch;

@@ -62,7 +62,9 @@ struct ColLaunch {
   long long frame_stride;
   int frames;
   int T, pad;
-  int W;
+  int W;            // valid float columns of the whole image (cols * Cp)
+  int w_begin = 0;  // column-band launch: float columns [w_begin, w_end) only, w_begin a multiple of 32
+  int w_end = 0;    // 0 = W
   uint8_t* out;
   long long out_pitch;
   long long out_frame_stride;

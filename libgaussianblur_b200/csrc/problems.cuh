@@ -319,7 +319,8 @@ struct ColParams {
   long long pitch;         // floats per row (multiple of 4)
   long long frame_stride;  // floats per frame
   int T, pad;              // line length (rows) and reflect pad
-  int W;                   // valid float columns per row (cols * Cp)
+  int W;                   // end of the valid float columns (cols * Cp): columns >= W are not stored
+  int w_begin;             // first float column of this launch (a multiple of 32; column-band launches)
   int groups_per_frame;    // ceil(W / (2*NSEQ))
   int nunits;              // frames * groups_per_frame
   uint8_t* out;            // HWC u8
@@ -353,7 +354,7 @@ struct ColProblem {
   static __device__ __forceinline__ void tma_request(const ColParams& P, int unit, void* smbase, uint64_t* bar) {
     const int f = unit / P.groups_per_frame;
     const int g = unit - f * P.groups_per_frame;
-    const int w0 = g * L;
+    const int w0 = P.w_begin + g * L;
     const int panel = f * P.panels_per_frame + (w0 >> 5);
     fence_proxy_async();
     mbar_expect_tx(bar, (uint32_t)P.np * (uint32_t)(4 * L));
@@ -363,7 +364,7 @@ struct ColProblem {
   static __device__ __forceinline__ const float* bulk_src(const ColParams& P, int unit) {
     const int f = unit / P.groups_per_frame;
     const int g = unit - f * P.groups_per_frame;
-    const int w0 = g * L;
+    const int w0 = P.w_begin + g * L;
     return P.inter + (long long)f * P.frame_stride + (long long)(w0 >> 5) * P.panel_stride + (w0 & 31);
   }
   struct Loader {
@@ -433,7 +434,7 @@ struct ColProblem {
   static __device__ __forceinline__ void make(const ColParams& P, int unit, Loader& ld, Storer& st) {
     const int f = unit / P.groups_per_frame;
     const int g = unit - f * P.groups_per_frame;
-    const int w0 = g * L;
+    const int w0 = P.w_begin + g * L;
     ld.pad = st.pad = P.pad;
     ld.T = st.T = P.T;
     ld.pitch = P.pitch;
