@@ -131,7 +131,7 @@ class BandShardedBlur:
     # ---- product binding: CUDA plans through the C ABI ----
     @classmethod
     def cuda(cls, rows: int, cols: int, channels: int, sigma: float, apply_to_alpha: bool = False, device: int = 0,
-             group=None, fused: bool = True) -> "BandShardedBlur":
+             group=None, fused: bool = True, pipeline_chunks: int = 0) -> "BandShardedBlur":
         import libgaussianblur_b200 as gb
 
         world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -171,6 +171,44 @@ class BandShardedBlur:
         self.rowpass_split = rowpass_split
         self.plans = (p_row, p_col)
         self._opened = []
+        if (not fused) and pipeline_chunks > 1 and world > 1 and cols % world == 0 and (r1 - r0) >= pipeline_chunks:
+            # NCCL all-to-all pipelined under the row pass: the band's rows go in K chunks; chunk k's blocks
+            # travel on a side stream while chunk k+1 is being computed.
+            K = pipeline_chunks
+            bc = cols // world
+            chunk_plans = []
+            for k in range(K):
+                a, b = shard_range(r1 - r0, K, k)
+                chunk_plans.append(gb.Plan(rows, cols, channels, sigma, device=device, band_rows=b - a, band_cols=cols))
+            side = torch.cuda.Stream(device=dev)
+            row_ranges = self.row_ranges
+
+            def pipelined_run(band: torch.Tensor) -> torch.Tensor:
+                comp = torch.cuda.current_stream()
+                recv_buf = torch.empty((rows, bc, cp), dtype=torch.float32, device=dev)
+                recv_buf.record_stream(side)
+                for k, pk in enumerate(chunk_plans):
+                    a, b = shard_range(r1 - r0, K, k)
+                    send = torch.empty((world, b - a, bc, cp), dtype=torch.float32, device=dev)
+                    pk.rowpass_split(band[a:b], send, bc, (b - a) * bc * cp, apply_to_alpha)
+                    ev = torch.cuda.Event()
+                    ev.record(comp)
+                    send.record_stream(side)
+                    recv = []
+                    for g, (g0, g1) in enumerate(row_ranges):  # rank g cuts ITS band the same way
+                        ga, gb_ = shard_range(g1 - g0, K, k)
+                        recv.append(recv_buf[g0 + ga:g0 + gb_])
+                    with torch.cuda.stream(side):
+                        side.wait_event(ev)
+                        exchange(list(send.unbind(0)), recv, group)
+                comp.wait_stream(side)
+                alpha_src = self._exchange_alpha(band) if cp < channels else None
+                return colpass(recv_buf.view(rows, bc * cp), alpha_src)
+
+            self.fused_run = pipelined_run
+            self.plans = (p_row, p_col, *chunk_plans)
+            self.exchange_kind = f"NCCL all-to-all in {K} row chunks, pipelined under the row pass"
+            return self
         if fused and (cols * cp) % (32 * world) == 0 and world <= 8:
             # Fused exchange: every rank's row pass stores its lines straight into the panel buffer of the rank
             # that owns those columns (CUDA IPC mapping of the peers' buffers, NVLink stores). Two tiny

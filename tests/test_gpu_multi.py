@@ -29,6 +29,18 @@ for ch, alpha, fused in ((1, False, True), (3, False, True), (4, False, True), (
     d = np.abs(out.cpu().numpy().astype(int) - want.reshape(rows, cols, ch)[r0:r1].astype(int)).max()
     assert d <= 1, (ch, alpha, fused, d)
     b.close()
+for ch, alpha in ((1, False), (4, False)):
+    rows, cols, sigma = 250, 384, 6.0
+    img = go.synth_u8((rows, cols, ch) if ch > 1 else (rows, cols), 9 + ch)
+    want = (ref_lib.gaussianblur(img, sigma, alpha) if ch > 1 else ref_lib.blur_plane_u8(img, sigma)) if ref_lib.available() else go.gaussianblur(img, sigma, alpha)
+    b = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, device=local, fused=False, pipeline_chunks=3)
+    assert "pipelined" in b.exchange_kind
+    r0, r1 = b.my_rows
+    out = b.run(torch.from_numpy(img.reshape(rows, cols, ch)[r0:r1].copy()).cuda(), gather_rows=True)
+    torch.cuda.synchronize()
+    d = np.abs(out.cpu().numpy().astype(int) - want.reshape(rows, cols, ch)[r0:r1].astype(int)).max()
+    assert d <= 1, ("pipelined", ch, d)
+    b.close()
 fs = FrameShardedBlur(6, 135, 240, 3, 5.0, device=local, chunk_frames=2)
 f0, f1 = fs.frames
 frames = np.stack([go.synth_u8((135, 240, 3), 100 + f) for f in range(6)])
