@@ -362,6 +362,7 @@ __device__ __forceinline__ void run_line_static(const float2* twsm, const float*
   const float2* tw2 = twsm + SS::TW0 + SS::TW1;
   fwd_stage<N / SS::M0, NSEQ, !SMEM_IN, true>(ld, sm, tw0, N, SS::M0, PQ, tid, nthreads);
   __syncthreads();
+  if constexpr (Loader::kStageNext) ld.after_first_stage();  // staged input consumed: fetch the next line
   if constexpr (SS::S >= 3) {
     fwd_stage<SS::M0 / SS::M1, NSEQ, false, true>(ld, sm, tw1, N, SS::M1, PQ, tid, nthreads);
     __syncthreads();

@@ -104,6 +104,7 @@ cudaError_t launch_rowpass(const LinePlan& lp, const RowLaunch& a, int num_sms, 
   P.split_stride = a.split_stride;
   P.npeers = blocked ? a.npeers : 0;
   P.peer_panels = a.peer_panels;
+  P.peer_magic = a.peer_panels > 0 ? (unsigned)(0x100000000ULL / (unsigned)a.peer_panels) + 1u : 0u;
   P.row_offset = a.row_offset;
   for (int i = 0; i < 8; ++i) P.peer[i] = a.peer[i];
   if (P.npeers) P.inter = reinterpret_cast<float*>(kPeerFakeBase);

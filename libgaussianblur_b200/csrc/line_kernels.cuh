@@ -63,8 +63,22 @@ __global__ void __maxnreg__(MAXREG)
   for (int i = threadIdx.x; i < SS::TWTOT; i += NT) twsm[i] = __ldg(sh.tw[0] + i);
   for (int i = threadIdx.x; i < SS::N; i += NT) kpsm[i] = __ldg(sh.kperm + i);
   // the mbarrier lives behind the tables in dynamic shared memory (a static __shared__ would shift the base)
-  uint64_t& tma_bar = *reinterpret_cast<uint64_t*>(reinterpret_cast<char*>(kpsm + SS::N) + ((SS::N & 1) ? 4 : 0));
+  uint64_t& tma_bar = *reinterpret_cast<uint64_t*>(
+      (reinterpret_cast<uintptr_t>(kpsm + SS::N) + 15) & ~static_cast<uintptr_t>(15));
   uint32_t tma_parity = 0;
+  // staged row input (RowProblemRGBA<.., true>): [mbarrier][row bytes] behind the TMA barrier slot
+  uint64_t* stage_bar = &tma_bar + 1;
+  uint32_t* stage = reinterpret_cast<uint32_t*>(&tma_bar + 2);
+  if constexpr (Problem::kStageIn) {
+    if (threadIdx.x == 0) {
+      mbar_init(stage_bar, 1);
+      fence_proxy_async();
+      if ((int)blockIdx.x < P.nunits) {
+        mbar_expect_tx(stage_bar, (uint32_t)P.T * 4u);
+        bulk_g2s(stage, P.in + (long long)blockIdx.x * P.in_pitch, (uint32_t)P.T * 4u, stage_bar);
+      }
+    }
+  }
   if constexpr (Problem::kTmaIn) {
     static_assert(SS::M0 == NT, "TMA prefetch needs one last-stage butterfly per thread");
     if (threadIdx.x == 0) {
@@ -88,6 +102,12 @@ __global__ void __maxnreg__(MAXREG)
     } else if constexpr (Problem::kBulkIn) {
       gather_wait();
     }
+    if constexpr (Problem::kStageIn) {
+      ld.row = stage;
+      ld.bar = stage_bar;
+      mbar_wait(stage_bar, tma_parity);  // this row's bytes have landed in the staging buffer
+      tma_parity ^= 1u;
+    }
     run_line_static<NSEQ, SS, Problem::kBulkIn>(twsm, kpsm, ld, st, sm, (int)threadIdx.x, NT);
   }
 }
@@ -109,8 +129,11 @@ inline LineShape to_device_shape(const LinePlan& lp) {
 // Persistent grid: one CTA per resident slot (SMs x occupancy), each looping over line units.
 // The occupancy query and the smem opt-in are done once per (kernel, smem size).
 template <auto k, class Params>
-cudaError_t launch_line(const LinePlan& lp, const Params& P, int nthreads, int num_sms, cudaStream_t stream) {
+cudaError_t launch_line(const LinePlan& lp_in, const Params& P, int nthreads, int num_sms, cudaStream_t stream,
+                        size_t extra_smem = 0) {
   if (P.nunits <= 0) return cudaSuccess;
+  LinePlan lp = lp_in;
+  lp.smem_bytes += extra_smem;
   static thread_local size_t cached_smem = (size_t)-1;
   static thread_local int cached_threads = -1;
   static thread_local int cached_device = -1;

@@ -107,7 +107,7 @@ inline bool plan_line(int N, LinePlan& lp) {
         m /= f.radix[s];
         smem += (size_t)tw_nbase(f.radix[s]) * (size_t)m * 8;
       }
-      smem += (size_t)N * 4 + 16;  // + mbarrier of the TMA gather
+      smem += (size_t)N * 4 + 48;  // + alignment slack and the two mbarriers (TMA gather, staged row input)
     }
     if (smem > kMaxSmemBytes) continue;
     lp.exch_elems = exch;

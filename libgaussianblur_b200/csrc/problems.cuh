@@ -58,6 +58,7 @@ struct RowParams {
   float* peer[8];
   int npeers;
   int peer_panels;
+  unsigned peer_magic;  // floor(2^32 / peer_panels) + 1: panel / peer_panels == umulhi(panel, magic) for panel < 2^16
   int row_offset;  // first image row of this band (slot = pad + row_offset + r)
   // panel intermediate (BLOCKED problems): [frame][panel = w/32][slot physc(n)][32 floats] with
   // w = x*Cp + ch the float column: every row writes whole 128-byte lines, and a column unit
@@ -78,7 +79,7 @@ constexpr unsigned long long kPeerFakeBase = 4096;
 
 struct BlockedDst {
   float* base;      // inter + frame offset + physc(pad + r) * 32
-  long long dl, dr; // float offsets of the left / right mirror slot relative to base, 0 = none
+  int dl, dr;       // float offsets of the left / right mirror slot relative to base, 0 = none
   long long gstride;  // floats between consecutive panels = np * 32
 };
 
@@ -90,8 +91,8 @@ __device__ __forceinline__ BlockedDst make_blocked_dst(const RowParams& P, long 
   const int p1 = phys(pad + r, P.blk_padq);
   d.base = P.inter + f * P.blk_frame_stride + (long long)p1 * L;
   d.gstride = (long long)P.blk_np * L;
-  d.dl = (r >= 1 && r <= pad) ? (long long)(phys(pad - r, P.blk_padq) - p1) * L : 0;
-  d.dr = (r >= Tc - 1 - pad && r <= Tc - 2) ? (long long)(phys(pad + 2 * Tc - 2 - r, P.blk_padq) - p1) * L : 0;
+  d.dl = (r >= 1 && r <= pad) ? (phys(pad - r, P.blk_padq) - p1) * L : 0;
+  d.dr = (r >= Tc - 1 - pad && r <= Tc - 2) ? (phys(pad + 2 * Tc - 2 - r, P.blk_padq) - p1) * L : 0;
   return d;
 }
 
@@ -102,7 +103,9 @@ struct RowProblemGeneric {
   static constexpr int L = 2 * NSEQ;
   static constexpr bool kBulkIn = false;
   static constexpr bool kTmaIn = false;
+  static constexpr bool kStageIn = false;
   struct Loader {
+    static constexpr bool kStageNext = false;
     const uint8_t* p[L];
     int C, pad, T;
     __device__ __forceinline__ Pt<NSEQ> load(int n) const {
@@ -122,20 +125,17 @@ struct RowProblemGeneric {
     static constexpr bool kPrefetch = false;
     static constexpr bool kTmaNext = false;
     float* q[L];  // nullptr: line does not exist (tail unit); BLOCKED: BlockedDst::base
-    long long dl[L], dr[L], gstride;
+    int dl[L], dr[L];
+    long long gstride;
     int ch[L];
     int Cp, pad, T;
-    int split_cols;
-    long long split_stride;
-    float* const* peers;  // BLOCKED: panel buffers of the ranks (nullptr: q[k] points into the local buffer)
-    int peer_panels;
-    unsigned peer_magic;  // floor(2^32 / peer_panels) + 1: panel / peer_panels == umulhi(panel, magic) for panel < 2^16
+    const RowParams* prm;  // rarely used fields (split store, peer panels) are read from the parameter bank
     __device__ __forceinline__ void put(int k, int x, int w0, float v) const {
       if (!q[k]) return;
       if constexpr (!BLOCKED) {
-        if (split_cols) {
-          const int h = x / split_cols;
-          q[k][(long long)h * split_stride + (long long)(x - h * split_cols) * Cp] = v;
+        if (prm->split_cols) {
+          const int h = x / prm->split_cols;
+          q[k][(long long)h * prm->split_stride + (long long)(x - h * prm->split_cols) * Cp] = v;
         } else {
           q[k][(long long)x * Cp] = v;
         }
@@ -143,10 +143,11 @@ struct RowProblemGeneric {
         const int w = w0 + ch[k];
         int panel = w >> 5;
         float* d = q[k];
-        if (peers) {  // q[k] holds the offset inside a panel buffer; pick the owner of this panel
-          const int h = peer_panels == 1 ? panel : (int)__umulhi((unsigned)panel, peer_magic);
-          panel -= h * peer_panels;
-          d = peers[h] + ((reinterpret_cast<uintptr_t>(q[k]) - kPeerFakeBase) >> 2);
+        if (prm->npeers) {  // q[k] holds the offset inside a panel buffer; pick the owner of this panel
+          const int pp = prm->peer_panels;
+          const int h = pp == 1 ? panel : (int)__umulhi((unsigned)panel, prm->peer_magic);
+          panel -= h * pp;
+          d = prm->peer[h] + ((reinterpret_cast<uintptr_t>(q[k]) - kPeerFakeBase) >> 2);
         }
         d += (long long)panel * (int)gstride + (w & 31);
         *d = v;
@@ -171,11 +172,7 @@ struct RowProblemGeneric {
     ld.T = st.T = P.T;
     st.Cp = P.Cp;
     st.gstride = 0;
-    st.split_cols = P.split_cols;
-    st.split_stride = P.split_stride;
-    st.peers = (BLOCKED && P.npeers) ? P.peer : nullptr;
-    st.peer_panels = P.peer_panels;
-    st.peer_magic = P.peer_panels > 0 ? (unsigned)(0x100000000ULL / (unsigned)P.peer_panels) + 1u : 0u;
+    st.prm = &P;
 #pragma unroll
     for (int k = 0; k < L; ++k) {
       long long sig = (long long)unit * L + k;
@@ -201,28 +198,45 @@ struct RowProblemGeneric {
 
 // C == Cp == 4, two sequences: one uchar4 load feeds (R + iG, B + iA), one float4 store per pixel.
 // BLOCKED (needs a column plan with two sequences, L = 4): pixel x is column group x.
-template <bool BLOCKED = false>
+// STAGED: the row's bytes are not loaded from global memory by the first stage; a bulk asynchronous copy
+// (TMA 1-D) has put them into a shared-memory staging buffer while the previous row was being transformed,
+// and the copy of the NEXT row is started as soon as the first stage has consumed this one.
+template <bool BLOCKED = false, bool STAGED = false>
 struct RowProblemRGBA {
   static constexpr bool kBulkIn = false;
   static constexpr bool kTmaIn = false;
+  static constexpr bool kStageIn = STAGED;
   struct Loader {
-    const uint32_t* row;
+    static constexpr bool kStageNext = STAGED;
+    const uint32_t* row;  // global row, or the staging buffer when STAGED
     int pad, T;
+    uint64_t* bar;         // STAGED only
+    const void* next_row;  // global address of the row this CTA transforms next, or nullptr
+    uint32_t row_bytes;
     __device__ __forceinline__ Pt<2> load(int n) const {
       const int x = reflect101(n, pad, T);
-      const uint32_t w = __ldg(row + (x < 0 ? 0 : x));
+      const uint32_t w = STAGED ? row[x < 0 ? 0 : x] : __ldg(row + (x < 0 ? 0 : x));
       Pt<2> r;
       r.v[0] = make_float2(u8_to_f32(w, 0), u8_to_f32(w, 1));
       r.v[1] = make_float2(u8_to_f32(w, 2), u8_to_f32(w, 3));
       if (x < 0) r.v[0] = r.v[1] = make_float2(0.f, 0.f);
       return r;
     }
+    // every thread calls this after the barrier that ends the first stage
+    __device__ __forceinline__ void after_first_stage() const {
+      if (threadIdx.x == 0 && next_row) {
+        fence_proxy_async();
+        mbar_expect_tx(bar, row_bytes);
+        bulk_g2s(const_cast<uint32_t*>(row), next_row, row_bytes, bar);
+      }
+    }
   };
   struct Storer {
     static constexpr bool kPrefetch = false;
     static constexpr bool kTmaNext = false;
     float* row;  // row-major: start of the row; blocked: BlockedDst::base
-    long long dl, dr, gstride;
+    int dl, dr;
+    long long gstride;
     int pad, T;
     __device__ __forceinline__ void store(int n, const Pt<2>& v) const {
       const int x = n - pad;
@@ -242,6 +256,13 @@ struct RowProblemRGBA {
     ld.pad = st.pad = P.pad;
     ld.T = st.T = P.T;
     ld.row = reinterpret_cast<const uint32_t*>(P.in + (long long)unit * P.in_pitch);
+    ld.bar = nullptr;
+    ld.next_row = nullptr;
+    ld.row_bytes = (uint32_t)P.T * 4u;
+    if constexpr (STAGED) {
+      const long long next = (long long)unit + gridDim.x;
+      if (next < P.nunits) ld.next_row = P.in + next * P.in_pitch;
+    }
     st.dl = st.dr = st.gstride = 0;
     if constexpr (!BLOCKED) {
       st.row = P.inter + (long long)unit * P.inter_pitch;
@@ -262,7 +283,9 @@ template <bool BLOCKED = false>
 struct RowProblemRGBA1 {
   static constexpr bool kBulkIn = false;
   static constexpr bool kTmaIn = false;
+  static constexpr bool kStageIn = false;
   struct Loader {
+    static constexpr bool kStageNext = false;
     const uint16_t* row;  // already offset by the pair
     int pad, T;
     __device__ __forceinline__ Pt<1> load(int n) const {
@@ -277,7 +300,8 @@ struct RowProblemRGBA1 {
     static constexpr bool kPrefetch = false;
     static constexpr bool kTmaNext = false;
     float* row;
-    long long dl, dr, gstride;
+    int dl, dr;
+    long long gstride;
     int pad, T;
     __device__ __forceinline__ void store(int n, const Pt<1>& v) const {
       const int x = n - pad;
@@ -350,6 +374,7 @@ struct ColProblem {
   static constexpr int L = 2 * NSEQ;
   static constexpr bool kBulkIn = BULK;
   static constexpr bool kTmaIn = BULK && TMA;
+  static constexpr bool kStageIn = false;
   // request every tile of `unit` (one elected thread); completion is counted in bytes on `bar`
   static __device__ __forceinline__ void tma_request(const ColParams& P, int unit, void* smbase, uint64_t* bar) {
     const int f = unit / P.groups_per_frame;
@@ -368,6 +393,7 @@ struct ColProblem {
     return P.inter + (long long)f * P.frame_stride + (long long)(w0 >> 5) * P.panel_stride + (w0 & 31);
   }
   struct Loader {
+    static constexpr bool kStageNext = false;
     const float* col;  // inter + frame*frame_stride + w0
     long long pitch;
     int pad, T;

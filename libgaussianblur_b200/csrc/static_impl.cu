@@ -1,4 +1,6 @@
 // static_impl.cu — compiled once per entry of static_shapes.h with -DGBLUR_TU_SHAPE=<id>.
+#include <cstdlib>
+
 #include "line_kernels.cuh"
 #include "static_shapes.h"
 
@@ -25,6 +27,15 @@ cudaError_t launch_row_static(const LinePlan& lp, const RowParams& P, bool rgba,
   using S = ShapeOf<ID>;
   using SS = typename S::SS;
   if constexpr (S::NSEQ == 2) {
+    // staged input: the next row is bulk-copied into shared memory behind the tables while this one is
+    // transformed; needs 16-byte aligned rows and room for T*4 bytes
+    const size_t stage_bytes = (size_t)P.T * 4;
+    const bool staged = rgba && blocked && (stage_bytes % 16) == 0 && (P.in_pitch % 16) == 0 &&
+                        (reinterpret_cast<uintptr_t>(P.in) % 16) == 0 &&
+                        lp.smem_bytes + stage_bytes <= (size_t)227 * 1024 - 64 && !getenv("GBLUR_NO_STAGE");
+    if (staged)
+      return launch_line<line_kernel_static<2, SS, S::NT, S::MAXREG, RowProblemRGBA<true, true>, RowParams>>(
+          lp, P, S::NT, num_sms, s, stage_bytes);
     if (rgba && blocked)
       return launch_line<line_kernel_static<2, SS, S::NT, S::MAXREG, RowProblemRGBA<true>, RowParams>>(lp, P, S::NT,
                                                                                                        num_sms, s);
