@@ -48,6 +48,19 @@ METRIC = "Mpixel/s 8K RGBA sigma=20"
 UNIT = "Mpixel/s"
 
 
+def load_traffic(workload, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel`, from the committed ncu --set full capture of
+    this workload (profiles/r01/traffic_8k.json; tools/gpu_final.sh regenerates it). None when there is no capture."""
+    if workload != "8k_rgba_sigma20":
+        return None, None
+    p = os.path.join(ROOT, "profiles", "r01", "traffic_8k.json")
+    try:
+        t = json.load(open(p))[kernel]
+        return int(t["traffic"]), t["source"]
+    except Exception:
+        return None, None
+
+
 def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -457,6 +470,7 @@ def main():
         dom = max(kern_ms, key=kern_ms.get)
         alg_bytes = npx * cp * 5 + (npx * (ch - cp) if dom == "col_pass" else 0)  # u8 + fp32 per pixel-channel
         achieved = alg_bytes / (kern_ms[dom] * 1e-3) / 1e9
+        traffic, traffic_src = load_traffic(wl, dom)
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_total / args.steps, "higher_is_better": True,
@@ -471,7 +485,7 @@ def main():
             "gpu_launches": int(launches),
             "kernels_ms": kern_ms,
             "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                         "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": int(alg_bytes),
                          "whole_step_frac": (npx * (10 * cp + 2 * (ch - cp)) / (ms_total / args.steps * 1e-3) / 1e9) / peak},
             "clocks": clocks,
