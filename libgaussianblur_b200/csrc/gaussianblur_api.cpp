@@ -140,7 +140,8 @@ void gaussianblur_batch(uint8_t *frames, const int n_frames, const ImgGeom frame
                         const bool apply_to_alpha) {
   if (n_frames <= 0) return;
   if (!valid_request(frame_geometry, sigma, true)) return;
-  GblurPlanHandle plan = cache().get(make_key(frame_geometry, sigma, n_frames));
+  // the plan holds workspace for 16 frames; longer batches are streamed through it (H2D || blur || D2H)
+  GblurPlanHandle plan = cache().get(make_key(frame_geometry, sigma, n_frames < 16 ? n_frames : 16));
   check(gblur_run_batch_host(plan.get(), frames, n_frames, apply_to_alpha ? 1 : 0));
 }
 
