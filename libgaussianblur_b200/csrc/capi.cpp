@@ -91,8 +91,8 @@ struct gblur_plan {
 
 namespace {
 
-int build_tables(LineTables& t, int N, const std::vector<float>& taps) {
-  if (!host::plan_line(N, t.lp))
+int build_tables(LineTables& t, int N, const std::vector<float>& taps, int cluster_nseq) {
+  if (!host::plan_line(N, t.lp, cluster_nseq))
     return fail(GBLUR_E_UNSUPPORTED, "FFT length %d does not fit one CTA's shared memory", N);
   const std::vector<double> gains = host::kernel_gains(taps, N);
   t.kerf = host::kerf_ordered(gains, N);
@@ -129,8 +129,9 @@ BlockedLayout blocked_layout(const gblur_plan* p, int cp) {
   const LinePlan& c = p->col.lp;
   b.enabled = 1;
   b.L = 2 * c.nseq;
-  b.np = c.exch_elems;
-  b.padq = c.padq;
+  // cluster column plans read the panel through their loader: natural slot order, no padding holes
+  b.np = c.cluster > 1 ? c.N : c.exch_elems;
+  b.padq = c.cluster > 1 ? 0 : c.padq;
   b.rows_per_frame = p->full_rows;
   const long long panels = ((long long)p->cols * cp + 31) / 32;
   b.frame_stride = panels * b.np * 32;
@@ -184,8 +185,8 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
   int rc = GBLUR_OK;
   if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess)
     rc = fail(GBLUR_E_CUDA, "cudaStreamCreate failed");
-  if (rc == GBLUR_OK) rc = build_tables(p->row, sz.n_rowpass, taps);
-  if (rc == GBLUR_OK) rc = build_tables(p->col, sz.n_colpass, taps);
+  if (rc == GBLUR_OK) rc = build_tables(p->row, sz.n_rowpass, taps, 1);
+  if (rc == GBLUR_OK) rc = build_tables(p->col, sz.n_colpass, taps, 2);
   if (rc != GBLUR_OK) {
     std::string keep = g_err;
     gblur_plan_destroy(p);
@@ -265,6 +266,7 @@ int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d
   a.w_end = w_end;
   if (blk) {
     a.blk = *blk;
+    a.panel_in = p->col.lp.cluster > 1 ? 1 : 0;
     const long long panels = ((long long)p->cols * cp + 31) / 32 * frames;
     if (p->col.lp.cluster == 1 && panel_tensor_map(p, d_inter, *blk, panels)) {
       a.tmap = &p->tmap;
@@ -380,8 +382,12 @@ int fused_prepare(gblur_plan* p, int n_frames, int apply_to_alpha, cudaStream_t 
     return e && std::strcmp(e, "rowmajor") == 0;
   }();
   c.blk = blocked_layout(p, c.cp);
-  // a column pass that runs on a cluster reads the row-major intermediate
-  const bool use_rowmajor = rowmajor || p->col.lp.cluster > 1;
+  // single-GPU run with a cluster column pass: the row-major intermediate is a little faster (cheaper stores)
+  static const bool panel_forced = [] {
+    const char* e = getenv("GBLUR_LAYOUT");
+    return e && std::strcmp(e, "panel") == 0;
+  }();
+  const bool use_rowmajor = rowmajor || (p->col.lp.cluster > 1 && !panel_forced);
   c.bp = use_rowmajor ? nullptr : &c.blk;
   c.pitch = default_pitch((long long)p->cols * c.cp);
   const int layout_tag = use_rowmajor ? -c.cp : c.cp;

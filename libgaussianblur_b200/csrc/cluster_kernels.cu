@@ -229,31 +229,36 @@ static cudaError_t launch_cluster(const LinePlan& lp, const Params& P, cudaStrea
   return e != cudaSuccess ? e : cudaGetLastError();
 }
 
-template <int G, class SS>
+template <int Q, int G, class SS>
 static cudaError_t row_gs(const LinePlan& lp, const RowParams& P, bool blocked, cudaStream_t s) {
-  if (blocked) return launch_cluster<line_kernel_cluster<1, G, SS, RowProblemGeneric<1, true>, RowParams>, G>(lp, P, s);
-  return launch_cluster<line_kernel_cluster<1, G, SS, RowProblemGeneric<1, false>, RowParams>, G>(lp, P, s);
+  if (blocked) return launch_cluster<line_kernel_cluster<Q, G, SS, RowProblemGeneric<Q, true>, RowParams>, G>(lp, P, s);
+  return launch_cluster<line_kernel_cluster<Q, G, SS, RowProblemGeneric<Q, false>, RowParams>, G>(lp, P, s);
 }
-template <int G, class SS>
+template <int Q, int G, class SS>
 static cudaError_t col_gs(const LinePlan& lp, const ColParams& P, bool packed, cudaStream_t s) {
-  if (packed) return launch_cluster<line_kernel_cluster<1, G, SS, ColProblem<1, true, false>, ColParams>, G>(lp, P, s);
-  return launch_cluster<line_kernel_cluster<1, G, SS, ColProblem<1, false, false>, ColParams>, G>(lp, P, s);
+  if (packed) return launch_cluster<line_kernel_cluster<Q, G, SS, ColProblem<Q, true, false>, ColParams>, G>(lp, P, s);
+  return launch_cluster<line_kernel_cluster<Q, G, SS, ColProblem<Q, false, false>, ColParams>, G>(lp, P, s);
 }
+// compile-time stage lists exist for (34560: G = 2 one sequence, G = 4 two sequences) and (69120: G = 4 one sequence)
 template <int G>
 static cudaError_t row_g(const LinePlan& lp, const RowParams& P, bool blocked, cudaStream_t s) {
   if constexpr (G == 2)
-    if (plan_matches<Shape34560>(lp, 2)) return row_gs<2, Shape34560>(lp, P, blocked, s);
-  if constexpr (G == 4)
-    if (plan_matches<Shape69120>(lp, 4)) return row_gs<4, Shape69120>(lp, P, blocked, s);
-  return row_gs<G, void>(lp, P, blocked, s);
+    if (lp.nseq == 1 && plan_matches<Shape34560>(lp, 2)) return row_gs<1, 2, Shape34560>(lp, P, blocked, s);
+  if constexpr (G == 4) {
+    if (lp.nseq == 2 && plan_matches<Shape34560>(lp, 4)) return row_gs<2, 4, Shape34560>(lp, P, blocked, s);
+    if (lp.nseq == 1 && plan_matches<Shape69120>(lp, 4)) return row_gs<1, 4, Shape69120>(lp, P, blocked, s);
+  }
+  return lp.nseq == 2 ? row_gs<2, G, void>(lp, P, blocked, s) : row_gs<1, G, void>(lp, P, blocked, s);
 }
 template <int G>
 static cudaError_t col_g(const LinePlan& lp, const ColParams& P, bool packed, cudaStream_t s) {
   if constexpr (G == 2)
-    if (plan_matches<Shape34560>(lp, 2)) return col_gs<2, Shape34560>(lp, P, packed, s);
-  if constexpr (G == 4)
-    if (plan_matches<Shape69120>(lp, 4)) return col_gs<4, Shape69120>(lp, P, packed, s);
-  return col_gs<G, void>(lp, P, packed, s);
+    if (lp.nseq == 1 && plan_matches<Shape34560>(lp, 2)) return col_gs<1, 2, Shape34560>(lp, P, packed, s);
+  if constexpr (G == 4) {
+    if (lp.nseq == 2 && plan_matches<Shape34560>(lp, 4)) return col_gs<2, 4, Shape34560>(lp, P, packed, s);
+    if (lp.nseq == 1 && plan_matches<Shape69120>(lp, 4)) return col_gs<1, 4, Shape69120>(lp, P, packed, s);
+  }
+  return lp.nseq == 2 ? col_gs<2, G, void>(lp, P, packed, s) : col_gs<1, G, void>(lp, P, packed, s);
 }
 
 cudaError_t launch_row_cluster(const LinePlan& lp, const RowParams& P, bool blocked, cudaStream_t s) {

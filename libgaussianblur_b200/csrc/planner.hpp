@@ -4,6 +4,7 @@
 #pragma once
 #include <cmath>
 #include <cstddef>
+#include <cstdlib>
 #include <vector>
 
 #include "hostsem.hpp"
@@ -83,7 +84,9 @@ inline int tw_nbase(int R) {
 
 // Fill everything of a LinePlan that does not live on the device. Returns false when the length
 // does not fit one CTA's shared memory even with a single sequence.
-inline bool plan_line(int N, LinePlan& lp) {
+// cluster_nseq: preferred sequences per unit when the line needs a cluster (the row pass runs best with one —
+// byte loads from 2 rows, G = 2 — the column pass with two — 16-byte gathers, 4-byte stores); 0 = no preference
+inline bool plan_line(int N, LinePlan& lp, int cluster_nseq = 0) {
   lp = LinePlan{};
   lp.N = N;
   for (int nseq = 2; nseq >= 1; --nseq) {
@@ -129,7 +132,22 @@ inline bool plan_line(int N, LinePlan& lp) {
   // Too long for one CTA: split the line over a thread-block cluster of G CTAs (distributed
   // shared memory). Stage 0 is radix 16 and crosses CTAs; after it the line falls apart into 16
   // independent sub-transforms of length N/16, 16/G of them per CTA, which run locally.
-  for (int G = 2; G <= 8; G *= 2) {
+  // Two sequences per cluster (16-byte pieces for the column gather, shared twiddles) when that fits a
+  // cluster of at most 4 CTAs, else one sequence. GBLUR_CLUSTER_NSEQ=1|2 forces the choice (tuning).
+  static const int forced_nseq = [] {
+    const char* e = getenv("GBLUR_CLUSTER_NSEQ");
+    return e ? atoi(e) : 0;
+  }();
+  struct Cand {
+    int G, nseq;
+  };
+  const Cand order2[] = {{2, 2}, {4, 2}, {2, 1}, {4, 1}, {8, 2}, {8, 1}};
+  const Cand order1[] = {{2, 1}, {4, 1}, {2, 2}, {4, 2}, {8, 1}, {8, 2}};
+  const Cand* order = cluster_nseq == 1 ? order1 : order2;
+  for (int ci = 0; ci < 6; ++ci) {
+    const Cand cand = order[ci];
+    const int G = cand.G;
+    if (forced_nseq && cand.nseq != forced_nseq) continue;
     if (N % (16 * G)) continue;
     Factorization rest;
     int cur[kHostMaxStages];
@@ -168,10 +186,10 @@ inline bool plan_line(int N, LinePlan& lp) {
     const int rlast = rest.radix[rest.nstages - 1];
     const int nloc = N / G;
     const int exch = exch_elems_for(nloc, rlast);
-    const size_t smem = (size_t)exch * 8;
+    const size_t smem = (size_t)exch * 8 * (size_t)cand.nseq;
     if (smem > kMaxSmemBytes) continue;
     lp.cluster = G;
-    lp.nseq = 1;
+    lp.nseq = cand.nseq;
     lp.exch_elems = exch;
     lp.nstages = rest.nstages + 1;
     lp.radix[0] = 16;
