@@ -155,9 +155,38 @@ struct RowProblemGeneric {
         if (dr[k]) d[dr[k]] = v;
       }
     }
+    // one plane (Cp == 1), panel layout: every line of the unit lands in the same panel column, so the panel
+    // arithmetic (and the owner lookup of the fused exchange) is done once per position
+    __device__ __forceinline__ void store_planar(int x, const Pt<NSEQ>& v) const {
+      int panel = x >> 5;
+      long long off = x & 31;
+      float* peer_base = nullptr;
+      if (prm->npeers) {
+        const int pp = prm->peer_panels;
+        const int h = pp == 1 ? panel : (int)__umulhi((unsigned)panel, prm->peer_magic);
+        panel -= h * pp;
+        peer_base = prm->peer[h];
+      }
+      off += (long long)panel * (int)gstride;
+#pragma unroll
+      for (int k = 0; k < L; ++k) {
+        if (!q[k]) continue;
+        float* d = (peer_base ? peer_base + ((reinterpret_cast<uintptr_t>(q[k]) - kPeerFakeBase) >> 2) : q[k]) + off;
+        const float val = (k & 1) ? v.v[k >> 1].y : v.v[k >> 1].x;
+        *d = val;
+        if (dl[k]) d[dl[k]] = val;
+        if (dr[k]) d[dr[k]] = val;
+      }
+    }
     __device__ __forceinline__ void store(int n, const Pt<NSEQ>& v) const {
       const int x = n - pad;
       if (x < 0 || x >= T) return;
+      if constexpr (BLOCKED) {
+        if (Cp == 1) {
+          store_planar(x, v);
+          return;
+        }
+      }
       const int w0 = x * Cp;
 #pragma unroll
       for (int s = 0; s < NSEQ; ++s) {
