@@ -117,15 +117,21 @@ cudaError_t launch_rowpass(const LinePlan& lp, const RowLaunch& a, int num_sms, 
   const bool rgba = P.split_cols == 0 && P.npeers == 0 && (lp.nseq == 2 || lp.static_id >= 0) && a.C == 4 && a.Cp == 4 && (a.in_pitch % 4) == 0 &&
                     (reinterpret_cast<uintptr_t>(a.in) % 4) == 0 && (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0 &&
                     (blocked || (a.inter_pitch % 4) == 0);
+  // three processed channels (RGB, or RGBA without alpha), panel layout, two sequences: byte loads at fixed
+  // offsets, 32-bit panel arithmetic (so every float offset inside a frame's panels must fit an int)
+  const bool rgb3 = blocked && P.npeers == 0 && lp.nseq == 2 && a.Cp == 3 && (a.C == 3 || a.C == 4) &&
+                    a.in_pitch < (1LL << 30) && !getenv("GBLUR_NO_RGB3") &&
+                    (long long)((3LL * a.T + 31) / 32 + 1) * a.blk.np * kPanelFloats < (1LL << 31);
+  const int fast = rgba ? kRowFastRGBA : rgb3 ? kRowFastRGB3 : kRowFastNone;
   if (lp.cluster > 1) return launch_row_cluster(lp, P, blocked, stream);
   switch (lp.static_id) {
 #define X(ID, NSEQ, R0, R1, R2, R3, NT, MINB) \
   case ID:                                    \
-    return launch_row_static<ID>(lp, P, rgba, blocked, num_sms, stream);
+    return launch_row_static<ID>(lp, P, fast, blocked, num_sms, stream);
     GBLUR_STATIC_SHAPES(X)
 #undef X
     default:
-      return launch_row_generic(lp, P, rgba, blocked, num_sms, stream);
+      return launch_row_generic(lp, P, fast, blocked, num_sms, stream);
   }
 }
 

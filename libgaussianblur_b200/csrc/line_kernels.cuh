@@ -12,6 +12,9 @@ namespace gblur {
 
 void count_launch();  // kernels.cu
 
+// which specialised row problem the launch arguments allow
+constexpr int kRowFastNone = 0, kRowFastRGBA = 1, kRowFastRGB3 = 2;
+
 // Stage one unit into shared memory (BULK problems): np pieces of one exchange-buffer element each,
 // 128 bytes apart in the panel intermediate, gathered with cp.async (no registers, all in flight
 // at once). Every thread waits for its own copies; the caller's barrier publishes them.
@@ -74,8 +77,9 @@ __global__ void __maxnreg__(MAXREG)
       mbar_init(stage_bar, 1);
       fence_proxy_async();
       if ((int)blockIdx.x < P.nunits) {
-        mbar_expect_tx(stage_bar, (uint32_t)P.T * 4u);
-        bulk_g2s(stage, P.in + (long long)blockIdx.x * P.in_pitch, (uint32_t)P.T * 4u, stage_bar);
+        const uint32_t bytes = Problem::stage_bytes(P, (long long)blockIdx.x);
+        mbar_expect_tx(stage_bar, bytes);
+        bulk_g2s(stage, Problem::stage_src(P, (long long)blockIdx.x), bytes, stage_bar);
       }
     }
   }
@@ -103,8 +107,7 @@ __global__ void __maxnreg__(MAXREG)
       gather_wait();
     }
     if constexpr (Problem::kStageIn) {
-      ld.row = stage;
-      ld.bar = stage_bar;
+      ld.set_stage(stage, stage_bar);
       mbar_wait(stage_bar, tma_parity);  // this row's bytes have landed in the staging buffer
       tma_parity ^= 1u;
     }
@@ -164,11 +167,11 @@ cudaError_t launch_line(const LinePlan& lp_in, const Params& P, int nthreads, in
 // entry points implemented one per translation unit
 // rgba: uchar4/float4 fast path; blocked: blocked intermediate; packed: aligned u16/u32 output stores
 template <int ID>
-cudaError_t launch_row_static(const LinePlan&, const RowParams&, bool rgba, bool blocked, int num_sms, cudaStream_t);
+cudaError_t launch_row_static(const LinePlan&, const RowParams&, int fast, bool blocked, int num_sms, cudaStream_t);
 // input: 0 = row-major loader, 1 = panel layout gathered with cp.async, 2 = panel layout through TMA tiles
 template <int ID>
 cudaError_t launch_col_static(const LinePlan&, const ColParams&, bool packed, int input, int num_sms, cudaStream_t);
-cudaError_t launch_row_generic(const LinePlan&, const RowParams&, bool rgba, bool blocked, int num_sms, cudaStream_t);
+cudaError_t launch_row_generic(const LinePlan&, const RowParams&, int fast, bool blocked, int num_sms, cudaStream_t);
 cudaError_t launch_col_generic(const LinePlan&, const ColParams&, bool packed, bool blocked, int num_sms,
                                cudaStream_t);
 // cluster_kernels.cu: lines split over the shared memories of a thread-block cluster

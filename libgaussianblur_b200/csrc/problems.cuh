@@ -242,6 +242,10 @@ struct RowProblemRGBA {
     uint64_t* bar;         // STAGED only
     const void* next_row;  // global address of the row this CTA transforms next, or nullptr
     uint32_t row_bytes;
+    __device__ __forceinline__ void set_stage(void* buf, uint64_t* b) {
+      row = static_cast<const uint32_t*>(buf);
+      bar = b;
+    }
     __device__ __forceinline__ Pt<2> load(int n) const {
       const int x = reflect101(n, pad, T);
       const uint32_t w = STAGED ? row[x < 0 ? 0 : x] : __ldg(row + (x < 0 ? 0 : x));
@@ -281,6 +285,11 @@ struct RowProblemRGBA {
       }
     }
   };
+  // STAGED: what the bulk copy for `unit` moves (one image row)
+  static __device__ __forceinline__ const void* stage_src(const RowParams& P, long long unit) {
+    return P.in + unit * P.in_pitch;
+  }
+  static __device__ __forceinline__ uint32_t stage_bytes(const RowParams& P, long long) { return (uint32_t)P.T * 4u; }
   static __device__ __forceinline__ void make(const RowParams& P, int unit, Loader& ld, Storer& st) {
     ld.pad = st.pad = P.pad;
     ld.T = st.T = P.T;
@@ -360,6 +369,148 @@ struct RowProblemRGBA1 {
       st.dl = d.dl;
       st.dr = d.dr;
       st.gstride = d.gstride;
+    }
+  }
+};
+
+// Cp == 3 (RGB, or RGBA with the alpha plane left alone), two sequences, panel intermediate only.
+// A unit is the same four consecutive lines sigma = 4u .. 4u+3 that RowProblemGeneric<2> takes (so
+// the pairing (a + ib) and therefore every rounding is identical), but they always lie in the image
+// rows r0 = 4u/3 and r0 + 1: the loader is four byte loads at fixed offsets from one base, the storer
+// four scalar stores with one 32-bit panel computation each. Rows inside the reflect border and
+// the tail unit take a checked slow path.
+// STAGED: rows r0 and r0+1 are bulk-copied into shared memory while the previous unit runs.
+template <bool STAGED = false>
+struct RowProblemRGB3 {
+  static constexpr bool kBulkIn = false;
+  static constexpr bool kTmaIn = false;
+  static constexpr bool kStageIn = STAGED;
+  struct Loader {
+    static constexpr bool kStageNext = STAGED;
+    const uint8_t* row;  // global row r0, or the staging buffer when STAGED
+    int off[4];          // byte offset of line k's channel: (row select) * pitch + channel
+    int C, pad, T;
+    uint64_t* bar;         // STAGED only
+    const void* next_row;  // global address of the rows this CTA stages next, or nullptr
+    uint32_t next_bytes;
+    __device__ __forceinline__ void set_stage(void* buf, uint64_t* b) {
+      row = static_cast<const uint8_t*>(buf);
+      bar = b;
+    }
+    static __device__ __forceinline__ float byte_to_f32(uint32_t b) {
+      return __uint_as_float(b | 0x4B000000u) - 8388608.0f;
+    }
+    __device__ __forceinline__ Pt<2> load(int n) const {
+      const int x = reflect101(n, pad, T);
+      const int xo = (x < 0 ? 0 : x) * C;
+      float f[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        uint32_t b;
+        if constexpr (STAGED) {
+          asm volatile("ld.shared.u8 %0, [%1];" : "=r"(b) : "r"(smem_addr(row) + (uint32_t)(off[k] + xo)));
+        } else {
+          b = __ldg(row + (off[k] + xo));
+        }
+        f[k] = byte_to_f32(b);
+      }
+      Pt<2> r;
+      r.v[0] = make_float2(f[0], f[1]);
+      r.v[1] = make_float2(f[2], f[3]);
+      if (x < 0) r.v[0] = r.v[1] = make_float2(0.f, 0.f);
+      return r;
+    }
+    __device__ __forceinline__ void after_first_stage() const {
+      if (threadIdx.x == 0 && next_row) {
+        fence_proxy_async();
+        mbar_expect_tx(bar, next_bytes);
+        bulk_g2s(const_cast<uint8_t*>(row), next_row, next_bytes, bar);
+      }
+    }
+  };
+  struct Storer {
+    static constexpr bool kPrefetch = false;
+    static constexpr bool kTmaNext = false;
+    float* q[4];    // BlockedDst::base of line k's image row
+    int ch[4];      // channel of line k
+    int dl0, dr0, dl1, dr1;  // mirror slots of rows r0, r0 + 1 (float offsets, 0 = none)
+    int m0;         // lines k < m0 are in row r0, the others in row r0 + 1
+    int nvalid;     // lines k >= nvalid do not exist (tail unit)
+    int gs32;       // floats between consecutive panels minus 32
+    int slow;       // any mirror slot or missing line: take the checked path
+    int pad, T;
+    __device__ __forceinline__ void store(int n, const Pt<2>& v) const {
+      const int x = n - pad;
+      if (x < 0 || x >= T) return;
+      const int w0 = 3 * x;
+      const float val[4] = {v.v[0].x, v.v[0].y, v.v[1].x, v.v[1].y};
+      if (!slow) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const int w = w0 + ch[k];
+          q[k][w + (w >> 5) * gs32] = val[k];
+        }
+      } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          if (k >= nvalid) continue;
+          const int w = w0 + ch[k];
+          float* d = q[k] + (w + (w >> 5) * gs32);
+          const int ml = k >= m0 ? dl1 : dl0, mr = k >= m0 ? dr1 : dr0;  // no dynamic indexing: keeps the struct in registers
+          *d = val[k];
+          if (ml) d[ml] = val[k];
+          if (mr) d[mr] = val[k];
+        }
+      }
+    }
+  };
+  static __device__ __forceinline__ long long first_row(long long unit) { return (unit * 4) / 3; }
+  // STAGED: the bulk copy for `unit` moves rows r0 and (when it exists) r0 + 1; needs in_pitch == T * C
+  static __device__ __forceinline__ const void* stage_src(const RowParams& P, long long unit) {
+    return P.in + first_row(unit) * P.in_pitch;
+  }
+  static __device__ __forceinline__ uint32_t stage_bytes(const RowParams& P, long long unit) {
+    const long long rows_total = P.nreal / 3;
+    return (uint32_t)P.in_pitch * (first_row(unit) + 1 < rows_total ? 2u : 1u);
+  }
+  static __device__ __forceinline__ void make(const RowParams& P, int unit, Loader& ld, Storer& st) {
+    const long long sig0 = (long long)unit * 4;
+    const long long r0 = sig0 / 3;
+    const int c0 = (int)(sig0 - r0 * 3);
+    ld.C = P.C;
+    ld.pad = st.pad = P.pad;
+    ld.T = st.T = P.T;
+    ld.row = P.in + r0 * P.in_pitch;
+    ld.bar = nullptr;
+    ld.next_row = nullptr;
+    ld.next_bytes = 0;
+    if constexpr (STAGED) {
+      const long long next = (long long)unit + gridDim.x;
+      if (next < P.nunits) {
+        ld.next_row = stage_src(P, next);
+        ld.next_bytes = stage_bytes(P, next);
+      }
+    }
+    const long long left = P.nreal - sig0;
+    st.nvalid = left < 4 ? (int)left : 4;
+    st.m0 = 3 - c0;
+    const BlockedDst d0 = make_blocked_dst(P, r0);
+    BlockedDst d1 = d0;
+    if (st.nvalid > st.m0) d1 = make_blocked_dst(P, r0 + 1);
+    st.dl0 = d0.dl;
+    st.dr0 = d0.dr;
+    st.dl1 = d1.dl;
+    st.dr1 = d1.dr;
+    st.gs32 = (int)d0.gstride - kPanelFloats;
+    st.slow = (st.nvalid < 4) | d0.dl | d0.dr | d1.dl | d1.dr;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const bool ok = k < st.nvalid;
+      const int rs = (ok && k >= st.m0) ? 1 : 0;
+      const int ch = ok ? (rs ? k - st.m0 : c0 + k) : c0;  // a missing line re-reads line 0 and is never stored
+      ld.off[k] = rs * (int)P.in_pitch + ch;
+      st.ch[k] = ch;
+      st.q[k] = rs ? d1.base : d0.base;
     }
   }
 };

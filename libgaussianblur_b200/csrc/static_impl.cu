@@ -22,11 +22,24 @@ GBLUR_STATIC_SHAPES(X)
 #undef X
 
 template <int ID>
-cudaError_t launch_row_static(const LinePlan& lp, const RowParams& P, bool rgba, bool blocked, int num_sms,
+cudaError_t launch_row_static(const LinePlan& lp, const RowParams& P, int fast, bool blocked, int num_sms,
                               cudaStream_t s) {
   using S = ShapeOf<ID>;
   using SS = typename S::SS;
+  const bool rgba = fast == kRowFastRGBA;
   if constexpr (S::NSEQ == 2) {
+    if (fast == kRowFastRGB3 && blocked) {
+      // staged input: rows r0 and r0 + 1 of the next unit, contiguous in memory
+      const size_t stage_bytes = (size_t)P.in_pitch * 2;
+      const bool staged = (P.in_pitch % 16) == 0 && P.in_pitch == (long long)P.T * P.C &&
+                          (reinterpret_cast<uintptr_t>(P.in) % 16) == 0 &&
+                          lp.smem_bytes + stage_bytes <= (size_t)227 * 1024 - 64 && !getenv("GBLUR_NO_STAGE");
+      if (staged)
+        return launch_line<line_kernel_static<2, SS, S::NT, S::MAXREG, RowProblemRGB3<true>, RowParams>>(
+            lp, P, S::NT, num_sms, s, stage_bytes);
+      return launch_line<line_kernel_static<2, SS, S::NT, S::MAXREG, RowProblemRGB3<false>, RowParams>>(lp, P, S::NT,
+                                                                                                        num_sms, s);
+    }
     // staged input: the next row is bulk-copied into shared memory behind the tables while this one is
     // transformed; needs 16-byte aligned rows and room for T*4 bytes
     const size_t stage_bytes = (size_t)P.T * 4;
@@ -87,7 +100,7 @@ cudaError_t launch_col_static(const LinePlan& lp, const ColParams& P, bool packe
       lp, P, S::NT, num_sms, s);
 }
 
-template cudaError_t launch_row_static<GBLUR_TU_SHAPE>(const LinePlan&, const RowParams&, bool, bool, int,
+template cudaError_t launch_row_static<GBLUR_TU_SHAPE>(const LinePlan&, const RowParams&, int, bool, int,
                                                        cudaStream_t);
 template cudaError_t launch_col_static<GBLUR_TU_SHAPE>(const LinePlan&, const ColParams&, bool, int, int,
                                                        cudaStream_t);

@@ -341,3 +341,40 @@ def test_batch_longer_than_plan_is_streamed(gb, refcheck):
     plan.close()
     for f in range(7):
         _assert_close_u8(out[f], refcheck.blur(frames[f], 6.0, False), f"streamed frame {f}")
+
+
+@pytest.mark.parametrize("rows,cols,ch,alpha", [(1081, 1920, 3, False), (1082, 1920, 3, False), (1083, 1918, 3, False),
+                                                (1080, 1920, 4, False), (271, 1900, 4, False)])
+def test_three_channel_row_problem_n2048(gb, refcheck, rows, cols, ch, alpha):
+    """Row FFT length 2048 (the 1080p shape) with three processed channels: the specialised row problem
+    (two image rows per unit, staged through shared memory when the rows are 16-byte aligned), every tail
+    phase of rows*3 mod 4, unaligned rows (no staging), and RGBA with the alpha plane left alone."""
+    import os
+    sigma = 5.0
+    assert gb.host_plan_sizes(rows, cols, sigma)["n_rowpass"] == 2048
+    img = go.synth_u8((rows, cols, ch), rows + cols)
+    out, _, rad = _blur_gpu(gb, img, sigma, alpha)
+    assert rad[0][1], "compile-time row kernel expected"
+    _assert_close_u8(out, refcheck.blur(img, sigma, alpha), f"{rows}x{cols}x{ch}")
+    if ch == 4:
+        assert np.array_equal(out[..., 3], img[..., 3])
+    os.environ["GBLUR_NO_RGB3"] = "1"  # same lines paired the same way: the general row problem gives the same bits
+    try:
+        out2, _, _ = _blur_gpu(gb, img, sigma, alpha)
+    finally:
+        del os.environ["GBLUR_NO_RGB3"]
+    assert np.array_equal(out, out2)
+
+
+def test_three_channel_row_problem_batch_straddles_frames(gb, refcheck):
+    """Frames stacked as extra rows: with 5 rows x 3 channels per frame a unit of four lines crosses frame
+    boundaries; runtime-radix kernel (N = 160) and compile-time kernel (N = 2048)."""
+    for rows, cols, sigma in ((5, 150, 1.0), (33, 1920, 5.0)):
+        frames = 3
+        batch = go.synth_u8((frames, rows, cols, 3), 4242 + cols)
+        plan = gb.Plan(rows, cols, 3, sigma, max_frames=frames)
+        out = batch.copy()
+        plan.run_host(out, False, n_frames=frames)
+        plan.close()
+        for f in range(frames):
+            _assert_close_u8(out[f], refcheck.blur(batch[f], sigma, False), f"frame {f} of {rows}x{cols}")
