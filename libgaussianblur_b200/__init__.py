@@ -287,18 +287,67 @@ def ipc_close(d_ptr: int) -> None:
     _check(lib().gblur_ipc_close(C.c_void_p(d_ptr)))
 
 
-def gaussianblur(img: np.ndarray, sigma: float, apply_to_alpha: bool = False, device: int = 0) -> np.ndarray:
-    """Blur an HWC (channels 3/4) or HW uint8 numpy array in place on the GPU and return it.
+def _device_view(obj):
+    """(device pointer, shape, device index or None, stream handle or None) when `obj` lives in GPU memory:
+    a torch CUDA tensor or anything exporting __cuda_array_interface__ (CuPy, Numba, ...). None for host data."""
+    if hasattr(obj, "is_cuda") and hasattr(obj, "data_ptr"):
+        if not obj.is_cuda:
+            return None
+        if str(obj.dtype) != "torch.uint8" or not obj.is_contiguous():
+            raise TypeError("device tensor must be contiguous uint8")
+        return obj.data_ptr(), tuple(obj.shape), obj.device.index, None
+    cai = getattr(obj, "__cuda_array_interface__", None)
+    if cai is None:
+        return None
+    shape = tuple(cai["shape"])
+    if cai["typestr"] not in ("|u1", "<u1", "u1"):
+        raise TypeError("device array must be uint8")
+    strides = cai.get("strides")
+    if strides is not None:
+        want, acc = [], 1
+        for n in reversed(shape):
+            want.append(acc)
+            acc *= n
+        if tuple(strides) != tuple(reversed(want)):
+            raise TypeError("device array must be C-contiguous")
+    if cai["data"][1]:
+        raise TypeError("device array is read-only")
+    return int(cai["data"][0]), shape, None, cai.get("stream")
+
+
+def gaussianblur(img, sigma: float, apply_to_alpha: bool = False, device: int = 0):
+    """Blur an HWC (channels 3/4) or HW uint8 image in place on the GPU and return it.
+
+    `img` is a numpy array or a pinned/pageable torch CPU tensor (copied to the GPU and back, pipelined),
+    or — zero copy — a torch CUDA tensor / any object with __cuda_array_interface__: the kernels then
+    read and write the caller's device memory directly, stream-ordered on the caller's current stream.
+    The reference's Python surface moves pixels through list[int] <-> std::vector<uint8_t>
+    (/root/reference/python/bindings/gaussianblur_py.cpp:20); this entry point never touches them on the host.
     Error behaviour follows gaussianblur::gaussianblur (/root/reference/src/gaussianblur.cpp:307-317):
     sigma <= 0 or an unsupported channel count leaves the data untouched."""
     if sigma <= 0:
         print("Invalid smoothing factor")
         return img
-    ch = 1 if img.ndim == 2 else img.shape[2]
+    dev = _device_view(img)
+    shape = dev[1] if dev else tuple(img.shape)
+    if len(shape) not in (2, 3):
+        raise ValueError("expected an HW or HWC image")
+    ch = 1 if len(shape) == 2 else shape[2]
     if ch not in (1, 3, 4):
         print("Unsupported number of channels", file=sys.stderr)
         return img
-    plan = Plan(img.shape[0], img.shape[1], ch, sigma, device=device)
+    if dev:
+        ptr, _, index, stream = dev
+        plan = Plan(shape[0], shape[1], ch, sigma, device=device if index is None else index)
+        try:
+            st = C.c_void_p(int(stream)) if isinstance(stream, int) and stream > 2 else \
+                (C.c_void_p(0) if index is None else _stream_ptr(None))
+            _check(lib().gblur_run_batch_device(plan._h, C.c_void_p(ptr), C.c_void_p(ptr), 1,
+                                                int(bool(apply_to_alpha)), st))
+        finally:
+            plan.close()  # plan destruction waits for the work queued on it
+        return img
+    plan = Plan(shape[0], shape[1], ch, sigma, device=device)
     try:
         plan.run_host(img, apply_to_alpha)
     finally:

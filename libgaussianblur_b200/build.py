@@ -5,6 +5,7 @@
 Outputs (git-ignored, but they travel to the GPU box with the snapshot):
     libgaussianblur_b200/lib/libgblur_b200.so          C ABI (include/gblur_capi.h) + C++ API
     libgaussianblur_b200/lib/gaussianblur.<abi>.so     pybind11 module mirroring the reference's
+    libgaussianblur_b200/lib/gaussianblur              desktop command line (examples/desktop/main.cpp)
 Every CUDA translation unit is compiled with
     nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo
 static_impl.cu is compiled once per compile-time FFT shape (static_shapes.h) so the shapes
@@ -40,7 +41,8 @@ def _static_ids():
 
 def _sources_digest(extra: str = "") -> str:
     h = hashlib.sha256(extra.encode())
-    for d in (CSRC, os.path.join(ROOT, "include"), os.path.join(ROOT, "include", "gaussianblur")):
+    for d in (CSRC, os.path.join(ROOT, "include"), os.path.join(ROOT, "include", "gaussianblur"),
+              os.path.join(ROOT, "examples", "desktop")):
         if not os.path.isdir(d):
             continue
         for f in sorted(os.listdir(d)):
@@ -68,12 +70,17 @@ def pymod_path() -> str:
     return os.path.join(LIB, "gaussianblur" + sysconfig.get_config_var("EXT_SUFFIX"))
 
 
+def cli_path() -> str:
+    return os.path.join(LIB, "gaussianblur")
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ, exist_ok=True)
     os.makedirs(LIB, exist_ok=True)
     stamp = os.path.join(LIB, "build.stamp")
     digest = _sources_digest()
-    if (not force and os.path.exists(lib_path()) and os.path.exists(pymod_path()) and os.path.exists(stamp)
+    if (not force and os.path.exists(lib_path()) and os.path.exists(pymod_path()) and os.path.exists(cli_path())
+            and os.path.exists(stamp)
             and open(stamp).read().strip() == digest):
         return lib_path()
     if not os.path.exists(NVCC):
@@ -112,6 +119,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
           "-I", os.path.join(ROOT, "include"), "-I", pybind11.get_include(), "-I", py_inc,
           os.path.join(CSRC, "pybind_module.cpp"), "-L", LIB, "-lgblur_b200", "-Wl,-rpath,$ORIGIN",
           "-o", pymod_path()], os.path.join(OBJ, "pybind.log"))
+    # desktop command line with the reference's usage (examples/desktop/main.cpp)
+    _run([cxx, "-std=c++17", "-O2", "-I", os.path.join(ROOT, "include"),
+          os.path.join(ROOT, "examples", "desktop", "main.cpp"), "-L", LIB, "-lgblur_b200", "-Wl,-rpath,$ORIGIN",
+          "-o", cli_path()], os.path.join(OBJ, "cli.log"))
     with open(stamp, "w") as fh:
         fh.write(digest)
     return lib_path()

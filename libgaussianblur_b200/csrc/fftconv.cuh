@@ -219,7 +219,11 @@ __device__ __forceinline__ void inv_stage(const Storer& st, typename SmemElem<NS
         for (int q = 0; q < NSEQ; ++q) c[q][j] = cmulc(p.v[q], w);
       }
     }
-    if constexpr (FINAL && Storer::kTmaNext) st.after_reads();  // exactly one butterfly per thread here
+    // the buffer is dead once the LAST pass has read its slots (nb is a multiple of the CTA size for these
+    // problems, so every thread reaches the barrier inside after_reads)
+    if constexpr (FINAL && Storer::kTmaNext) {
+      if (u + nthreads >= nb) st.after_reads();
+    }
     if constexpr (FINAL && Storer::kPrefetch) {
       // the slots this thread just read are dead for the current unit: refill them, asynchronously,
       // with the next unit's samples while the last butterflies and the global stores run

@@ -84,7 +84,7 @@ __global__ void __maxnreg__(MAXREG)
     }
   }
   if constexpr (Problem::kTmaIn) {
-    static_assert(SS::M0 == NT, "TMA prefetch needs one last-stage butterfly per thread");
+    static_assert(SS::M0 % NT == 0, "TMA prefetch needs whole passes of last-stage butterflies");
     if (threadIdx.x == 0) {
       mbar_init(&tma_bar, 1);
       fence_proxy_async();

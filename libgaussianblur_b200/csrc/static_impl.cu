@@ -77,7 +77,7 @@ cudaError_t launch_col_static(const LinePlan& lp, const ColParams& P, bool packe
   using S = ShapeOf<ID>;
   using SS = typename S::SS;
   constexpr int Q = S::NSEQ;
-  if constexpr (SS::M0 == S::NT) {  // one last-stage butterfly per thread: the TMA prefetch protocol applies
+  if constexpr (SS::M0 % S::NT == 0) {  // whole passes of last-stage butterflies: the TMA prefetch protocol applies
     if (input == 2) {
       if (packed)
         return launch_line<line_kernel_static<Q, SS, S::NT, S::MAXREG, ColProblem<Q, true, true, true>, ColParams>>(

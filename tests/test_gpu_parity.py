@@ -378,3 +378,34 @@ def test_three_channel_row_problem_batch_straddles_frames(gb, refcheck):
         plan.close()
         for f in range(frames):
             _assert_close_u8(out[f], refcheck.blur(batch[f], sigma, False), f"frame {f} of {rows}x{cols}")
+
+
+def test_python_zero_copy_device_arrays(gb, refcheck):
+    """gaussianblur() on GPU-resident pixels — a torch CUDA tensor and a bare
+    __cuda_array_interface__ exporter — blurs the caller's device memory in place, no host round trip."""
+    import torch
+
+    img = go.synth_u8((211, 317, 4), 77)
+    want = refcheck.blur(img, 4.0, True)
+    t = torch.from_numpy(img).cuda()
+    assert gb.gaussianblur(t, 4.0, True) is t
+    torch.cuda.synchronize()
+    _assert_close_u8(t.cpu().numpy(), want, "torch CUDA tensor")
+
+    class Exporter:  # what CuPy / Numba arrays look like to a consumer
+        def __init__(self, tensor):
+            self._keep = tensor
+            self.__cuda_array_interface__ = {"shape": tuple(tensor.shape), "typestr": "|u1", "version": 3,
+                                             "data": (tensor.data_ptr(), False), "strides": None}
+
+    t2 = torch.from_numpy(img).cuda()
+    torch.cuda.synchronize()
+    gb.gaussianblur(Exporter(t2), 4.0, True)
+    torch.cuda.synchronize()
+    assert torch.equal(t, t2)
+    with pytest.raises(TypeError):
+        gb.gaussianblur(torch.zeros((8, 8, 3), dtype=torch.float32, device="cuda"), 1.0)
+    # reference no-op cases keep their behaviour on device data too
+    t3 = torch.from_numpy(img).cuda()
+    gb.gaussianblur(t3, 0.0, True)
+    assert torch.equal(t3.cpu(), torch.from_numpy(img))
