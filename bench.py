@@ -259,8 +259,8 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier):
         h2d = d2h = band.numel()
         closer = plan.close
     else:
-        bs = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, device=local, fused=(args.exchange == "fused"),
-                                  pipeline_chunks=(args.pipeline_chunks if args.exchange == "nccl_pipelined" else 0))
+        bs = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, device=local, fused=(args.exchange if args.exchange in ("staged", "hybrid") else args.exchange == "fused"),
+                                  pipeline_chunks=(args.pipeline_chunks if args.exchange in ("nccl_pipelined", "staged", "hybrid") else 0))
         step = lambda: bs.run(band)
         h_out = torch.empty((rows, bs.my_cols[1] - bs.my_cols[0], ch), dtype=torch.uint8).pin_memory()
 
@@ -295,7 +295,7 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier):
             torch.cuda.synchronize()
             phases[name] = k0.elapsed_time(k1) / args.steps
     else:
-        if bs.fused_run is not None and args.exchange == "fused":
+        if bs.fused_run is not None and args.exchange in ("fused", "staged", "hybrid"):
             bs.profile = True
             step()
             torch.cuda.synchronize()
@@ -359,9 +359,10 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--chunk-frames", type=int, default=16, help="frames per launch in the video workload")
     ap.add_argument("--force-band", action="store_true", help="band workloads at 1 GPU: run the band-sharded path anyway")
-    ap.add_argument("--pipeline-chunks", type=int, default=4)
-    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl", "nccl_pipelined"],
-                    help="band workloads: row pass stores into peer memory (fused) or NCCL all-to-all")
+    ap.add_argument("--pipeline-chunks", type=int, default=8)
+    ap.add_argument("--exchange", default="staged", choices=["fused", "staged", "hybrid", "nccl", "nccl_pipelined"],
+                    help="band workloads: row pass stores into peer memory (fused), local row pass in chunks with "
+                         "copy-engine pushes into the owners' panel buffers (staged), or NCCL all-to-all")
     args = ap.parse_args()
     wl = args.workload
     if args.impl == "reference":

@@ -110,6 +110,14 @@ int gblur_rowpass_peer_device(gblur_plan* row_plan, const uint8_t* d_in, float* 
                               int row_offset, int apply_to_alpha, void* cuda_stream);
 int gblur_colpass_panel_device(gblur_plan* col_plan, const float* d_panel, uint8_t* d_out, long long out_pitch_bytes,
                                int apply_to_alpha, void* cuda_stream);
+/* Staged variant of the same exchange (copy engines instead of peer stores): the row pass stores into LOCAL
+ * buffers with the panel geometry of each destination rank (pass them to gblur_rowpass_peer_device as the
+ * "peers"), and this call then moves the slots [slot_begin, slot_end) of the padded column lines (slot = pad +
+ * image row; reflect_101 mirror slots lie in [0, pad) and [pad + rows, pad + rows + pad)) of every panel from
+ * src_panel to dst_panel — one strided device-to-device copy, asynchronous on cuda_stream, dst_panel usually the
+ * IPC mapping of the owner's panel buffer (NVLink). Row chunks can travel while the next chunk is computed. */
+int gblur_panel_push_device(const gblur_plan* col_plan, int apply_to_alpha, const float* src_panel, float* dst_panel,
+                            int slot_begin, int slot_end, void* cuda_stream);
 
 /* Test hook: fp32 row-pass output of the last gblur_run_* call on this plan (frame 0), copied to
  * host as [rows][cols*Cp]. */

@@ -29,7 +29,7 @@ EXPORTED_SYMBOLS = [
     "gblur_plan_info", "gblur_plan_spectrum", "gblur_plan_radices", "gblur_run_host", "gblur_run_batch_host",
     "gblur_run_device", "gblur_run_batch_device", "gblur_run_stage_device", "gblur_rowpass_device", "gblur_rowpass_split_device", "gblur_colpass_device",
     "gblur_plan_panel_geometry", "gblur_band_panel_alloc", "gblur_ipc_export", "gblur_ipc_open", "gblur_ipc_close",
-    "gblur_rowpass_peer_device", "gblur_colpass_panel_device",
+    "gblur_rowpass_peer_device", "gblur_colpass_panel_device", "gblur_panel_push_device",
     "gblur_dump_intermediate", "gblur_launch_count", "gblur_last_error", "gblur_device_count",
     "gblur_host_plan_sizes", "gblur_host_taps", "gblur_host_spectrum", "gblur_host_line_plan", "gblur_host_kperm",
 ]
@@ -79,6 +79,7 @@ def lib():
         "gblur_ipc_close": (C.c_int, [vp]),
         "gblur_rowpass_peer_device": (C.c_int, [vp, u8p, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, vp]),
         "gblur_colpass_panel_device": (C.c_int, [vp, vp, u8p, ll, C.c_int, vp]),
+        "gblur_panel_push_device": (C.c_int, [vp, C.c_int, vp, vp, C.c_int, C.c_int, vp]),
         "gblur_dump_intermediate": (C.c_int, [vp, fp, C.c_int]),
         "gblur_launch_count": (C.c_ulonglong, []),
         "gblur_last_error": (C.c_char_p, []),
@@ -262,6 +263,13 @@ class Plan:
                 stream=None):
         _check(lib().gblur_colpass_device(self._h, _ptr(d_inter), inter_pitch_floats, _ptr(d_out), out_pitch_bytes,
                                           int(bool(apply_to_alpha)), _stream_ptr(stream)))
+
+    def panel_push(self, src_panel: int, dst_panel: int, slot_begin: int, slot_end: int, apply_to_alpha: bool = False,
+                   stream=None):
+        """Copy slots [slot_begin, slot_end) of every panel from one panel buffer to another (column-band plan);
+        dst may be the IPC mapping of a peer's buffer. Asynchronous on `stream`."""
+        _check(lib().gblur_panel_push_device(self._h, int(bool(apply_to_alpha)), C.c_void_p(src_panel),
+                                             C.c_void_p(dst_panel), slot_begin, slot_end, _stream_ptr(stream)))
 
     def dump_intermediate(self, apply_to_alpha: bool = False) -> np.ndarray:
         cp = self.processed_channels(apply_to_alpha)

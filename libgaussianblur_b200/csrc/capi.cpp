@@ -694,6 +694,25 @@ int gblur_rowpass_peer_device(gblur_plan* p, const uint8_t* d_in, float* const* 
   return GBLUR_OK;
 }
 
+int gblur_panel_push_device(const gblur_plan* p, int apply_to_alpha, const float* src_panel, float* dst_panel,
+                            int slot_begin, int slot_end, void* cuda_stream) {
+  if (!p || !src_panel || !dst_panel) return fail(GBLUR_E_INVALID, "null argument");
+  int np, padq;
+  panel_geometry(p, &np, &padq);
+  const int n_slots = p->sz.n_colpass;
+  if (slot_begin < 0 || slot_end > n_slots || slot_begin > slot_end) return fail(GBLUR_E_INVALID, "slot range outside the padded line");
+  if (slot_begin == slot_end) return GBLUR_OK;
+  DeviceGuard guard(p->device);
+  const int cp = processed_channels(p, apply_to_alpha);
+  const long long panels = ((long long)p->cols * cp + 31) / 32;
+  auto physical = [padq](long long n) { return padq ? n + n / padq : n; };  // fftconv.cuh phys()
+  const long long first = physical(slot_begin), last = physical(slot_end - 1);  // padding holes inside travel too (zeros)
+  const size_t pitch = (size_t)np * 128, width = (size_t)(last - first + 1) * 128;
+  CU(cudaMemcpy2DAsync(dst_panel + first * 32, pitch, src_panel + first * 32, pitch, width, (size_t)panels,
+                       cudaMemcpyDefault, static_cast<cudaStream_t>(cuda_stream)));
+  return GBLUR_OK;
+}
+
 int gblur_colpass_panel_device(gblur_plan* p, const float* d_panel, uint8_t* d_out, long long out_pitch_bytes,
                                int apply_to_alpha, void* cuda_stream) {
   if (!p || !d_panel || !d_out) return fail(GBLUR_E_INVALID, "null argument");

@@ -15,6 +15,7 @@ exchange without a GPU. There is no CPU compute path in this module.
 """
 from __future__ import annotations
 
+import os
 from typing import Callable, List, Sequence, Tuple
 
 import torch
@@ -239,12 +240,66 @@ class BandShardedBlur:
                     e.record()
                     self.marks.append(e)
 
+            staged = fused in ("staged", "hybrid") and world > 1
+            hybrid = fused == "hybrid"  # every other chunk stores straight into the peers: SM stores and copy engines share the load
+            if staged:
+                # Staged exchange: the row pass stores into LOCAL buffers with each destination's panel geometry,
+                # in K row chunks; copy engines push chunk k's slots into the owners' panel buffers over NVLink
+                # while chunk k+1 is computed. The SMs never wait on remote stores.
+                K = max(1, min(pipeline_chunks or 4, r1 - r0))
+                local = [panel_ptr if h == rank else p_col.panel_alloc(apply_to_alpha)[0] for h in range(world)]
+                chunk_plans = [gb.Plan(rows, cols, channels, sigma, device=device,
+                                       band_rows=shard_range(r1 - r0, K, k)[1] - shard_range(r1 - r0, K, k)[0],
+                                       band_cols=cols) for k in range(K)]
+                self.plans = (p_row, p_col, *chunk_plans)
+                n_streams = int(os.environ.get("GBLUR_STAGED_STREAMS", world - 1))  # one per peer unless overridden
+                copy_streams = [torch.cuda.Stream(device=dev) for _ in range(max(1, min(n_streams, world - 1)))]
+                order = [(rank + 1 + i) % world for i in range(world - 1)]  # spread the first pushes over the links
+                pad = p_col.pad
+
+                def mirror_slots(lo_row: int, hi_row: int):
+                    """reflect_101 mirror slots written by image rows [lo_row, hi_row) (problems.cuh make_blocked_dst)."""
+                    out = []
+                    lo, hi = max(lo_row, 1), min(hi_row - 1, pad)
+                    if lo <= hi:
+                        out.append((pad - hi, pad - lo + 1))
+                    lo, hi = max(lo_row, rows - 1 - pad), min(hi_row - 1, rows - 2)
+                    if lo <= hi:
+                        out.append((pad + 2 * rows - 2 - hi, pad + 2 * rows - 2 - lo + 1))
+                    return out
+
+                def push(slot_a: int, slot_b: int, ev):
+                    for i, h in enumerate(order):
+                        st = copy_streams[i % len(copy_streams)]
+                        st.wait_event(ev)
+                        p_col.panel_push(local[h], peers[h], slot_a, slot_b, apply_to_alpha, stream=st)
+
+                def staged_rowpass(band: torch.Tensor):
+                    comp = torch.cuda.current_stream()
+                    for k, pk in enumerate(chunk_plans):
+                        a, b = shard_range(r1 - r0, K, k)
+                        if hybrid and (K - 1 - k) % 2 == 0:  # the last chunk goes direct: no push tail after it
+                            pk.rowpass_peer(band[a:b], peers, r0 + a, apply_to_alpha)
+                            continue
+                        pk.rowpass_peer(band[a:b], local, r0 + a, apply_to_alpha)
+                        ev = torch.cuda.Event()
+                        ev.record(comp)
+                        push(pad + r0 + a, pad + r0 + b, ev)
+                        for m0, m1 in mirror_slots(r0 + a, r0 + b):
+                            push(m0, m1, ev)
+                    mark()  # the band's row pass is done; pushes of the last chunks are still in flight
+                    for st in copy_streams:
+                        comp.wait_stream(st)
+
             def fused_run(band: torch.Tensor) -> torch.Tensor:
                 self.marks = []
                 mark()
                 fence()  # every rank has finished the previous column pass
                 mark()
-                p_row.rowpass_peer(band, peers, r0, apply_to_alpha)
+                if staged:
+                    staged_rowpass(band)
+                else:
+                    p_row.rowpass_peer(band, peers, r0, apply_to_alpha)
                 mark()
                 fence()  # every rank's row pass (and its peer stores) has completed
                 mark()
@@ -256,7 +311,11 @@ class BandShardedBlur:
                 return out
 
             self.fused_run = fused_run
-            self.exchange_kind = "fused peer stores (NVLink), no collective on the data path"
+            self.exchange_kind = ((f"hybrid: row pass in {K} chunks, alternately peer stores and " if hybrid else
+                                   f"staged: local row pass in {K} chunks, ") +
+                                  "copy-engine pushes into the owners' panel buffers (NVLink), no collective on the "
+                                  "data path") if staged else \
+                "fused peer stores (NVLink), no collective on the data path"
         else:
             self.exchange_kind = "NCCL all-to-all"
         return self
@@ -265,7 +324,9 @@ class BandShardedBlur:
         """After a profiled fused run (and a synchronize): ms spent in fence, row pass, fence, column pass."""
         m = self.marks
         names = ["fence_before", "row_pass_peer_stores", "fence_after", "col_pass"]
-        return {n: m[i].elapsed_time(m[i + 1]) for i, n in enumerate(names)} if len(m) == 5 else {}
+        if len(m) == 6:  # staged exchange: the row pass is local, the tail is what the copy engines still owe
+            names = ["fence_before", "row_pass_local_chunks", "push_tail", "fence_after", "col_pass"]
+        return {n: m[i].elapsed_time(m[i + 1]) for i, n in enumerate(names)} if len(m) == len(names) + 1 else {}
 
     def _exchange_alpha(self, band: torch.Tensor) -> torch.Tensor:
         """The un-blurred alpha bytes of all rows for my column band (u8 all-to-all)."""

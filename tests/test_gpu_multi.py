@@ -41,6 +41,21 @@ for ch, alpha in ((1, False), (4, False)):
     d = np.abs(out.cpu().numpy().astype(int) - want.reshape(rows, cols, ch)[r0:r1].astype(int)).max()
     assert d <= 1, ("pipelined", ch, d)
     b.close()
+for ch, alpha, chunks, sigma, kind in ((1, False, 3, 6.0, "staged"), (3, False, 1, 6.0, "staged"), (4, True, 4, 6.0, "staged"),
+                                       (1, False, 2, 40.0, "staged"), (1, False, 4, 40.0, "hybrid"), (3, False, 5, 6.0, "hybrid")):
+    rows, cols = 250, 384  # sigma=40: pad 132 > the 125-row bands, so both ranks write reflect_101 mirror slots
+    img = go.synth_u8((rows, cols, ch) if ch > 1 else (rows, cols), 19 + ch)
+    want = (ref_lib.gaussianblur(img, sigma, alpha) if ch > 1 else ref_lib.blur_plane_u8(img, sigma)) if ref_lib.available() else go.gaussianblur(img, sigma, alpha)
+    b = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, device=local, fused=kind, pipeline_chunks=chunks)
+    assert kind in b.exchange_kind
+    r0, r1 = b.my_rows
+    band = torch.from_numpy(img.reshape(rows, cols, ch)[r0:r1].copy()).cuda()
+    for rep in range(2):  # the second image reuses the staging and panel buffers
+        out = b.run(band, gather_rows=True)
+        torch.cuda.synchronize()
+        d = np.abs(out.cpu().numpy().astype(int) - want.reshape(rows, cols, ch)[r0:r1].astype(int)).max()
+        assert d <= 1, (kind, ch, chunks, rep, d)
+    b.close()
 fs = FrameShardedBlur(6, 135, 240, 3, 5.0, device=local, chunk_frames=2)
 f0, f1 = fs.frames
 frames = np.stack([go.synth_u8((135, 240, 3), 100 + f) for f in range(6)])
