@@ -53,6 +53,39 @@ def _sources_digest(extra: str = "") -> str:
     return h.hexdigest()
 
 
+def _deps_digest(src: str, cmd) -> str:
+    """sha256 of the command line, the source and every quoted/bracketed header it reaches inside
+    csrc/ and include/ (so a change to one kernel file rebuilds only the objects that see it)."""
+    roots = [CSRC, os.path.join(ROOT, "include")]
+    seen, todo = set(), [src]
+    h = hashlib.sha256(" ".join(cmd).encode())
+    while todo:
+        f = todo.pop()
+        if f in seen or not os.path.isfile(f):
+            continue
+        seen.add(f)
+        txt = open(f, "rb").read()
+        h.update(os.path.basename(f).encode())
+        h.update(txt)
+        for inc in re.findall(rb'^\s*#\s*include\s*[<"]([^>"]+)[>"]', txt, flags=re.M):
+            name = inc.decode()
+            for d in [os.path.dirname(f)] + roots:
+                todo.append(os.path.normpath(os.path.join(d, name)))
+    return h.hexdigest()
+
+
+def _run_cached(cmd, obj, src):
+    """compile `src` to `obj` unless an object built from identical inputs is already there"""
+    tag = obj + ".dep"
+    digest = _deps_digest(src, cmd)
+    if os.path.exists(obj) and os.path.exists(tag) and open(tag).read().strip() == digest:
+        return None
+    r = _run(cmd, obj + ".log")
+    with open(tag, "w") as fh:
+        fh.write(digest)
+    return r
+
+
 def _run(cmd, log):
     r = subprocess.run(cmd, capture_output=True, text=True)
     with open(log, "w") as fh:
@@ -79,6 +112,10 @@ def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(LIB, exist_ok=True)
     stamp = os.path.join(LIB, "build.stamp")
     digest = _sources_digest()
+    if force:
+        for f in os.listdir(OBJ):
+            if f.endswith(".dep"):
+                os.remove(os.path.join(OBJ, f))
     if (not force and os.path.exists(lib_path()) and os.path.exists(pymod_path()) and os.path.exists(cli_path())
             and os.path.exists(stamp)
             and open(stamp).read().strip() == digest):
@@ -86,27 +123,28 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not os.path.exists(NVCC):
         raise RuntimeError(f"nvcc not found at {NVCC}; cannot build the sm_100a library")
 
-    jobs = []  # (name, cmd)
-    for name in ("kernels.cu", "generic_row.cu", "generic_col.cu", "cluster_kernels.cu"):
+    jobs = []  # (object, cmd, source)
+    for name in ("kernels.cu", "generic_row.cu", "generic_col.cu", "cluster_kernels.cu", "ols_kernels.cu"):
         o = os.path.join(OBJ, name.replace(".cu", ".o"))
-        jobs.append((o, [NVCC, *ARCH, *COMMON, "-c", os.path.join(CSRC, name), "-o", o]))
+        jobs.append((o, [NVCC, *ARCH, *COMMON, "-c", os.path.join(CSRC, name), "-o", o], os.path.join(CSRC, name)))
     for sid in _static_ids():
         o = os.path.join(OBJ, f"static_{sid}.o")
         jobs.append((o, [NVCC, *ARCH, *COMMON, f"-DGBLUR_TU_SHAPE={sid}", "-c",
-                         os.path.join(CSRC, "static_impl.cu"), "-o", o]))
+                         os.path.join(CSRC, "static_impl.cu"), "-o", o], os.path.join(CSRC, "static_impl.cu")))
     for name in ("capi.cpp", "gaussianblur_api.cpp"):
         o = os.path.join(OBJ, name.replace(".cpp", ".o"))
-        jobs.append((o, [NVCC, *COMMON, "-c", os.path.join(CSRC, name), "-o", o]))  # host-only TU
+        jobs.append((o, [NVCC, *COMMON, "-c", os.path.join(CSRC, name), "-o", o],
+                     os.path.join(CSRC, name)))  # host-only TU
 
     workers = max(1, min(len(jobs), os.cpu_count() or 1))
     with cf.ThreadPoolExecutor(workers) as ex:
-        futs = {ex.submit(_run, cmd, o + ".log"): o for o, cmd in jobs}
+        futs = {ex.submit(_run_cached, cmd, o, src): o for o, cmd, src in jobs}
         for f in cf.as_completed(futs):
             f.result()
             if verbose:
                 print("built", os.path.basename(futs[f]), flush=True)
 
-    objs = [o for o, _ in jobs]
+    objs = [o for o, _, _ in jobs]
     _run([NVCC, *ARCH, "-shared", "-Xcompiler", "-fPIC", "-cudart", "static", *objs, "-o", lib_path()],
          os.path.join(OBJ, "link.log"))
 

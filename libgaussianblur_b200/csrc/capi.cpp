@@ -15,6 +15,7 @@
 #include "../../include/gblur_capi.h"
 #include "hostsem.hpp"
 #include "kernels.h"
+#include "ols.h"
 #include "planner.hpp"
 
 using namespace gblur;
@@ -87,6 +88,8 @@ struct gblur_plan {
   int last_cp = 0;       // processed channels of the last run (layout of d_inter)
   int inter_cp = 0;      // processed-channel count the blocked workspace is currently laid out for
   int last_frames = 0;
+  // overlap-save row pass (ols.h); only created when GBLUR_ROW_OLS=1 is set at plan creation (experimental)
+  ols::RowPlan* ols_row = nullptr;
 };
 
 namespace {
@@ -187,6 +190,13 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
     rc = fail(GBLUR_E_CUDA, "cudaStreamCreate failed");
   if (rc == GBLUR_OK) rc = build_tables(p->row, sz.n_rowpass, taps, 1);
   if (rc == GBLUR_OK) rc = build_tables(p->col, sz.n_colpass, taps, 2);
+  if (rc == GBLUR_OK) {
+    const char* e = getenv("GBLUR_ROW_OLS");
+    if (e && atoi(e) > 0 && channels == 4) {
+      const cudaError_t ce = ols::row_plan_create(&p->ols_row, taps, sz.n_rowpass);
+      if (ce != cudaSuccess) rc = fail(GBLUR_E_CUDA, "overlap-save row plan: %s", cudaGetErrorString(ce));
+    }
+  }
   if (rc != GBLUR_OK) {
     std::string keep = g_err;
     gblur_plan_destroy(p);
@@ -222,6 +232,10 @@ int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pi
       a.row_offset = row0;  // panel layout: the slot index carries the row
     else
       a.inter = d_inter + (long long)row0 * pitch;
+  }
+  if (p->ols_row && ols::row_eligible(p->ols_row, a)) {
+    CU(ols::launch_row(p->ols_row, a, p->num_sms, s));
+    return GBLUR_OK;
   }
   CU(launch_rowpass(p->row.lp, a, p->num_sms, s));
   return GBLUR_OK;
@@ -316,6 +330,7 @@ void gblur_plan_destroy(gblur_plan* p) {
   if (p->stream) cudaStreamSynchronize(p->stream);
   free_tables(p->row);
   free_tables(p->col);
+  ols::row_plan_destroy(p->ols_row);
   if (p->d_inter) cudaFree(p->d_inter);
   if (p->d_stage) cudaFree(p->d_stage);
   if (p->d_stage2) cudaFree(p->d_stage2);

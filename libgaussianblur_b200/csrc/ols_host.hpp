@@ -1,0 +1,46 @@
+// ols_host.hpp — host-only tables of the overlap-save row pass (ols_core.cuh): the 32 x 32 twiddles, the
+// block gains K_1024[k] / 1024 of the reference's centred taps (src/gaussianblur.cpp:28-60) and the
+// coefficient of the reference's Nyquist term for its own transform length N (src/gaussianblur.cpp:62-79
+// with pffft.h:143-146).
+#pragma once
+#include <cmath>
+#include <vector>
+
+#include "hostsem.hpp"
+
+namespace gblur {
+namespace ols {
+
+struct HostTables {
+  std::vector<float> tw;     // 1024 complex values, tw[a*32+b] = exp(-2 pi i a b / 1024)
+  std::vector<float> gains;  // 32 rows of 36 floats, gains[k1*36 + k2] = K_1024[k1 + 32 k2] / 1024
+  float q = 0.f;             // (K_N[0] - K_N[N/2]) / N
+};
+
+// taps.size() must not exceed 1024 - 512 + 1 (pad <= 256)
+inline HostTables build_tables(const std::vector<float>& taps, int n_ref) {
+  constexpr int NB = 1024, R = 32, GS = 36;
+  constexpr double two_pi = 6.28318530717958647692528676655900577;
+  HostTables t;
+  t.tw.resize(2 * NB);
+  for (int a = 0; a < R; ++a)
+    for (int b = 0; b < R; ++b) {
+      const double ang = two_pi * (double)((a * b) % NB) / (double)NB;
+      t.tw[2 * (a * R + b)] = (float)std::cos(ang);
+      t.tw[2 * (a * R + b) + 1] = (float)(-std::sin(ang));
+    }
+  const std::vector<double> kb = host::kernel_gains(taps, NB);
+  t.gains.assign((size_t)R * GS, 0.0f);
+  for (int k1 = 0; k1 < R; ++k1)
+    for (int k2 = 0; k2 < R; ++k2) {
+      const int k = k1 + R * k2;
+      const int kk = k <= NB / 2 ? k : NB - k;
+      t.gains[(size_t)k1 * GS + k2] = (float)(kb[(size_t)kk] / (double)NB);
+    }
+  const std::vector<double> kn = host::kernel_gains(taps, n_ref);
+  t.q = (float)((kn[0] - kn[(size_t)n_ref / 2]) / (double)n_ref);
+  return t;
+}
+
+}  // namespace ols
+}  // namespace gblur

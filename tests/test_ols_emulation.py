@@ -1,0 +1,100 @@
+"""Overlap-save row pass (csrc/ols_core.cuh, csrc/ols_kernels.cu), checked WITHOUT a GPU: the
+kernel's lane functions are plain C++ as well, so tests/cpp/ols_emulate.cpp runs them lane by lane on the host (same
+tables, same panel layout, same index maps) and this file compares the result with the float64 oracle of the
+reference's row pass (process_channel_tiles, /root/reference/src/gaussianblur.cpp:202-244, including the Nyquist
+behaviour of :62-79) and, where it was built, with the compiled reference itself.
+Tolerance: 5e-4 absolute on the fp32 intermediate (the bar tests/test_gpu_parity.py uses for the row pass)."""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import gblur_oracle as go
+from oracle import ref_lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+TOL = 5e-4
+
+
+@pytest.fixture(scope="module")
+def emu(tmp_path_factory):
+    so = tmp_path_factory.mktemp("ols") / "libols_emu.so"
+    cmd = ["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-w", "-I", "/usr/local/cuda/include",
+           "-I", os.path.join(ROOT, "libgaussianblur_b200", "csrc"), os.path.join(ROOT, "tests", "cpp", "ols_emulate.cpp"),
+           "-o", str(so)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    lib = ctypes.CDLL(str(so))
+    lib.ols_emulate_rowpass.restype = ctypes.c_int
+
+    def run(img, sigma, padq=0):
+        rows, cols, _ = img.shape
+        ksize, pad, n_rp, _, _, _ = go.plan_sizes(rows, cols, sigma)
+        img = np.ascontiguousarray(img)
+        out = np.empty((rows, cols * 4), np.float32)
+        rc = lib.ols_emulate_rowpass(img.ctypes.data_as(ctypes.c_void_p), rows, cols, ctypes.c_float(sigma), ksize, n_rp,
+                                     padq, out.ctypes.data_as(ctypes.c_void_p))
+        assert rc == 0, f"mirrored border slot mismatch ({rc})"
+        return out, ksize, pad, n_rp
+
+    return run
+
+
+def _oracle_rows(img, sigma, ksize, pad, n):
+    want = np.empty((img.shape[0], img.shape[1] * 4), np.float64)
+    for ch in range(4):
+        want[:, ch::4] = go.conv_lines(img[:, :, ch].astype(np.float64), sigma, ksize, pad, n)
+    return want
+
+
+@pytest.mark.parametrize("rows,cols,sigma,padq", [
+    (140, 2000, 20.0, 0),    # three blocks, last one partial
+    (150, 3000, 20.0, 18),   # panel slots with bank-padding holes (the 4608-point column plan's padq)
+    (40, 700, 5.0, 16),      # one block holds the whole padded row
+    (40, 994, 5.0, 0),       # cols == L: exactly one full block
+    (40, 995, 5.0, 0),       # one pixel into a second block
+    (340, 1500, 50.0, 0),    # pad = 165
+    (520, 1100, 76.0, 0),    # pad = 252, close to the widest window the 1024-sample block takes
+])
+def test_emulated_rowpass_matches_oracle(emu, rows, cols, sigma, padq):
+    img = go.synth_u8((rows, cols, 4), 0x51 + cols)
+    out, ksize, pad, n = emu(img, sigma, padq)
+    want = _oracle_rows(img, sigma, ksize, pad, n)
+    assert np.abs(out - want).max() <= TOL
+
+
+def test_emulated_rowpass_headline_width(emu):
+    """the 8K row: 7680 pixels, sigma 20 -> 9 blocks of 894 outputs against the reference's N = 8000"""
+    img = go.synth_u8((132, 7680, 4), 0x1236)
+    out, ksize, pad, n = emu(img, 20.0, 18)
+    assert (ksize, pad) == (131, 65)
+    want = _oracle_rows(img, 20.0, ksize, pad, n)
+    assert np.abs(out - want).max() <= TOL
+    if ref_lib.available():
+        ref = ref_lib.rowpass_plane(img, 2, 20.0)
+        assert np.abs(out[:, 2::4] - ref).max() <= TOL
+
+
+@pytest.mark.parametrize("pattern", ["altcols", "altrows", "checker", "const255", "impulse", "ramp"])
+def test_emulated_rowpass_adversarial(emu, pattern):
+    """alternating columns make the reference's Nyquist term as large as it gets"""
+    rows, cols, sigma = 136, 1203, 20.0
+    img = np.zeros((rows, cols, 4), np.uint8)
+    if pattern == "altcols":
+        img[:, ::2] = 255
+    elif pattern == "altrows":
+        img[::2] = 255
+    elif pattern == "checker":
+        img[::2, ::2] = 255
+        img[1::2, 1::2] = 255
+    elif pattern == "const255":
+        img[:] = 255
+    elif pattern == "impulse":
+        img[70, 600] = 255
+    else:
+        img[:] = (np.arange(cols) % 256).astype(np.uint8)[None, :, None]
+    out, ksize, pad, n = emu(img, sigma)
+    want = _oracle_rows(img, sigma, ksize, pad, n)
+    assert np.abs(out - want).max() <= TOL
