@@ -88,8 +88,10 @@ struct gblur_plan {
   int last_cp = 0;       // processed channels of the last run (layout of d_inter)
   int inter_cp = 0;      // processed-channel count the blocked workspace is currently laid out for
   int last_frames = 0;
-  // overlap-save row pass (ols.h); only created when GBLUR_ROW_OLS=1 is set at plan creation (experimental)
+  // overlap-save row pass (ols.h). GBLUR_ROW_OLS at plan creation: unset = automatic (single-frame fused runs of
+  // wide RGBA images whose blocks waste little, see ols::row_profitable), 1 = wherever eligible, 0 = never
   ols::RowPlan* ols_row = nullptr;
+  int ols_mode = 2;
 };
 
 namespace {
@@ -192,7 +194,8 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
   if (rc == GBLUR_OK) rc = build_tables(p->col, sz.n_colpass, taps, 2);
   if (rc == GBLUR_OK) {
     const char* e = getenv("GBLUR_ROW_OLS");
-    if (e && atoi(e) > 0 && channels == 4) {
+    p->ols_mode = e ? (atoi(e) > 0 ? 1 : 0) : 2;
+    if (p->ols_mode != 0 && channels == 4 && !band) {
       const cudaError_t ce = ols::row_plan_create(&p->ols_row, taps, sz.n_rowpass);
       if (ce != cudaSuccess) rc = fail(GBLUR_E_CUDA, "overlap-save row plan: %s", cudaGetErrorString(ce));
     }
@@ -210,7 +213,7 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
 // rows_sub > 0: only rows [row0, row0 + rows_sub) of a single frame (d_in / d_inter still point at row 0)
 int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pitch, int frames, int alpha,
                 cudaStream_t s, const BlockedLayout* blk = nullptr, int split_cols = 0, long long split_stride = 0,
-                int row0 = 0, int rows_sub = 0) {
+                int row0 = 0, int rows_sub = 0, bool fused_single = false) {
   const int cp = processed_channels(p, alpha);
   RowLaunch a{};
   a.in = d_in;
@@ -233,7 +236,8 @@ int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pi
     else
       a.inter = d_inter + (long long)row0 * pitch;
   }
-  if (p->ols_row && ols::row_eligible(p->ols_row, a)) {
+  if (p->ols_row && ols::row_eligible(p->ols_row, a) &&
+      (p->ols_mode == 1 || (fused_single && ols::row_profitable(a, p->sz.n_rowpass)))) {
     CU(ols::launch_row(p->ols_row, a, p->num_sms, s));
     return GBLUR_OK;
   }
@@ -426,7 +430,7 @@ static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_f
   int rc = fused_prepare(p, n_frames, apply_to_alpha, s, c);
   if (rc != GBLUR_OK) return rc;
   if (stages & 1) {
-    rc = run_rowpass(p, d_in, p->d_inter, c.pitch, n_frames, apply_to_alpha, s, c.bp);
+    rc = run_rowpass(p, d_in, p->d_inter, c.pitch, n_frames, apply_to_alpha, s, c.bp, 0, 0, 0, 0, n_frames == 1);
     if (rc != GBLUR_OK) return rc;
   }
   if (!(stages & 2)) return GBLUR_OK;

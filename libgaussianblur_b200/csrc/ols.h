@@ -1,5 +1,6 @@
 // ols.h — host interface of the overlap-save row pass (ols_kernels.cu, ols_core.cuh).
-// Experimental in round 1: selected with GBLUR_ROW_OLS=1 (capi.cpp), default off.
+// capi.cpp picks it automatically for single-frame fused runs where row_profitable() holds; GBLUR_ROW_OLS=1 forces
+// it wherever row_eligible() holds, GBLUR_ROW_OLS=0 turns it off.
 #pragma once
 #include <cuda_runtime.h>
 
@@ -18,6 +19,11 @@ void row_plan_destroy(RowPlan* p);
 
 // RGBA with all four channels processed, panel intermediate for a two-sequence column plan, no peer/split stores
 bool row_eligible(const RowPlan* p, const RowLaunch& a);
+
+// The 1024-sample blocks cost nblk * 1024 transform points per row against the whole line's n_ref: worth it for wide
+// rows (>= 4096 pixels, where the whole-line kernel is down to 13 warps per SM) when the blocks waste <= 20 %.
+// Measured on 7680x4320 RGBA sigma=20: 0.36 ms against 0.417 ms (profiles/r01/ols_rowpass_v2_check.jsonl).
+bool row_profitable(const RowLaunch& a, int n_ref);
 
 // two launches: alternating sums per row, then one warp per (row, block, channel pair)
 cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t stream);

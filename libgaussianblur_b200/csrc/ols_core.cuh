@@ -18,6 +18,7 @@
 #pragma once
 #include <math.h>
 
+#include <algorithm>
 #include <cstdint>
 
 #include "fft_radix.cuh"
@@ -30,6 +31,10 @@
 
 namespace gblur {
 namespace ols {
+
+#if !defined(__CUDACC__)
+using std::min;
+#endif
 
 constexpr int kNB = 1024;        // block transform length
 constexpr int kR = 32;           // radix of both stages = lanes per warp = points per lane
@@ -73,12 +78,52 @@ __device__ __forceinline__ int altsum_weight(int x, int pad, int T) {
   return ((pad + x) & 1) ? -m : m;
 }
 
+__device__ __forceinline__ void altsum_acc(uint32_t w, int x, int pad, int T, int (&a)[4]) {
+  const int m = altsum_weight(x, pad, T);
+  a[0] += m * (int)(w & 255u);
+  a[1] += m * (int)((w >> 8) & 255u);
+  a[2] += m * (int)((w >> 16) & 255u);
+  a[3] += m * (int)(w >> 24);
+}
+
+// One lane's share of a row's alternating sums (the warp adds its 32 shares): 16-byte loads of four pixels when
+// the row is 16-byte aligned, groups without a mirrored pixel take the +-1 shortcut.
+__device__ __forceinline__ void altsum_lane(const uint32_t* __restrict__ row, int T, int pad, int lane, int (&a)[4]) {
+  int x_scalar = 0;  // first pixel the scalar loop still has to take
+  if ((reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+    const uint4* row4 = reinterpret_cast<const uint4*>(row);
+    const int n4 = T >> 2;
+#pragma unroll 4
+    for (int g = lane; g < n4; g += 32) {
+      const uint4 v = GBLUR_OLS_LDG(row4 + g);
+      const int x = 4 * g;
+      if (x > pad && x + 3 < T - 1 - pad) {
+        const int sg = ((pad + x) & 1) ? -1 : 1;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          const int sh = 8 * c;
+          a[c] += sg * ((int)((v.x >> sh) & 255u) - (int)((v.y >> sh) & 255u) + (int)((v.z >> sh) & 255u) -
+                        (int)((v.w >> sh) & 255u));
+        }
+      } else {
+        altsum_acc(v.x, x, pad, T, a);
+        altsum_acc(v.y, x + 1, pad, T, a);
+        altsum_acc(v.z, x + 2, pad, T, a);
+        altsum_acc(v.w, x + 3, pad, T, a);
+      }
+    }
+    x_scalar = 4 * n4;
+  }
+  for (int x = x_scalar + lane; x < T; x += 32) altsum_acc(GBLUR_OLS_LDG(row + x), x, pad, T, a);
+}
+
 // bytes (2 * pair, 2 * pair + 1) of an RGBA word as a complex sample
 __device__ __forceinline__ float2 u8_pair(uint32_t w, int pair) {
 #if defined(__CUDA_ARCH__)
   // 0x4B000000 | b is the float 8388608 + b: no conversion-pipe instruction
-  const uint32_t lo = pair ? __byte_perm(w, 0x4B000000u, 0x7542u) : __byte_perm(w, 0x4B000000u, 0x7540u);
-  const uint32_t hi = pair ? __byte_perm(w, 0x4B000000u, 0x7543u) : __byte_perm(w, 0x4B000000u, 0x7541u);
+  const uint32_t sel = 0x7540u + 2u * (uint32_t)pair;
+  const uint32_t lo = __byte_perm(w, 0x4B000000u, sel);
+  const uint32_t hi = __byte_perm(w, 0x4B000000u, sel + 1u);
   return make_float2(__uint_as_float(lo) - 8388608.0f, __uint_as_float(hi) - 8388608.0f);
 #else
   return make_float2((float)((w >> (16 * pair)) & 255u), (float)((w >> (16 * pair + 8)) & 255u));
@@ -104,11 +149,23 @@ __device__ __forceinline__ RowDst make_row_dst(const RowParams& P, long long r_g
   return d;
 }
 
-// ---- phase A (lane = l): samples b[s + l + 32 i] -> DFT over i -> twiddle w^(l k1) -> column l of the exchange ----
+// One item = one 1024-sample block of one channel pair. Per lane, 32 complex values stay in registers:
+//   load_block : c[i] = b[s + lane + 32 i]                                           (lane = l, register = i)
+//   then four passes q = 0..3 of ONE rolled loop, each starting with the same 32-point DFT over the register index:
+//     q = 0: twiddle w^(lane k), column `lane` of the exchange, __syncwarp, row `lane` back   (lane = k1, register = l)
+//     q = 1: X[lane + 32 k2] is complete: gains, complex conjugate
+//     q = 2: as q = 0 — the inverse transform is conj(DFT(conj(.))) and conj(a conj(w)) = conj(a) w, so the inverse
+//            half is THE SAME CODE on conjugated data                                         (lane = l, register = k1)
+//     q = 3: nothing more: c[i] = conj(1024 y_lin[s + lane + 32 i])
+//   store_block: conjugate back, add the Nyquist term, crop, panel stores
+// The loop is kept rolled on purpose: the warps of an SM run out of phase here, so the instructions of an item must
+// fit the SM's 32 KB instruction cache. The fully unrolled first version (four DFT copies, 44 KB) ran no faster than
+// the whole-line kernel and slowed down with more independent CTAs (profiles/r01/ols_rowpass_v1_check.jsonl).
+// Exchange pattern: S[row][col], row stride 34 slots. tw_write_col writes S[k][lane] (STS.64, conflict-free),
+// read_row reads S[lane][0..31] (LDS.128, conflict-free). __syncwarp between them and after the reads.
 template <bool INTERIOR>
-__device__ __forceinline__ void phase_a(const RowParams& P, const uint32_t* __restrict__ row, int s, int pair, int lane,
-                                        float2* __restrict__ ex, const float2* __restrict__ tw) {
-  float2 c[kR];
+__device__ __forceinline__ void load_block(float2 (&c)[kR], const RowParams& P, const uint32_t* __restrict__ row, int s,
+                                           int pair, int lane) {
   if constexpr (INTERIOR) {
     const uint32_t* p = row + (s - P.pad + lane);
 #pragma unroll
@@ -121,62 +178,69 @@ __device__ __forceinline__ void phase_a(const RowParams& P, const uint32_t* __re
       c[i] = (x < 0) ? make_float2(0.f, 0.f) : v;
     }
   }
-  dft<kR, false>(c);
+}
+
+// twiddle w^(lane * k) on register k, then column `lane` of the exchange
+__device__ __forceinline__ void tw_write_col(const float2 (&c)[kR], int lane, float2* __restrict__ ex,
+                                             const float2* __restrict__ tw) {
   ex[lane] = c[0];
 #pragma unroll
   for (int k = 1; k < kR; ++k) ex[k * kRowStride + lane] = cmul(c[k], tw[k * kR + lane]);
 }
 
-// ---- phase B (lane = k1): row k1 -> DFT over l -> gains -> inverse DFT over k2 -> conj twiddle -> row k1 ----
-__device__ __forceinline__ void phase_b(int lane, float2* __restrict__ ex, const float2* __restrict__ tw,
-                                        const float* __restrict__ gains) {
-  float2 c[kR];
-  float4* rowp = reinterpret_cast<float4*>(ex + lane * kRowStride);
+// row `lane` of the exchange
+__device__ __forceinline__ void read_row(float2 (&c)[kR], int lane, const float2* __restrict__ ex) {
+  const float4* rowp = reinterpret_cast<const float4*>(ex + lane * kRowStride);
 #pragma unroll
   for (int m = 0; m < kR / 2; ++m) {
     const float4 t = rowp[m];
     c[2 * m] = make_float2(t.x, t.y);
     c[2 * m + 1] = make_float2(t.z, t.w);
   }
-  dft<kR, false>(c);  // c[k2] = X[k1 + 32 k2]
+}
+
+// c[k2] = conj(X[lane + 32 k2] * gain)
+__device__ __forceinline__ void mid_gains(float2 (&c)[kR], int lane, const float* __restrict__ gains) {
   const float4* g = reinterpret_cast<const float4*>(gains + lane * kGainStride);
 #pragma unroll
   for (int m = 0; m < kR / 4; ++m) {
     const float4 t = g[m];
-    c[4 * m].x *= t.x, c[4 * m].y *= t.x;
-    c[4 * m + 1].x *= t.y, c[4 * m + 1].y *= t.y;
-    c[4 * m + 2].x *= t.z, c[4 * m + 2].y *= t.z;
-    c[4 * m + 3].x *= t.w, c[4 * m + 3].y *= t.w;
+    c[4 * m].x *= t.x, c[4 * m].y *= -t.x;
+    c[4 * m + 1].x *= t.y, c[4 * m + 1].y *= -t.y;
+    c[4 * m + 2].x *= t.z, c[4 * m + 2].y *= -t.z;
+    c[4 * m + 3].x *= t.w, c[4 * m + 3].y *= -t.w;
   }
-  dft<kR, true>(c);  // c[l] = sum_k2 X[k1 + 32 k2] w32^(-l k2)
-#pragma unroll
-  for (int l = 1; l < kR; ++l) c[l] = cmulc(c[l], tw[l * kR + lane]);
-#pragma unroll
-  for (int m = 0; m < kR / 2; ++m) rowp[m] = make_float4(c[2 * m].x, c[2 * m].y, c[2 * m + 1].x, c[2 * m + 1].y);
 }
 
-// ---- phase C (lane = l): column l -> inverse DFT over k1 -> + Nyquist term -> crop -> panel stores ----
-__device__ __forceinline__ void phase_c(const RowParams& P, const RowDst& d, float2 qa, int s, int pair, int lane,
-                                        const float2* __restrict__ ex) {
-  float2 c[kR];
-#pragma unroll
-  for (int k = 0; k < kR; ++k) c[k] = ex[k * kRowStride + lane];
-  dft<kR, true>(c);  // c[i] = 1024 * y_lin[s + lane + 32 i] (the 1/1024 sits in the gains)
+// c[i] = conj(1024 * y_lin[s + lane + 32 i]) (the 1/1024 sits in the gains)
+__device__ __forceinline__ void store_block(const float2 (&c)[kR], const RowParams& P, const RowDst& d, float2 qa, int s,
+                                            int pair, int lane) {
   // (-1)^n for n = s + lane + 32 i does not depend on i
   const float sg = ((s + lane) & 1) ? -1.0f : 1.0f;
   const float2 add = make_float2(qa.x * sg, qa.y * sg);
-  const int lo = P.pad, hi = P.pad + P.L;
-  float* colbase = d.base + 2 * pair;
+  // register i holds block index lane + 32 i; outputs are the indices [pad, min(pad + L, T - s + pad))
+  const int lo = P.pad - lane;
+  const int hi = min(P.pad + P.L, P.T - s + P.pad) - lane;
+  // pixel x = x0 + 32 i lands in panel (x >> 3) = (x0 >> 3) + 4 i at float offset (x0 & 7) * 4 (+ 2 for pair 1)
+  const int x0 = s + lane - P.pad;
+  float* dp = d.base + 2 * pair + (long long)(x0 >> 3) * d.gstride + ((x0 & 7) << 2);
+  const long long step = 4 * d.gstride;
+  if ((d.dl | d.dr) == 0) {
 #pragma unroll
-  for (int i = 0; i < kR; ++i) {
-    const int idx = lane + kR * i;
-    const int x = s + idx - P.pad;
-    if (idx >= lo && idx < hi && x < P.T) {
-      const float2 v = make_float2(c[i].x + add.x, c[i].y + add.y);
-      float* dp = colbase + (long long)(x >> 3) * d.gstride + ((x & 7) << 2);
-      *reinterpret_cast<float2*>(dp) = v;
-      if (d.dl) *reinterpret_cast<float2*>(dp + d.dl) = v;
-      if (d.dr) *reinterpret_cast<float2*>(dp + d.dr) = v;
+    for (int i = 0; i < kR; ++i) {
+      if (kR * i >= lo && kR * i < hi) *reinterpret_cast<float2*>(dp) = make_float2(c[i].x + add.x, add.y - c[i].y);
+      dp += step;
+    }
+  } else {  // rows inside the reflect_101 border also fill the column pass's mirrored slots
+#pragma unroll
+    for (int i = 0; i < kR; ++i) {
+      if (kR * i >= lo && kR * i < hi) {
+        const float2 v = make_float2(c[i].x + add.x, add.y - c[i].y);
+        *reinterpret_cast<float2*>(dp) = v;
+        if (d.dl) *reinterpret_cast<float2*>(dp + d.dl) = v;
+        if (d.dr) *reinterpret_cast<float2*>(dp + d.dr) = v;
+      }
+      dp += step;
     }
   }
 }

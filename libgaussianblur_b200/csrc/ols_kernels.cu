@@ -25,48 +25,28 @@ struct RowPlan {
   int ksize = 0;
   float4* d_qa = nullptr;
   long long qa_rows = 0;
+  bool qa_valid = false;
 };
 
-// (K[0] - K[N/2]) / N * sum over the reflect_101-padded row of (-1)^n b[n], per channel; exact integer sums
-__global__ void __launch_bounds__(256) altsum_rows_kernel(const uint8_t* __restrict__ in, long long in_pitch, int T,
-                                                          int pad, float q, float4* __restrict__ qa) {
-  const long long r = blockIdx.x;
+// (K[0] - K[N/2]) / N * sum over the reflect_101-padded row of (-1)^n b[n], per channel; exact integer sums.
+// One warp per row, 16-byte loads (four in flight per lane) when the row allows them.
+constexpr int kAltsumWarps = 8;
+
+__global__ void __launch_bounds__(kAltsumWarps * 32)
+    altsum_rows_kernel(const uint8_t* __restrict__ in, long long in_pitch, int T, int pad, float q, long long rows_total,
+                       float4* __restrict__ qa) {
+  const int lane = threadIdx.x & 31;
+  const long long r = (long long)blockIdx.x * kAltsumWarps + (threadIdx.x >> 5);
+  if (r >= rows_total) return;
   const uint32_t* row = reinterpret_cast<const uint32_t*>(in + r * in_pitch);
-  int a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-  for (int x = threadIdx.x; x < T; x += blockDim.x) {
-    const uint32_t w = __ldg(row + x);
-    const int m = altsum_weight(x, pad, T);
-    a0 += m * (int)(w & 255u);
-    a1 += m * (int)((w >> 8) & 255u);
-    a2 += m * (int)((w >> 16) & 255u);
-    a3 += m * (int)(w >> 24);
-  }
+  int a[4] = {0, 0, 0, 0};
+  altsum_lane(row, T, pad, lane, a);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
-    a0 += __shfl_xor_sync(0xffffffffu, a0, o);
-    a1 += __shfl_xor_sync(0xffffffffu, a1, o);
-    a2 += __shfl_xor_sync(0xffffffffu, a2, o);
-    a3 += __shfl_xor_sync(0xffffffffu, a3, o);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) a[c] += __shfl_xor_sync(0xffffffffu, a[c], o);
   }
-  __shared__ int part[8][4];
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  if (lane == 0) {
-    part[warp][0] = a0;
-    part[warp][1] = a1;
-    part[warp][2] = a2;
-    part[warp][3] = a3;
-  }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    int s0 = 0, s1 = 0, s2 = 0, s3 = 0;
-    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) {
-      s0 += part[w][0];
-      s1 += part[w][1];
-      s2 += part[w][2];
-      s3 += part[w][3];
-    }
-    qa[r] = make_float4(q * (float)s0, q * (float)s1, q * (float)s2, q * (float)s3);
-  }
+  if (lane == 0) qa[r] = make_float4(q * (float)a[0], q * (float)a[1], q * (float)a[2], q * (float)a[3]);
 }
 
 template <int WARPS, int MAXREG>
@@ -87,17 +67,26 @@ __global__ void __maxnreg__(MAXREG) ols_row_rgba_kernel(const __grid_constant__ 
     const int j = (int)(bj - r * P.nblk);
     const int s = j * P.L;
     const uint32_t* row = reinterpret_cast<const uint32_t*>(P.in + r * P.in_pitch);
+    float2 c[kR];
     if (s - P.pad >= 0 && s - P.pad + kNB <= P.T)
-      phase_a<true>(P, row, s, pair, lane, ex, tw);
+      load_block<true>(c, P, row, s, pair, lane);
     else
-      phase_a<false>(P, row, s, pair, lane, ex, tw);
-    __syncwarp();
-    phase_b(lane, ex, tw, gains);
-    __syncwarp();
+      load_block<false>(c, P, row, s, pair, lane);
+#pragma unroll 1
+    for (int q = 0; q < 4; ++q) {
+      dft<kR, false>(c);
+      if ((q & 1) == 0) {
+        tw_write_col(c, lane, ex, tw);
+        __syncwarp();
+        read_row(c, lane, ex);
+        __syncwarp();  // every row has been read before the next pass overwrites columns
+      } else if (q == 1) {
+        mid_gains(c, lane, gains);
+      }
+    }
     const RowDst d = make_row_dst(P, r);
     const float4 q4 = __ldg(P.qa + r);
-    phase_c(P, d, pair ? make_float2(q4.z, q4.w) : make_float2(q4.x, q4.y), s, pair, lane, ex);
-    // the next item's phase A writes column `lane`, which only this lane has just read: no barrier needed
+    store_block(c, P, d, pair ? make_float2(q4.z, q4.w) : make_float2(q4.x, q4.y), s, pair, lane);
   }
 }
 
@@ -136,9 +125,40 @@ bool row_eligible(const RowPlan* p, const RowLaunch& a) {
          a.T >= 1 && a.rows_total >= 1;
 }
 
+bool row_profitable(const RowLaunch& a, int n_ref) {
+  const int L = kNB - 2 * a.pad;
+  if (L < 1 || a.T < 4096) return false;
+  const long long nblk = (a.T + L - 1) / L;
+  return nblk * kNB * 5 <= (long long)n_ref * 6;
+}
+
 namespace {
-constexpr int kWarps = 8;
-constexpr size_t kSmem = (size_t)kNB * 8 + (size_t)kR * kGainStride * 4 + (size_t)kWarps * kExch * 8;
+
+template <int WARPS, int MAXREG>
+cudaError_t launch_blocks(const RowParams& P, int num_sms, cudaStream_t stream) {
+  constexpr size_t smem = (size_t)kNB * 8 + (size_t)kR * kGainStride * 4 + (size_t)WARPS * kExch * 8;
+  auto k = ols_row_rgba_kernel<WARPS, MAXREG>;
+  static thread_local int cached_device = -1, cached_per_sm = 0;
+  int device = 0;
+  cudaGetDevice(&device);
+  if (cached_device != device) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, WARPS * 32, smem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    cached_device = device;
+    cached_per_sm = per_sm;
+  }
+  long long grid = (long long)num_sms * cached_per_sm;
+  const long long need = (P.nitems + WARPS - 1) / WARPS;
+  if (grid > need) grid = need;
+  k<<<(unsigned)grid, WARPS * 32, smem, stream>>>(P);
+  count_launch();
+  return cudaGetLastError();
+}
+
 }  // namespace
 
 cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t stream) {
@@ -149,6 +169,7 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
     cudaError_t e = cudaMalloc(&p->d_qa, (size_t)a.rows_total * sizeof(float4));
     if (e != cudaSuccess) return e;
     p->qa_rows = a.rows_total;
+    p->qa_valid = false;
   }
   RowParams P{};
   P.in = a.in;
@@ -168,31 +189,36 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
   P.tw = p->d_tw;
   P.gains = p->d_gains;
 
-  altsum_rows_kernel<<<(unsigned)a.rows_total, 256, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, p->d_qa);
-  count_launch();
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
-
-  auto k = ols_row_rgba_kernel<kWarps, 128>;
-  static thread_local int cached_device = -1, cached_per_sm = 0;
-  int device = 0;
-  cudaGetDevice(&device);
-  if (cached_device != device) {
-    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmem);
+  // timing aid only: GBLUR_OLS_NO_ALTSUM=1 reuses the sums of the previous call on this plan (same input assumed)
+  static const bool reuse_sums = getenv("GBLUR_OLS_NO_ALTSUM") != nullptr;
+  cudaError_t e = cudaSuccess;
+  if (!(reuse_sums && p->qa_valid)) {
+    const unsigned nb = (unsigned)((a.rows_total + kAltsumWarps - 1) / kAltsumWarps);
+    altsum_rows_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total, p->d_qa);
+    count_launch();
+    e = cudaGetLastError();
     if (e != cudaSuccess) return e;
-    int per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kWarps * 32, kSmem);
-    if (e != cudaSuccess) return e;
-    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-    cached_device = device;
-    cached_per_sm = per_sm;
+    p->qa_valid = true;
   }
-  long long grid = (long long)num_sms * cached_per_sm;
-  const long long need = (P.nitems + kWarps - 1) / kWarps;
-  if (grid > need) grid = need;
-  k<<<(unsigned)grid, kWarps * 32, kSmem, stream>>>(P);
-  count_launch();
-  return cudaGetLastError();
+
+  // warps per CTA / register cap; resident warps per SM: 20 in two CTAs (default: 0.362 ms on 8K RGBA against 0.375
+  // for 16 in one CTA and 0.38 for 16 in two or four, profiles/r01/ols_rowpass_v2_check.jsonl), 16, 16, 24, 16
+  static const int variant = [] {
+    const char* v = getenv("GBLUR_OLS_VARIANT");
+    return v ? atoi(v) : 1;
+  }();
+  switch (variant) {
+    case 0:
+      return launch_blocks<8, 128>(P, num_sms, stream);
+    case 2:
+      return launch_blocks<4, 128>(P, num_sms, stream);
+    case 3:
+      return launch_blocks<24, 80>(P, num_sms, stream);
+    case 4:
+      return launch_blocks<16, 128>(P, num_sms, stream);
+    default:
+      return launch_blocks<10, 96>(P, num_sms, stream);
+  }
 }
 
 }  // namespace ols

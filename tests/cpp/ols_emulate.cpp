@@ -45,8 +45,13 @@ int ols_emulate_rowpass(const uint8_t* in, int rows, int T, float sigma, int ksi
   std::vector<float4> qa((size_t)rows);
   for (int r = 0; r < rows; ++r) {
     int a[4] = {0, 0, 0, 0};
+    for (int lane = 0; lane < 32; ++lane)
+      ols::altsum_lane(reinterpret_cast<const uint32_t*>(in + (size_t)r * T * 4), T, pad, lane, a);
+    int chk[4] = {0, 0, 0, 0};  // the definition, pixel by pixel
     for (int x = 0; x < T; ++x)
-      for (int ch = 0; ch < 4; ++ch) a[ch] += ols::altsum_weight(x, pad, T) * (int)in[((size_t)r * T + x) * 4 + ch];
+      for (int ch = 0; ch < 4; ++ch) chk[ch] += ols::altsum_weight(x, pad, T) * (int)in[((size_t)r * T + x) * 4 + ch];
+    for (int ch = 0; ch < 4; ++ch)
+      if (chk[ch] != a[ch]) return -3;
     qa[(size_t)r] = make_float4(tb.q * (float)a[0], tb.q * (float)a[1], tb.q * (float)a[2], tb.q * (float)a[3]);
   }
   P.qa = qa.data();
@@ -62,17 +67,26 @@ int ols_emulate_rowpass(const uint8_t* in, int rows, int T, float sigma, int ksi
     const int s = j * P.L;
     const uint32_t* row = reinterpret_cast<const uint32_t*>(P.in + r * P.in_pitch);
     const bool interior = s - P.pad >= 0 && s - P.pad + ols::kNB <= P.T;
+    static float2 regs[32][ols::kR];  // the registers of the 32 lanes, kept across the __syncwarp points
     for (int lane = 0; lane < 32; ++lane) {
       if (interior)
-        ols::phase_a<true>(P, row, s, pair, lane, ex, P.tw);
+        ols::load_block<true>(regs[lane], P, row, s, pair, lane);
       else
-        ols::phase_a<false>(P, row, s, pair, lane, ex, P.tw);
+        ols::load_block<false>(regs[lane], P, row, s, pair, lane);
     }
-    for (int lane = 0; lane < 32; ++lane) ols::phase_b(lane, ex, P.tw, P.gains);
+    for (int q = 0; q < 4; ++q) {
+      for (int lane = 0; lane < 32; ++lane) dft<ols::kR, false>(regs[lane]);
+      if ((q & 1) == 0) {
+        for (int lane = 0; lane < 32; ++lane) ols::tw_write_col(regs[lane], lane, ex, P.tw);
+        for (int lane = 0; lane < 32; ++lane) ols::read_row(regs[lane], lane, ex);
+      } else if (q == 1) {
+        for (int lane = 0; lane < 32; ++lane) ols::mid_gains(regs[lane], lane, P.gains);
+      }
+    }
     const ols::RowDst d = ols::make_row_dst(P, r);
     const float4 q4 = P.qa[r];
     for (int lane = 0; lane < 32; ++lane)
-      ols::phase_c(P, d, pair ? make_float2(q4.z, q4.w) : make_float2(q4.x, q4.y), s, pair, lane, ex);
+      ols::store_block(regs[lane], P, d, pair ? make_float2(q4.z, q4.w) : make_float2(q4.x, q4.y), s, pair, lane);
   }
   // read the panel layout back: slot(pad + r) is row r; mirrored border slots must hold the same values
   auto at = [&](int slot_logical, int w) -> float {
