@@ -22,6 +22,9 @@ using namespace gblur;
 
 namespace {
 
+// default of the overlap-save column pass when GBLUR_COL_OLS is unset: 0 = off, 2 = automatic (ols::col_profitable)
+constexpr int kColOlsAuto = 0;
+
 thread_local std::string g_err;
 
 int fail(int code, const char* fmt, ...) {
@@ -92,6 +95,8 @@ struct gblur_plan {
   // wide RGBA images whose blocks waste little, see ols::row_profitable), 1 = wherever eligible, 0 = never
   ols::RowPlan* ols_row = nullptr;
   int ols_mode = 2;
+  // overlap-save column pass, same plan object. GBLUR_COL_OLS: 1 = wherever eligible, 0 = never, unset = kColOlsAuto
+  int ols_col_mode = 0;
 };
 
 namespace {
@@ -196,7 +201,9 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
     const char* e = getenv("GBLUR_ROW_OLS");
     p->ols_mode = e ? (atoi(e) > 0 ? 1 : 0) : 2;
     if (p->ols_mode != 0 && channels == 4 && !band) {
-      const cudaError_t ce = ols::row_plan_create(&p->ols_row, taps, sz.n_rowpass);
+      const char* ec = getenv("GBLUR_COL_OLS");
+      p->ols_col_mode = ec ? (atoi(ec) > 0 ? 1 : 0) : kColOlsAuto;
+      const cudaError_t ce = ols::row_plan_create(&p->ols_row, taps, sz.n_rowpass, sz.n_colpass);
       if (ce != cudaSuccess) rc = fail(GBLUR_E_CUDA, "overlap-save row plan: %s", cudaGetErrorString(ce));
     }
   }
@@ -264,8 +271,11 @@ bool panel_tensor_map(gblur_plan* p, const float* base, const BlockedLayout& b, 
 }
 
 // w_end > 0: only the float columns [w_begin, w_end) (w_begin a multiple of 32) of a single frame
+// ols_in: the u8 image the intermediate was computed from (single-frame fused runs only): lets the overlap-save
+// column pass form the column term of the reference's Nyquist behaviour (ols_core.cuh)
 int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d_out, long long out_pitch, int frames,
-                int alpha, cudaStream_t s, const BlockedLayout* blk = nullptr, int w_begin = 0, int w_end = 0) {
+                int alpha, cudaStream_t s, const BlockedLayout* blk = nullptr, int w_begin = 0, int w_end = 0,
+                const uint8_t* ols_in = nullptr) {
   const int cp = processed_channels(p, alpha);
   ColLaunch a{};
   a.inter = d_inter;
@@ -290,6 +300,11 @@ int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d
       a.tmap = &p->tmap;
       a.tma_rows = p->tmap_rows;
     }
+  }
+  if (p->ols_row && ols_in && p->ols_col_mode != 0 && ols::col_eligible(p->ols_row, a) &&
+      (p->ols_col_mode == 1 || ols::col_profitable(a, p->sz.n_colpass))) {
+    CU(ols::launch_col(p->ols_row, a, ols_in, (long long)p->full_cols * p->channels, p->num_sms, s));
+    return GBLUR_OK;
   }
   CU(launch_colpass(p->col.lp, a, p->num_sms, s));
   return GBLUR_OK;
@@ -436,7 +451,8 @@ static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_f
   if (!(stages & 2)) return GBLUR_OK;
   if (d_in != d_out && c.cp < p->channels)
     CU(launch_copy_channel(d_in, d_out, (long long)p->rows * p->cols * n_frames, p->channels, 3, s));
-  return run_colpass(p, p->d_inter, c.pitch, d_out, (long long)p->cols * p->channels, n_frames, apply_to_alpha, s, c.bp);
+  return run_colpass(p, p->d_inter, c.pitch, d_out, (long long)p->cols * p->channels, n_frames, apply_to_alpha, s, c.bp,
+                     0, 0, n_frames == 1 ? d_in : nullptr);
 }
 
 int gblur_run_batch_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,

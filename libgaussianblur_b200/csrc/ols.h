@@ -14,7 +14,8 @@ namespace ols {
 struct RowPlan;  // device tables: twiddles, block gains, Nyquist coefficient, per-row alternating sums
 
 // taps: the reference's normalised taps; n_ref: the reference's transform length along a row
-cudaError_t row_plan_create(RowPlan** out, const std::vector<float>& taps, int n_ref);
+// n_ref_col: its transform length along a column (0: the column pass is not wanted)
+cudaError_t row_plan_create(RowPlan** out, const std::vector<float>& taps, int n_ref, int n_ref_col = 0);
 void row_plan_destroy(RowPlan* p);
 
 // RGBA with all four channels processed, panel intermediate for a two-sequence column plan, no peer/split stores
@@ -27,6 +28,15 @@ bool row_profitable(const RowLaunch& a, int n_ref);
 
 // two launches: alternating sums per row, then one warp per (row, block, channel pair)
 cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t stream);
+
+// ---- column pass (same plan object) ----
+// RGBA with all four channels processed, one frame, whole width, even pixel count, 8-byte aligned output rows
+bool col_eligible(const RowPlan* p, const ColLaunch& a);
+bool col_profitable(const ColLaunch& a, int n_ref_col);
+// Three launches: column sums of the u8 input (the synthetic row u), the row pass of u (one CTA), the block kernel.
+// d_in / in_pitch: the image the intermediate was computed from.
+cudaError_t launch_col(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long long in_pitch, int num_sms,
+                       cudaStream_t stream);
 
 }  // namespace ols
 }  // namespace gblur

@@ -245,5 +245,148 @@ __device__ __forceinline__ void store_block(const float2 (&c)[kR], const RowPara
   }
 }
 
+// ------------------------------------------------------------------------------------------------------------
+// Column pass: fp32 panel intermediate -> u8 image (replaces the second process_channel_tiles call and
+// interleave_channels, /root/reference/src/gaussianblur.cpp:261-305, helpers.hpp:248-274).
+// One CTA of four warps takes a QUARTER PANEL (8 float columns = 2 RGBA pixels = one 32-byte sector per slot) and one
+// 1024-slot block of the padded column; warp w transforms column pair w (floats 2w, 2w+1 of the quarter) with the
+// same four-pass loop as the row pass. The slots are fetched cooperatively with 16-byte loads straight into the four
+// exchange buffers (column layout, so every lane later reads exactly what it will overwrite), the u8 results are
+// collected in a shared tile and leave as one 8-byte store per image row.
+// The reference's Nyquist term along a column needs sum_n (-1)^n I[n][w] over the padded column of the row-pass
+// result I. By linearity that is the row pass applied to ONE synthetic row u = sum_r weight(r) x[r] (exact integers
+// on u8 input, colsum_lane below), so it costs one more line instead of a pass over the 531 MB intermediate.
+// ------------------------------------------------------------------------------------------------------------
+struct ColParams {
+  const float* inter;       // panel intermediate [panel][slot][32 floats]
+  long long panel_stride;   // floats per panel = np * 32
+  int padq;                 // slot holes of the whole-line column kernel's layout (0 = none)
+  int T, pad;               // image rows, reflect pad
+  int L, nblk;              // outputs per block, blocks per column
+  int nquarters;            // quarter panels with at least one valid pixel = ceil(cols / 2)
+  long long nitems;         // nquarters * nblk
+  int cols;
+  uint8_t* out;             // HWC u8, 4 channels
+  long long out_pitch;      // bytes per image row
+  const float2* qc;         // per column pair (2x + pair): (K[0] - K[N/2]) / N of the column length * row pass of u
+  const float2* tw;
+  const float* gains;
+};
+
+constexpr int kColWarps = 4;
+
+// cooperative fetch of one item: thread t of 128 takes the 16-byte half (t & 1) of slot k * 64 + (t >> 1), k < 16
+__device__ __forceinline__ void col_fetch(const ColParams& P, int quarter, int s, int t, float2* __restrict__ ex_all) {
+  const float* src = P.inter + (long long)(quarter >> 2) * P.panel_stride + (quarter & 3) * 8 + (t & 1) * 4;
+  float2* e0 = ex_all + (2 * (t & 1)) * kExch;  // exchange buffers of warps 2h and 2h + 1
+  float2* e1 = e0 + kExch;
+  const int nvalid = P.T + 2 * P.pad;
+  float4 v[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const int n = s + k * 64 + (t >> 1);
+    v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (n < nvalid) v[k] = GBLUR_OLS_LDG(reinterpret_cast<const float4*>(src + (long long)phys_slot(n, P.padq) * 32));
+  }
+#pragma unroll
+  for (int k = 0; k < 16; ++k) {
+    const int nl = k * 64 + (t >> 1);
+    const int slot = (nl >> 5) * kRowStride + (nl & 31);
+    e0[slot] = make_float2(v[k].x, v[k].y);
+    e1[slot] = make_float2(v[k].z, v[k].w);
+  }
+}
+
+// column `lane` of the exchange: c[i] = sample s + lane + 32 i
+__device__ __forceinline__ void read_col(float2 (&c)[kR], int lane, const float2* __restrict__ ex) {
+#pragma unroll
+  for (int i = 0; i < kR; ++i) c[i] = ex[i * kRowStride + lane];
+}
+
+// uint8_t(v + 0.5f): fp32 add, truncate (helpers.hpp:251-252,270); clamped to [0, 255]
+__device__ __forceinline__ uint32_t to_u8(float v) {
+  const float f = fminf(fmaxf(v + 0.5f, 0.0f), 255.0f);
+#if defined(__CUDA_ARCH__)
+  return __float2uint_rz(f);
+#else
+  return (uint32_t)f;
+#endif
+}
+
+// c[i] = conj(1024 y_lin[s + lane + 32 i]) -> two bytes per block index into the shared tile [1024][4 pairs]
+__device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, int s, int w, int lane,
+                                            uint16_t* __restrict__ tile) {
+  const float sg = ((s + lane) & 1) ? -1.0f : 1.0f;
+  const float2 add = make_float2(qc.x * sg, qc.y * sg);
+#pragma unroll
+  for (int i = 0; i < kR; ++i) {
+    const uint32_t b0 = to_u8(c[i].x + add.x), b1 = to_u8(add.y - c[i].y);
+    tile[(lane + kR * i) * 4 + w] = (uint16_t)(b0 | (b1 << 8));
+  }
+}
+
+// thread t of 128 stores block indices t + 128 k: 8 bytes (two RGBA pixels) per image row
+__device__ __forceinline__ void col_store(const ColParams& P, int quarter, int s, int t, const uint16_t* __restrict__ tile) {
+  const int hi = min(P.pad + P.L, P.T - s + P.pad);
+  const bool both = 2 * quarter + 1 < P.cols;
+  uint8_t* base = P.out + (long long)quarter * 8;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const int idx = t + 128 * k;
+    if (idx >= P.pad && idx < hi) {
+      const uint2 v = *reinterpret_cast<const uint2*>(tile + idx * 4);
+      uint8_t* dp = base + (long long)(s + idx - P.pad) * P.out_pitch;
+      if (both)
+        *reinterpret_cast<uint2*>(dp) = v;
+      else
+        *reinterpret_cast<uint32_t*>(dp) = v.x;
+    }
+  }
+}
+
+// ---- the synthetic row u and its row pass (one CTA) ----
+// u[4x + ch] = sum over image rows r of altsum_weight(r) * x[r][x][ch]; one thread per pixel column and row chunk
+__device__ __forceinline__ void colsum_lane(const uint8_t* __restrict__ in, long long in_pitch, int x, int r0, int r1,
+                                            int pad, int rows, int (&a)[4]) {
+  const uint32_t* p = reinterpret_cast<const uint32_t*>(in + (long long)r0 * in_pitch) + x;
+  for (int r = r0; r < r1; ++r) {
+    const uint32_t w = GBLUR_OLS_LDG(p);
+    const int m = altsum_weight(r, pad, rows);
+    a[0] += m * (int)(w & 255u);
+    a[1] += m * (int)((w >> 8) & 255u);
+    a[2] += m * (int)((w >> 16) & 255u);
+    a[3] += m * (int)(w >> 24);
+    p = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(p) + in_pitch);
+  }
+}
+
+// block loader for the synthetic row (int32 sums, always through the reflect map)
+__device__ __forceinline__ void load_block_u(float2 (&c)[kR], const int* __restrict__ u, int T, int pad, int s, int pair,
+                                             int lane) {
+#pragma unroll
+  for (int i = 0; i < kR; ++i) {
+    const int x = reflect_src(s + lane + kR * i, pad, T);
+    const int xx = x < 0 ? 0 : x;
+    const float2 v = make_float2((float)u[4 * xx + 2 * pair], (float)u[4 * xx + 2 * pair + 1]);
+    c[i] = (x < 0) ? make_float2(0.f, 0.f) : v;
+  }
+}
+
+// c[i] = conj(1024 * linear convolution of u at s + lane + 32 i): add u's own Nyquist term, scale by the column
+// coefficient and store per column pair (2x + pair)
+__device__ __forceinline__ void store_block_u(const float2 (&c)[kR], float2 qa_u, float q_col, int T, int pad, int L, int s,
+                                              int pair, int lane, float2* __restrict__ qc) {
+  const float sg = ((s + lane) & 1) ? -1.0f : 1.0f;
+  const int hi = min(pad + L, T - s + pad);
+#pragma unroll
+  for (int i = 0; i < kR; ++i) {
+    const int idx = lane + kR * i;
+    if (idx >= pad && idx < hi) {
+      const int x = s + idx - pad;
+      qc[2 * x + pair] = make_float2(q_col * (c[i].x + qa_u.x * sg), q_col * (qa_u.y * sg - c[i].y));
+    }
+  }
+}
+
 }  // namespace ols
 }  // namespace gblur

@@ -14,11 +14,12 @@ namespace ols {
 struct HostTables {
   std::vector<float> tw;     // 1024 complex values, tw[a*32+b] = exp(-2 pi i a b / 1024)
   std::vector<float> gains;  // 32 rows of 36 floats, gains[k1*36 + k2] = K_1024[k1 + 32 k2] / 1024
-  float q = 0.f;             // (K_N[0] - K_N[N/2]) / N
+  float q = 0.f;             // (K_N[0] - K_N[N/2]) / N for the reference's transform length along a row
+  float q_col = 0.f;         // the same for its transform length along a column
 };
 
 // taps.size() must not exceed 1024 - 512 + 1 (pad <= 256)
-inline HostTables build_tables(const std::vector<float>& taps, int n_ref) {
+inline HostTables build_tables(const std::vector<float>& taps, int n_ref, int n_ref_col = 0) {
   constexpr int NB = 1024, R = 32, GS = 36;
   constexpr double two_pi = 6.28318530717958647692528676655900577;
   HostTables t;
@@ -39,6 +40,10 @@ inline HostTables build_tables(const std::vector<float>& taps, int n_ref) {
     }
   const std::vector<double> kn = host::kernel_gains(taps, n_ref);
   t.q = (float)((kn[0] - kn[(size_t)n_ref / 2]) / (double)n_ref);
+  if (n_ref_col > 0) {
+    const std::vector<double> kc = host::kernel_gains(taps, n_ref_col);
+    t.q_col = (float)((kc[0] - kc[(size_t)n_ref_col / 2]) / (double)n_ref_col);
+  }
   return t;
 }
 

@@ -26,6 +26,11 @@ struct RowPlan {
   float4* d_qa = nullptr;
   long long qa_rows = 0;
   bool qa_valid = false;
+  // column pass
+  float q_col = 0.f;
+  int* d_u = nullptr;       // synthetic row u: 4 * cols integer sums
+  float2* d_qc = nullptr;   // 2 * cols column-pair terms
+  int u_cols = 0;
 };
 
 // (K[0] - K[N/2]) / N * sum over the reflect_101-padded row of (-1)^n b[n], per channel; exact integer sums.
@@ -90,12 +95,131 @@ __global__ void __maxnreg__(MAXREG) ols_row_rgba_kernel(const __grid_constant__ 
   }
 }
 
-cudaError_t row_plan_create(RowPlan** out, const std::vector<float>& taps, int n_ref) {
+// ---------------------------------------------------------------------------------------------------------------
+// column pass
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int kColsumRows = 64;  // image rows per thread of the column-sum kernel
+
+__global__ void __launch_bounds__(128) colsum_kernel(const uint8_t* __restrict__ in, long long in_pitch, int cols, int rows,
+                                                     int pad, int* __restrict__ u) {
+  const int x = blockIdx.x * 128 + threadIdx.x;
+  if (x >= cols) return;
+  const int r0 = blockIdx.y * kColsumRows;
+  const int r1 = min(rows, r0 + kColsumRows);
+  int a[4] = {0, 0, 0, 0};
+  colsum_lane(in, in_pitch, x, r0, r1, pad, rows, a);
+#pragma unroll
+  for (int c = 0; c < 4; ++c) atomicAdd(u + 4 * x + c, a[c]);  // integer atomics: exact, order-independent
+}
+
+// The row pass of the synthetic row: one CTA, kUWarps warps over the nblk * 2 items. Writes the column terms qc.
+constexpr int kUWarps = 16;
+
+__global__ void __launch_bounds__(kUWarps * 32, 1)
+    u_rowpass_kernel(const int* __restrict__ u, int T, int pad, float q_row, float q_col, const float2* __restrict__ g_tw,
+                     const float* __restrict__ g_gains, float2* __restrict__ qc) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float2* tw = reinterpret_cast<float2*>(smem_raw);
+  float* gains = reinterpret_cast<float*>(tw + kNB);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float2* ex = reinterpret_cast<float2*>(gains + kR * kGainStride) + warp * kExch;
+  __shared__ long long part[kUWarps][4];
+  __shared__ float qa_u[4];
+  for (int i = threadIdx.x; i < kNB; i += kUWarps * 32) tw[i] = __ldg(g_tw + i);
+  for (int i = threadIdx.x; i < kR * kGainStride; i += kUWarps * 32) gains[i] = __ldg(g_gains + i);
+  // u's own alternating sum over its reflect_101-padded line (64-bit integers: exact)
+  long long a[4] = {0, 0, 0, 0};
+  for (int x = threadIdx.x; x < T; x += kUWarps * 32) {
+    const long long m = altsum_weight(x, pad, T);
+#pragma unroll
+    for (int c = 0; c < 4; ++c) a[c] += m * (long long)u[4 * x + c];
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) a[c] += __shfl_xor_sync(0xffffffffu, a[c], o);
+  }
+  if (lane == 0) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) part[warp][c] = a[c];
+  }
+  __syncthreads();
+  if (threadIdx.x < 4) {
+    long long t = 0;
+    for (int w = 0; w < kUWarps; ++w) t += part[w][threadIdx.x];
+    qa_u[threadIdx.x] = q_row * (float)t;
+  }
+  __syncthreads();
+  const int L = kNB - 2 * pad;
+  const int nitems = ((T + L - 1) / L) * 2;
+  for (int it = warp; it < nitems; it += kUWarps) {
+    const int pair = it & 1, s = (it >> 1) * L;
+    float2 c[kR];
+    load_block_u(c, u, T, pad, s, pair, lane);
+#pragma unroll 1
+    for (int q = 0; q < 4; ++q) {
+      dft<kR, false>(c);
+      if ((q & 1) == 0) {
+        tw_write_col(c, lane, ex, tw);
+        __syncwarp();
+        read_row(c, lane, ex);
+        __syncwarp();
+      } else if (q == 1) {
+        mid_gains(c, lane, gains);
+      }
+    }
+    store_block_u(c, make_float2(qa_u[2 * pair], qa_u[2 * pair + 1]), q_col, T, pad, L, s, pair, lane, qc);
+  }
+}
+
+template <int MAXREG>
+__global__ void __maxnreg__(MAXREG) ols_col_rgba_kernel(const __grid_constant__ ColParams P) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float2* tw = reinterpret_cast<float2*>(smem_raw);
+  float* gains = reinterpret_cast<float*>(tw + kNB);
+  float2* ex_all = reinterpret_cast<float2*>(gains + kR * kGainStride);
+  uint16_t* tile = reinterpret_cast<uint16_t*>(ex_all + kColWarps * kExch);
+  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
+  float2* ex = ex_all + warp * kExch;
+  for (int i = t; i < kNB; i += kColWarps * 32) tw[i] = __ldg(P.tw + i);
+  for (int i = t; i < kR * kGainStride; i += kColWarps * 32) gains[i] = __ldg(P.gains + i);
+  // no barrier needed here: the first one inside the loop also publishes the tables
+  for (long long it = blockIdx.x; it < P.nitems; it += gridDim.x) {
+    // consecutive items = neighbouring quarter panels of the same block: their 32-byte sectors share 128-byte lines
+    const int j = (int)(it / P.nquarters);
+    const int quarter = (int)(it - (long long)j * P.nquarters);
+    const int s = j * P.L;
+    col_fetch(P, quarter, s, t, ex_all);
+    __syncthreads();
+    float2 c[kR];
+    read_col(c, lane, ex);
+#pragma unroll 1
+    for (int q = 0; q < 4; ++q) {
+      dft<kR, false>(c);
+      if ((q & 1) == 0) {
+        tw_write_col(c, lane, ex, tw);
+        __syncwarp();
+        read_row(c, lane, ex);
+        __syncwarp();
+      } else if (q == 1) {
+        mid_gains(c, lane, gains);
+      }
+    }
+    col_to_tile(c, __ldg(P.qc + quarter * 4 + warp), s, warp, lane, tile);
+    __syncthreads();
+    col_store(P, quarter, s, t, tile);
+    // the next fetch overwrites exchange buffers every warp has finished with (barrier above); the next
+    // col_to_tile comes after the next barrier, when every thread has left this col_store
+  }
+}
+
+cudaError_t row_plan_create(RowPlan** out, const std::vector<float>& taps, int n_ref, int n_ref_col) {
   *out = nullptr;
   if ((int)taps.size() > 2 * kMaxPad + 1) return cudaSuccess;  // window too wide for 1024-sample blocks: not eligible
-  const HostTables t = build_tables(taps, n_ref);
+  const HostTables t = build_tables(taps, n_ref, n_ref_col);
   RowPlan* p = new RowPlan();
   p->q = t.q;
+  p->q_col = t.q_col;
   p->ksize = (int)taps.size();
   cudaError_t e = cudaMalloc(&p->d_tw, t.tw.size() * sizeof(float));
   if (e == cudaSuccess) e = cudaMalloc(&p->d_gains, t.gains.size() * sizeof(float));
@@ -115,6 +239,8 @@ void row_plan_destroy(RowPlan* p) {
   if (p->d_tw) cudaFree(p->d_tw);
   if (p->d_gains) cudaFree(p->d_gains);
   if (p->d_qa) cudaFree(p->d_qa);
+  if (p->d_u) cudaFree(p->d_u);
+  if (p->d_qc) cudaFree(p->d_qc);
   delete p;
 }
 
@@ -219,6 +345,94 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
     default:
       return launch_blocks<10, 96>(P, num_sms, stream);
   }
+}
+
+bool col_eligible(const RowPlan* p, const ColLaunch& a) {
+  return p && p->q_col != 0.f && a.C == 4 && a.Cp == 4 && a.frames == 1 && a.blk.enabled && a.panel_in == 0 &&
+         a.w_begin == 0 && (a.w_end == 0 || a.w_end == a.W) && (a.W % 8) == 0 &&
+         (reinterpret_cast<uintptr_t>(a.out) % 8) == 0 && (a.out_pitch % 8) == 0 &&
+         (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0 && 2 * a.pad + 1 == p->ksize && a.pad <= kMaxPad && a.T >= 1;
+}
+
+bool col_profitable(const ColLaunch& a, int n_ref_col) {
+  const int L = kNB - 2 * a.pad;
+  if (L < 1 || a.T < 4096) return false;
+  const long long nblk = (a.T + L - 1) / L;
+  return nblk * kNB * 5 <= (long long)n_ref_col * 6;
+}
+
+cudaError_t launch_col(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long long in_pitch, int num_sms,
+                       cudaStream_t stream) {
+  const int cols = a.W / 4, rows = a.T;
+  cudaError_t e;
+  if (p->u_cols < cols) {
+    if (p->d_u) cudaFree(p->d_u);
+    if (p->d_qc) cudaFree(p->d_qc);
+    p->d_u = nullptr;
+    p->d_qc = nullptr;
+    p->u_cols = 0;
+    e = cudaMalloc(&p->d_u, (size_t)cols * 4 * sizeof(int));
+    if (e == cudaSuccess) e = cudaMalloc(&p->d_qc, (size_t)cols * 2 * sizeof(float2));
+    if (e != cudaSuccess) return e;
+    p->u_cols = cols;
+  }
+  e = cudaMemsetAsync(p->d_u, 0, (size_t)cols * 4 * sizeof(int), stream);
+  if (e != cudaSuccess) return e;
+  const dim3 cgrid((unsigned)((cols + 127) / 128), (unsigned)((rows + kColsumRows - 1) / kColsumRows));
+  colsum_kernel<<<cgrid, 128, 0, stream>>>(d_in, in_pitch, cols, rows, a.pad, p->d_u);
+  count_launch();
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+
+  constexpr size_t tables = (size_t)kNB * 8 + (size_t)kR * kGainStride * 4;
+  constexpr size_t usmem = tables + (size_t)kUWarps * kExch * 8;
+  static thread_local int u_device = -1;
+  int device = 0;
+  cudaGetDevice(&device);
+  if (u_device != device) {
+    e = cudaFuncSetAttribute(u_rowpass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)usmem);
+    if (e != cudaSuccess) return e;
+    u_device = device;
+  }
+  u_rowpass_kernel<<<1, kUWarps * 32, usmem, stream>>>(p->d_u, cols, a.pad, p->q, p->q_col, p->d_tw, p->d_gains, p->d_qc);
+  count_launch();
+  e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+
+  ColParams P{};
+  P.inter = a.inter;
+  P.panel_stride = (long long)a.blk.np * 32;
+  P.padq = a.blk.padq;
+  P.T = rows;
+  P.pad = a.pad;
+  P.L = kNB - 2 * a.pad;
+  P.nblk = (rows + P.L - 1) / P.L;
+  P.nquarters = (cols + 1) / 2;
+  P.nitems = (long long)P.nquarters * P.nblk;
+  P.cols = cols;
+  P.out = a.out;
+  P.out_pitch = a.out_pitch;
+  P.qc = p->d_qc;
+  P.tw = p->d_tw;
+  P.gains = p->d_gains;
+  constexpr size_t csmem = tables + (size_t)kColWarps * kExch * 8 + (size_t)kNB * 4 * sizeof(uint16_t);
+  auto k = ols_col_rgba_kernel<128>;
+  static thread_local int c_device = -1, c_per_sm = 0;
+  if (c_device != device) {
+    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem);
+    if (e != cudaSuccess) return e;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kColWarps * 32, csmem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    c_device = device;
+    c_per_sm = per_sm;
+  }
+  long long grid = (long long)num_sms * c_per_sm;
+  if (grid > P.nitems) grid = P.nitems;
+  k<<<(unsigned)grid, kColWarps * 32, csmem, stream>>>(P);
+  count_launch();
+  return cudaGetLastError();
 }
 
 }  // namespace ols

@@ -7,6 +7,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <algorithm>
 #include <vector>
 
 #include <cuda_runtime.h>
@@ -100,6 +101,133 @@ int ols_emulate_rowpass(const uint8_t* in, int rows, int T, float sigma, int ksi
       if (r >= 1 && r <= pad && at(pad - r, w) != v) return -1;
       if (r >= rows - 1 - pad && r <= rows - 2 && at(pad + 2 * rows - 2 - r, w) != v) return -2;
     }
+  return 0;
+}
+
+// Whole blur through the emulated kernels: row pass into the panel intermediate, column sums -> synthetic row u ->
+// its row pass -> column terms, then the column pass (four warps per quarter panel, 128 emulated threads).
+// in / out: rows x cols RGBA u8. Returns 0 or a negative code.
+int ols_emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksize, int n_row, int n_col, int padq,
+                     uint8_t* out) {
+  const std::vector<float> taps = host::gaussian_taps(sigma, ksize);
+  const ols::HostTables tb = ols::build_tables(taps, n_row, n_col);
+  const int pad = (ksize - 1) / 2, T = cols;
+  const float2* tw = reinterpret_cast<const float2*>(tb.tw.data());
+  ols::RowParams P{};
+  P.in = in;
+  P.in_pitch = (long long)T * 4;
+  P.T = T;
+  P.pad = pad;
+  P.L = ols::kNB - 2 * pad;
+  P.nblk = (T + P.L - 1) / P.L;
+  P.nitems = (long long)rows * P.nblk * 2;
+  P.rows_per_frame = rows;
+  P.blk_padq = padq;
+  P.blk_np = ols::phys_slot(rows + 2 * pad, padq) + 5;
+  const long long panels = ((long long)T * 4 + 31) / 32;
+  P.blk_frame_stride = panels * P.blk_np * 32;
+  std::vector<float> inter((size_t)P.blk_frame_stride, 0.0f);
+  P.inter = inter.data();
+  std::vector<float4> qa((size_t)rows);
+  for (int r = 0; r < rows; ++r) {
+    int a[4] = {0, 0, 0, 0};
+    for (int lane = 0; lane < 32; ++lane)
+      ols::altsum_lane(reinterpret_cast<const uint32_t*>(in + (size_t)r * T * 4), T, pad, lane, a);
+    qa[(size_t)r] = make_float4(tb.q * (float)a[0], tb.q * (float)a[1], tb.q * (float)a[2], tb.q * (float)a[3]);
+  }
+  P.qa = qa.data();
+  P.tw = tw;
+  P.gains = tb.gains.data();
+  std::vector<float4> exbuf((size_t)ols::kColWarps * ols::kExch / 2 + 8);
+  float2* ex_all = reinterpret_cast<float2*>(exbuf.data());
+  static float2 regs[ols::kColWarps][32][ols::kR];
+  auto passes = [&](float2 (*rg)[ols::kR], float2* ex) {
+    for (int q = 0; q < 4; ++q) {
+      for (int lane = 0; lane < 32; ++lane) dft<ols::kR, false>(rg[lane]);
+      if ((q & 1) == 0) {
+        for (int lane = 0; lane < 32; ++lane) ols::tw_write_col(rg[lane], lane, ex, tw);
+        for (int lane = 0; lane < 32; ++lane) ols::read_row(rg[lane], lane, ex);
+      } else if (q == 1) {
+        for (int lane = 0; lane < 32; ++lane) ols::mid_gains(rg[lane], lane, P.gains);
+      }
+    }
+  };
+  // ---- row pass ----
+  for (long long it = 0; it < P.nitems; ++it) {
+    const int pair = (int)(it & 1);
+    const long long bj = it >> 1;
+    const long long r = bj / P.nblk;
+    const int s = (int)(bj - r * P.nblk) * P.L;
+    const uint32_t* row = reinterpret_cast<const uint32_t*>(P.in + r * P.in_pitch);
+    const bool interior = s - P.pad >= 0 && s - P.pad + ols::kNB <= P.T;
+    for (int lane = 0; lane < 32; ++lane) {
+      if (interior)
+        ols::load_block<true>(regs[0][lane], P, row, s, pair, lane);
+      else
+        ols::load_block<false>(regs[0][lane], P, row, s, pair, lane);
+    }
+    passes(regs[0], ex_all);
+    const ols::RowDst d = ols::make_row_dst(P, r);
+    const float4 q4 = P.qa[r];
+    for (int lane = 0; lane < 32; ++lane)
+      ols::store_block(regs[0][lane], P, d, pair ? make_float2(q4.z, q4.w) : make_float2(q4.x, q4.y), s, pair, lane);
+  }
+  // ---- synthetic row u (colsum_kernel: 64 image rows per thread, integer atomics) ----
+  std::vector<int> u((size_t)T * 4, 0);
+  for (int r0 = 0; r0 < rows; r0 += 64)
+    for (int x = 0; x < T; ++x) {
+      int a[4] = {0, 0, 0, 0};
+      ols::colsum_lane(in, P.in_pitch, x, r0, std::min(rows, r0 + 64), pad, rows, a);
+      for (int c = 0; c < 4; ++c) u[(size_t)4 * x + c] += a[c];
+    }
+  // ---- its row pass (u_rowpass_kernel) ----
+  long long au[4] = {0, 0, 0, 0};
+  for (int x = 0; x < T; ++x)
+    for (int c = 0; c < 4; ++c) au[c] += (long long)ols::altsum_weight(x, pad, T) * u[(size_t)4 * x + c];
+  float qa_u[4];
+  for (int c = 0; c < 4; ++c) qa_u[c] = tb.q * (float)au[c];
+  std::vector<float2> qc((size_t)T * 2);
+  for (int it = 0; it < P.nblk * 2; ++it) {
+    const int pair = it & 1, s = (it >> 1) * P.L;
+    for (int lane = 0; lane < 32; ++lane) ols::load_block_u(regs[0][lane], u.data(), T, pad, s, pair, lane);
+    passes(regs[0], ex_all);
+    for (int lane = 0; lane < 32; ++lane)
+      ols::store_block_u(regs[0][lane], make_float2(qa_u[2 * pair], qa_u[2 * pair + 1]), tb.q_col, T, pad, P.L, s, pair,
+                         lane, qc.data());
+  }
+  // ---- column pass ----
+  if (T % 2) return -10;
+  ols::ColParams C{};
+  C.inter = inter.data();
+  C.panel_stride = (long long)P.blk_np * 32;
+  C.padq = padq;
+  C.T = rows;
+  C.pad = pad;
+  C.L = P.L;
+  C.nblk = (rows + C.L - 1) / C.L;
+  C.nquarters = (T + 1) / 2;
+  C.nitems = (long long)C.nquarters * C.nblk;
+  C.cols = T;
+  C.out = out;
+  C.out_pitch = (long long)T * 4;
+  C.qc = qc.data();
+  C.tw = tw;
+  C.gains = tb.gains.data();
+  std::vector<uint64_t> tilebuf(1024);
+  uint16_t* tile = reinterpret_cast<uint16_t*>(tilebuf.data());
+  for (long long it = 0; it < C.nitems; ++it) {
+    const int j = (int)(it / C.nquarters);
+    const int quarter = (int)(it - (long long)j * C.nquarters);
+    const int s = j * C.L;
+    for (int t = 0; t < 128; ++t) ols::col_fetch(C, quarter, s, t, ex_all);
+    for (int w = 0; w < ols::kColWarps; ++w) {
+      float2* ex = ex_all + w * ols::kExch;
+      for (int lane = 0; lane < 32; ++lane) ols::read_col(regs[w][lane], lane, ex);
+      passes(regs[w], ex);
+      for (int lane = 0; lane < 32; ++lane) ols::col_to_tile(regs[w][lane], C.qc[quarter * 4 + w], s, w, lane, tile);
+    }
+    for (int t = 0; t < 128; ++t) ols::col_store(C, quarter, s, t, tile);
+  }
   return 0;
 }
 

@@ -98,3 +98,63 @@ def test_emulated_rowpass_adversarial(emu, pattern):
     out, ksize, pad, n = emu(img, sigma)
     want = _oracle_rows(img, sigma, ksize, pad, n)
     assert np.abs(out - want).max() <= TOL
+
+
+@pytest.fixture(scope="module")
+def emu_blur(emu, tmp_path_factory):
+    so = tmp_path_factory.mktemp("ols2") / "libols_emu2.so"
+    cmd = ["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-w", "-I", "/usr/local/cuda/include",
+           "-I", os.path.join(ROOT, "libgaussianblur_b200", "csrc"), os.path.join(ROOT, "tests", "cpp", "ols_emulate.cpp"),
+           "-o", str(so)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    lib = ctypes.CDLL(str(so))
+    lib.ols_emulate_blur.restype = ctypes.c_int
+
+    def run(img, sigma, padq=0):
+        rows, cols, _ = img.shape
+        ksize, pad, n_rp, n_cp, _, _ = go.plan_sizes(rows, cols, sigma)
+        img = np.ascontiguousarray(img)
+        out = np.empty_like(img)
+        rc = lib.ols_emulate_blur(img.ctypes.data_as(ctypes.c_void_p), rows, cols, ctypes.c_float(sigma), ksize, n_rp, n_cp,
+                                  padq, out.ctypes.data_as(ctypes.c_void_p))
+        assert rc == 0, rc
+        return out
+
+    return run
+
+
+@pytest.mark.parametrize("rows,cols,sigma,padq", [
+    (1100, 70, 20.0, 0),     # two column blocks, last one partial
+    (2000, 68, 20.0, 18),    # three column blocks, panel slots with padding holes
+    (300, 130, 5.0, 16),     # one column block, pixel columns that are not a multiple of 8
+    (1900, 170, 50.0, 0),    # pad = 165
+    (895, 66, 20.0, 0),      # one row into a second column block
+])
+def test_emulated_two_pass_blur_matches_oracle(emu_blur, rows, cols, sigma, padq):
+    """row pass + column pass (synthetic-row Nyquist term, quarter-panel fetch, shared u8 tile) against the float64
+    oracle of the whole reference call and the compiled reference: max |delta| <= 1 LSB"""
+    img = go.synth_u8((rows, cols, 4), 0x77 + rows)
+    out = emu_blur(img, sigma, padq)
+    want = go.gaussianblur(img, sigma, True)
+    assert np.abs(out.astype(int) - want.astype(int)).max() <= 1
+    if ref_lib.available():
+        ref = ref_lib.gaussianblur(img, sigma, True)
+        assert np.abs(out.astype(int) - ref.astype(int)).max() <= 1
+
+
+@pytest.mark.parametrize("pattern", ["altrows", "altcols", "checker"])
+def test_emulated_two_pass_blur_adversarial(emu_blur, pattern):
+    """alternating rows make the column Nyquist term as large as it gets"""
+    rows, cols, sigma = 1000, 72, 20.0
+    img = np.zeros((rows, cols, 4), np.uint8)
+    if pattern == "altrows":
+        img[::2] = 255
+    elif pattern == "altcols":
+        img[:, ::2] = 255
+    else:
+        img[::2, ::2] = 255
+        img[1::2, 1::2] = 255
+    out = emu_blur(img, sigma)
+    want = go.gaussianblur(img, sigma, True)
+    assert np.abs(out.astype(int) - want.astype(int)).max() <= 1

@@ -43,6 +43,7 @@ int main(int argc, char** argv) {
   CU(cudaMemcpy(d_in, img.data(), n, cudaMemcpyHostToDevice));
 
   setenv("GBLUR_ROW_OLS", "0", 1);
+  setenv("GBLUR_COL_OLS", "0", 1);
   gblur_plan* pa = nullptr;
   CK(gblur_plan_create(&pa, 0, rows, cols, 4, sigma));
   CK(gblur_run_device(pa, d_in, d_a, 1, nullptr));
@@ -58,6 +59,8 @@ int main(int argc, char** argv) {
   // the kernel variant (GBLUR_OLS_VARIANT) is latched per process on first use: one variant per run
   // argv[4] = "auto": the library's own choice (GBLUR_ROW_OLS unset, default variant)
   const char* variant = argc > 4 ? argv[4] : "auto";
+  // argv[5] = 1: overlap-save column pass as well
+  if (argc > 5 && atoi(argv[5]) > 0) setenv("GBLUR_COL_OLS", "1", 1); else unsetenv("GBLUR_COL_OLS");
   if (variant[0] == 'a') {
     unsetenv("GBLUR_ROW_OLS");
   } else {
@@ -79,10 +82,10 @@ int main(int argc, char** argv) {
     if (d) ++ndiff;
     if (d > max_u) max_u = d;
   }
-  const float row_b = time_stage(pb, d_in, d_b, 1, 20);
-  printf("{\"path\": \"overlap_save\", \"variant\": \"%s\", \"row_ms\": %.4f, \"inter_max_abs_diff\": %.3g, "
+  const float row_b = time_stage(pb, d_in, d_b, 1, 20), col_b = time_stage(pb, d_in, d_b, 2, 20);
+  printf("{\"path\": \"overlap_save\", \"variant\": \"%s\", \"row_ms\": %.4f, \"col_ms\": %.4f, \"inter_max_abs_diff\": %.3g, "
          "\"u8_max_diff\": %d, \"u8_ndiff\": %zu, \"launches\": %llu}\n",
-         variant, row_b, max_i, max_u, ndiff, gblur_launch_count());
+         variant, row_b, col_b, max_i, max_u, ndiff, gblur_launch_count());
   fflush(stdout);
   gblur_plan_destroy(pb);
   gblur_plan_destroy(pa);
