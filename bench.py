@@ -431,6 +431,7 @@ def main():
     barrier()
     launches = gb.launch_count() - launches0
     ms_total = e0.elapsed_time(e1)
+    pass_kernels = plan.last_kernels()
 
     # ---- per-kernel durations (same stream, CUDA events) for the roofline ----
     cp = plan.processed_channels(alpha)
@@ -480,7 +481,8 @@ def main():
                        "apply_to_alpha": alpha, "frames_per_gpu_per_step": 1, "parallelism": f"frames x{world}",
                        "l2": "inputs larger than L2 (133 MB u8 + 531 MB fp32 intermediate per step)",
                        "fft_lengths": [plan.n_rowpass, plan.n_colpass],
-                       "radices": [plan.radices(0)[0], plan.radices(1)[0]]},
+                       "radices": [plan.radices(0)[0], plan.radices(1)[0]],
+                       "row_pass_kernel": pass_kernels[0], "col_pass_kernel": pass_kernels[1]},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(img.nbytes),
                     "d2h_bytes_per_step": int(img.nbytes), "ms_per_step": e2e_ms / args.steps},
             "gpu_launches": int(launches),

@@ -61,6 +61,11 @@ int gblur_plan_info(const gblur_plan* plan, int* ksize, int* pad, int* n_rowpass
 int gblur_plan_spectrum(const gblur_plan* plan, int axis, float* host_out);
 /* Stage radices chosen for an axis (for logs/tests): writes up to 5 ints, returns count via *n. */
 int gblur_plan_radices(const gblur_plan* plan, int axis, int* radices, int* n, int* static_kernel);
+/* Which kernels the last row pass / column pass launched on this plan used (for logs/tests/bench.py):
+ * 0 = whole-line transform of the reference's length (line_kernels.cuh), 1 = overlap-save over 1024-sample blocks
+ * (ols_kernels.cu; picked automatically for single-frame runs of wide RGBA images, GBLUR_ROW_OLS / GBLUR_COL_OLS = 0|1
+ * at plan creation override). Both produce the reference's result (src/gaussianblur.cpp:62-79,202-244). */
+int gblur_plan_last_kernels(const gblur_plan* plan, int* row_kind, int* col_kind);
 
 /* Host buffer in place: H2D, blur, D2H, synchronous on return. Large single images are pipelined against
  * PCIe (row chunks run under the H2D copy, column bands leave under the column pass); a batch longer than the

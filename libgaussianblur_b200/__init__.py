@@ -26,7 +26,7 @@ __all__ = ["Plan", "GblurError", "lib", "gaussianblur", "gaussianblur_module", "
 # every symbol include/gblur_capi.h declares
 EXPORTED_SYMBOLS = [
     "gblur_plan_create", "gblur_plan_create_batch", "gblur_plan_create_band", "gblur_plan_destroy",
-    "gblur_plan_info", "gblur_plan_spectrum", "gblur_plan_radices", "gblur_run_host", "gblur_run_batch_host",
+    "gblur_plan_info", "gblur_plan_spectrum", "gblur_plan_radices", "gblur_plan_last_kernels", "gblur_run_host", "gblur_run_batch_host",
     "gblur_run_device", "gblur_run_batch_device", "gblur_run_stage_device", "gblur_rowpass_device", "gblur_rowpass_split_device", "gblur_colpass_device",
     "gblur_plan_panel_geometry", "gblur_band_panel_alloc", "gblur_ipc_export", "gblur_ipc_open", "gblur_ipc_close",
     "gblur_rowpass_peer_device", "gblur_colpass_panel_device", "gblur_panel_push_device",
@@ -64,6 +64,7 @@ def lib():
         "gblur_plan_info": (C.c_int, [vp, ip, ip, ip, ip, ip, ip]),
         "gblur_plan_spectrum": (C.c_int, [vp, C.c_int, fp]),
         "gblur_plan_radices": (C.c_int, [vp, C.c_int, ip, ip, ip]),
+        "gblur_plan_last_kernels": (C.c_int, [vp, ip, ip]),
         "gblur_run_host": (C.c_int, [vp, u8p, C.c_int]),
         "gblur_run_batch_host": (C.c_int, [vp, u8p, C.c_int, C.c_int]),
         "gblur_run_device": (C.c_int, [vp, u8p, u8p, C.c_int, vp]),
@@ -203,6 +204,13 @@ class Plan:
         n, st = C.c_int(), C.c_int()
         _check(lib().gblur_plan_radices(self._h, axis, rad, C.byref(n), C.byref(st)))
         return [rad[i] for i in range(n.value)], bool(st.value)
+
+    def last_kernels(self):
+        """(row pass, column pass) kernels of the last run: "whole_line" or "overlap_save_1024"."""
+        r, c = C.c_int(), C.c_int()
+        _check(lib().gblur_plan_last_kernels(self._h, C.byref(r), C.byref(c)))
+        names = ("whole_line", "overlap_save_1024")
+        return names[r.value], names[c.value]
 
     def processed_channels(self, apply_to_alpha: bool) -> int:
         return 3 if (self.channels == 4 and not apply_to_alpha) else self.channels

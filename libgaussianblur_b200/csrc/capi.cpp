@@ -97,6 +97,7 @@ struct gblur_plan {
   int ols_mode = 2;
   // overlap-save column pass, same plan object. GBLUR_COL_OLS: 1 = wherever eligible, 0 = never, unset = kColOlsAuto
   int ols_col_mode = 0;
+  int last_row_kind = 0, last_col_kind = 0;  // kernels of the last pass launched: 0 = whole line, 1 = overlap-save
 };
 
 namespace {
@@ -244,10 +245,12 @@ int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pi
       a.inter = d_inter + (long long)row0 * pitch;
   }
   if (p->ols_row && ols::row_eligible(p->ols_row, a) &&
-      (p->ols_mode == 1 || (fused_single && ols::row_profitable(a, p->sz.n_rowpass)))) {
+      (p->ols_mode == 1 || (fused_single && p->row.lp.cluster == 1 && ols::row_profitable(a, p->sz.n_rowpass)))) {
     CU(ols::launch_row(p->ols_row, a, p->num_sms, s));
+    p->last_row_kind = 1;
     return GBLUR_OK;
   }
+  p->last_row_kind = 0;
   CU(launch_rowpass(p->row.lp, a, p->num_sms, s));
   return GBLUR_OK;
 }
@@ -302,10 +305,12 @@ int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d
     }
   }
   if (p->ols_row && ols_in && p->ols_col_mode != 0 && ols::col_eligible(p->ols_row, a) &&
-      (p->ols_col_mode == 1 || ols::col_profitable(a, p->sz.n_colpass))) {
+      (p->ols_col_mode == 1 || (p->col.lp.cluster == 1 && ols::col_profitable(a, p->sz.n_colpass)))) {
     CU(ols::launch_col(p->ols_row, a, ols_in, (long long)p->full_cols * p->channels, p->num_sms, s));
+    p->last_col_kind = 1;
     return GBLUR_OK;
   }
+  p->last_col_kind = 0;
   CU(launch_colpass(p->col.lp, a, p->num_sms, s));
   return GBLUR_OK;
 }
@@ -387,6 +392,13 @@ int gblur_plan_radices(const gblur_plan* p, int axis, int* radices, int* n, int*
     for (int s = 0; s < lp.nstages; ++s) radices[s] = lp.radix[s];
   if (n) *n = lp.nstages;
   if (static_kernel) *static_kernel = lp.static_id >= 0 ? 1 : 0;
+  return GBLUR_OK;
+}
+
+int gblur_plan_last_kernels(const gblur_plan* p, int* row_kind, int* col_kind) {
+  if (!p) return fail(GBLUR_E_INVALID, "null plan");
+  if (row_kind) *row_kind = p->last_row_kind;
+  if (col_kind) *col_kind = p->last_col_kind;
   return GBLUR_OK;
 }
 
