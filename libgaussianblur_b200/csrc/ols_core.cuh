@@ -86,32 +86,42 @@ __device__ __forceinline__ void altsum_acc(uint32_t w, int x, int pad, int T, in
   a[3] += m * (int)(w >> 24);
 }
 
+// four consecutive pixels starting at x (a multiple of 4)
+__device__ __forceinline__ void altsum_group(const uint4& v, int x, int pad, int T, int (&a)[4]) {
+  if (x > pad && x + 3 < T - 1 - pad) {  // no mirrored pixel in the group: weights +-1, alternating
+    const int sg = ((pad + x) & 1) ? -1 : 1;
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int sh = 8 * c;
+      a[c] += sg * ((int)((v.x >> sh) & 255u) - (int)((v.y >> sh) & 255u) + (int)((v.z >> sh) & 255u) -
+                    (int)((v.w >> sh) & 255u));
+    }
+  } else {
+    altsum_acc(v.x, x, pad, T, a);
+    altsum_acc(v.y, x + 1, pad, T, a);
+    altsum_acc(v.z, x + 2, pad, T, a);
+    altsum_acc(v.w, x + 3, pad, T, a);
+  }
+}
+
 // One lane's share of a row's alternating sums (the warp adds its 32 shares): 16-byte loads of four pixels when
-// the row is 16-byte aligned, groups without a mirrored pixel take the +-1 shortcut.
+// the row is 16-byte aligned, four of them issued before the first is used (the kernel is a pure stream over the
+// input: memory-level parallelism is all that matters), groups without a mirrored pixel take the +-1 shortcut.
 __device__ __forceinline__ void altsum_lane(const uint32_t* __restrict__ row, int T, int pad, int lane, int (&a)[4]) {
   int x_scalar = 0;  // first pixel the scalar loop still has to take
   if ((reinterpret_cast<uintptr_t>(row) & 15) == 0) {
     const uint4* row4 = reinterpret_cast<const uint4*>(row);
-    const int n4 = T >> 2;
-#pragma unroll 4
-    for (int g = lane; g < n4; g += 32) {
-      const uint4 v = GBLUR_OLS_LDG(row4 + g);
-      const int x = 4 * g;
-      if (x > pad && x + 3 < T - 1 - pad) {
-        const int sg = ((pad + x) & 1) ? -1 : 1;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          const int sh = 8 * c;
-          a[c] += sg * ((int)((v.x >> sh) & 255u) - (int)((v.y >> sh) & 255u) + (int)((v.z >> sh) & 255u) -
-                        (int)((v.w >> sh) & 255u));
-        }
-      } else {
-        altsum_acc(v.x, x, pad, T, a);
-        altsum_acc(v.y, x + 1, pad, T, a);
-        altsum_acc(v.z, x + 2, pad, T, a);
-        altsum_acc(v.w, x + 3, pad, T, a);
-      }
+    const int n4 = T >> 2;  // whole groups of four pixels
+    int g = lane;
+    for (; g + 96 < n4; g += 128) {  // groups g, g + 32, g + 64, g + 96 all exist
+      const uint4 v0 = GBLUR_OLS_LDG(row4 + g), v1 = GBLUR_OLS_LDG(row4 + g + 32);
+      const uint4 v2 = GBLUR_OLS_LDG(row4 + g + 64), v3 = GBLUR_OLS_LDG(row4 + g + 96);
+      altsum_group(v0, 4 * g, pad, T, a);
+      altsum_group(v1, 4 * (g + 32), pad, T, a);
+      altsum_group(v2, 4 * (g + 64), pad, T, a);
+      altsum_group(v3, 4 * (g + 96), pad, T, a);
     }
+    for (; g < n4; g += 32) altsum_group(GBLUR_OLS_LDG(row4 + g), 4 * g, pad, T, a);
     x_scalar = 4 * n4;
   }
   for (int x = x_scalar + lane; x < T; x += 32) altsum_acc(GBLUR_OLS_LDG(row + x), x, pad, T, a);
