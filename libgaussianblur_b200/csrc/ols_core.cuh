@@ -258,9 +258,9 @@ __device__ __forceinline__ void store_block(const float2 (&c)[kR], const RowPara
 // ------------------------------------------------------------------------------------------------------------
 // Column pass: fp32 panel intermediate -> u8 image (replaces the second process_channel_tiles call and
 // interleave_channels, /root/reference/src/gaussianblur.cpp:261-305, helpers.hpp:248-274).
-// One CTA of four warps takes a QUARTER PANEL (8 float columns = 2 RGBA pixels = one 32-byte sector per slot) and one
-// 1024-slot block of the padded column; warp w transforms column pair w (floats 2w, 2w+1 of the quarter) with the
-// same four-pass loop as the row pass. The slots are fetched cooperatively with 16-byte loads straight into the four
+// One CTA of CW = 4 (or 8) warps takes a QUARTER (HALF) PANEL — 8 (16) float columns = 2 (4) RGBA pixels = one (two)
+// 32-byte sectors per slot — and one 1024-slot block of the padded column; warp w transforms column pair w (floats
+// 2w, 2w+1 of the unit) with the same four-pass loop as the row pass. The slots are fetched cooperatively with 16-byte loads straight into the four
 // exchange buffers (column layout, so every lane later reads exactly what it will overwrite), the u8 results are
 // collected in a shared tile and leave as one 8-byte store per image row.
 // The reference's Nyquist term along a column needs sum_n (-1)^n I[n][w] over the padded column of the row-pass
@@ -273,8 +273,8 @@ struct ColParams {
   int padq;                 // slot holes of the whole-line column kernel's layout (0 = none)
   int T, pad;               // image rows, reflect pad
   int L, nblk;              // outputs per block, blocks per column
-  int nquarters;            // quarter panels with at least one valid pixel = ceil(cols / 2)
-  long long nitems;         // nquarters * nblk
+  int nunits;               // units (CW column pairs = CW / 2 pixels) with at least one valid pixel
+  long long nitems;         // nunits * nblk
   int cols;
   uint8_t* out;             // HWC u8, 4 channels
   long long out_pitch;      // bytes per image row
@@ -283,24 +283,28 @@ struct ColParams {
   const float* gains;
 };
 
-constexpr int kColWarps = 4;
-
-// cooperative fetch of one item: thread t of 128 takes the 16-byte half (t & 1) of slot k * 64 + (t >> 1), k < 16
-__device__ __forceinline__ void col_fetch(const ColParams& P, int quarter, int s, int t, float2* __restrict__ ex_all) {
-  const float* src = P.inter + (long long)(quarter >> 2) * P.panel_stride + (quarter & 3) * 8 + (t & 1) * 4;
-  float2* e0 = ex_all + (2 * (t & 1)) * kExch;  // exchange buffers of warps 2h and 2h + 1
+// CW = warps per CTA = column pairs per unit: 4 (quarter panel, 32 bytes per slot, 8-byte stores) or 8 (half panel,
+// 64 bytes per slot, 16-byte stores: half as many L1 line-operations per byte on both sides)
+// cooperative fetch of one item: CW/2 threads share a slot (16 bytes each); 64 slots per pass, 16 passes
+template <int CW>
+__device__ __forceinline__ void col_fetch(const ColParams& P, int unit, int s, int t, float2* __restrict__ ex_all) {
+  constexpr int TPS = CW / 2;         // threads per slot
+  constexpr int UPP = 16 / CW;        // units per panel
+  const int part = t % TPS, sl = t / TPS;
+  const float* src = P.inter + (long long)(unit / UPP) * P.panel_stride + (unit % UPP) * (2 * CW) + part * 4;
+  float2* e0 = ex_all + (2 * part) * kExch;  // exchange buffers of warps 2 * part and 2 * part + 1
   float2* e1 = e0 + kExch;
   const int nvalid = P.T + 2 * P.pad;
   float4 v[16];
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
-    const int n = s + k * 64 + (t >> 1);
+    const int n = s + k * 64 + sl;
     v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
     if (n < nvalid) v[k] = GBLUR_OLS_LDG(reinterpret_cast<const float4*>(src + (long long)phys_slot(n, P.padq) * 32));
   }
 #pragma unroll
   for (int k = 0; k < 16; ++k) {
-    const int nl = k * 64 + (t >> 1);
+    const int nl = k * 64 + sl;
     const int slot = (nl >> 5) * kRowStride + (nl & 31);
     e0[slot] = make_float2(v[k].x, v[k].y);
     e1[slot] = make_float2(v[k].z, v[k].w);
@@ -323,7 +327,8 @@ __device__ __forceinline__ uint32_t to_u8(float v) {
 #endif
 }
 
-// c[i] = conj(1024 y_lin[s + lane + 32 i]) -> two bytes per block index into the shared tile [1024][4 pairs]
+// c[i] = conj(1024 y_lin[s + lane + 32 i]) -> two bytes per block index into the shared tile [1024][CW pairs]
+template <int CW>
 __device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, int s, int w, int lane,
                                             uint16_t* __restrict__ tile) {
   const float sg = ((s + lane) & 1) ? -1.0f : 1.0f;
@@ -331,25 +336,31 @@ __device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, in
 #pragma unroll
   for (int i = 0; i < kR; ++i) {
     const uint32_t b0 = to_u8(c[i].x + add.x), b1 = to_u8(add.y - c[i].y);
-    tile[(lane + kR * i) * 4 + w] = (uint16_t)(b0 | (b1 << 8));
+    tile[(lane + kR * i) * CW + w] = (uint16_t)(b0 | (b1 << 8));
   }
 }
 
-// thread t of 128 stores block indices t + 128 k: 8 bytes (two RGBA pixels) per image row
-__device__ __forceinline__ void col_store(const ColParams& P, int quarter, int s, int t, const uint16_t* __restrict__ tile) {
+// thread t of 32 CW stores block indices t + 32 CW k: 2 CW bytes (CW / 2 RGBA pixels) per image row
+template <int CW>
+__device__ __forceinline__ void col_store(const ColParams& P, int unit, int s, int t, const uint16_t* __restrict__ tile) {
+  constexpr int PX = CW / 2;  // pixels per unit
   const int hi = min(P.pad + P.L, P.T - s + P.pad);
-  const bool both = 2 * quarter + 1 < P.cols;
-  uint8_t* base = P.out + (long long)quarter * 8;
+  const int npx = min(PX, P.cols - unit * PX);  // valid pixels of this unit (the last one may be cut)
+  uint8_t* base = P.out + (long long)unit * (4 * PX);
 #pragma unroll
-  for (int k = 0; k < 8; ++k) {
-    const int idx = t + 128 * k;
+  for (int k = 0; k < 1024 / (32 * CW); ++k) {
+    const int idx = t + 32 * CW * k;
     if (idx >= P.pad && idx < hi) {
-      const uint2 v = *reinterpret_cast<const uint2*>(tile + idx * 4);
+      const uint32_t* src = reinterpret_cast<const uint32_t*>(tile + idx * CW);
       uint8_t* dp = base + (long long)(s + idx - P.pad) * P.out_pitch;
-      if (both)
-        *reinterpret_cast<uint2*>(dp) = v;
-      else
-        *reinterpret_cast<uint32_t*>(dp) = v.x;
+      if (npx == PX) {
+        if constexpr (CW == 4)
+          *reinterpret_cast<uint2*>(dp) = *reinterpret_cast<const uint2*>(src);
+        else
+          *reinterpret_cast<uint4*>(dp) = *reinterpret_cast<const uint4*>(src);
+      } else {
+        for (int p = 0; p < npx; ++p) reinterpret_cast<uint32_t*>(dp)[p] = src[p];
+      }
     }
   }
 }

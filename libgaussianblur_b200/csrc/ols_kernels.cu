@@ -172,24 +172,24 @@ __global__ void __launch_bounds__(kUWarps * 32, 1)
   }
 }
 
-template <int MAXREG>
+template <int CW, int MAXREG>
 __global__ void __maxnreg__(MAXREG) ols_col_rgba_kernel(const __grid_constant__ ColParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float2* tw = reinterpret_cast<float2*>(smem_raw);
   float* gains = reinterpret_cast<float*>(tw + kNB);
   float2* ex_all = reinterpret_cast<float2*>(gains + kR * kGainStride);
-  uint16_t* tile = reinterpret_cast<uint16_t*>(ex_all + kColWarps * kExch);
+  uint16_t* tile = reinterpret_cast<uint16_t*>(ex_all + CW * kExch);
   const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
   float2* ex = ex_all + warp * kExch;
-  for (int i = t; i < kNB; i += kColWarps * 32) tw[i] = __ldg(P.tw + i);
-  for (int i = t; i < kR * kGainStride; i += kColWarps * 32) gains[i] = __ldg(P.gains + i);
+  for (int i = t; i < kNB; i += CW * 32) tw[i] = __ldg(P.tw + i);
+  for (int i = t; i < kR * kGainStride; i += CW * 32) gains[i] = __ldg(P.gains + i);
   // no barrier needed here: the first one inside the loop also publishes the tables
   for (long long it = blockIdx.x; it < P.nitems; it += gridDim.x) {
-    // consecutive items = neighbouring quarter panels of the same block: their 32-byte sectors share 128-byte lines
-    const int j = (int)(it / P.nquarters);
-    const int quarter = (int)(it - (long long)j * P.nquarters);
+    // consecutive items = neighbouring units of the same block: their sectors share 128-byte lines
+    const int j = (int)(it / P.nunits);
+    const int unit = (int)(it - (long long)j * P.nunits);
     const int s = j * P.L;
-    col_fetch(P, quarter, s, t, ex_all);
+    col_fetch<CW>(P, unit, s, t, ex_all);
     __syncthreads();
     float2 c[kR];
     read_col(c, lane, ex);
@@ -205,9 +205,9 @@ __global__ void __maxnreg__(MAXREG) ols_col_rgba_kernel(const __grid_constant__ 
         mid_gains(c, lane, gains);
       }
     }
-    col_to_tile(c, __ldg(P.qc + quarter * 4 + warp), s, warp, lane, tile);
+    col_to_tile<CW>(c, __ldg(P.qc + unit * CW + warp), s, warp, lane, tile);
     __syncthreads();
-    col_store(P, quarter, s, t, tile);
+    col_store<CW>(P, unit, s, t, tile);
     // the next fetch overwrites exchange buffers every warp has finished with (barrier above); the next
     // col_to_tile comes after the next barrier, when every thread has left this col_store
   }
@@ -347,10 +347,39 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
   }
 }
 
+namespace {
+template <int CW>
+cudaError_t launch_col_blocks(ColParams P, int num_sms, cudaStream_t stream) {
+  constexpr size_t tables = (size_t)kNB * 8 + (size_t)kR * kGainStride * 4;
+  constexpr size_t csmem = tables + (size_t)CW * kExch * 8 + (size_t)kNB * CW * sizeof(uint16_t);
+  P.nunits = (P.cols + CW / 2 - 1) / (CW / 2);
+  P.nitems = (long long)P.nunits * P.nblk;
+  auto k = ols_col_rgba_kernel<CW, 128>;
+  static thread_local int c_device = -1, c_per_sm = 0;
+  int device = 0;
+  cudaGetDevice(&device);
+  if (c_device != device) {
+    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem);
+    if (e != cudaSuccess) return e;
+    int per_sm = 0;
+    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, CW * 32, csmem);
+    if (e != cudaSuccess) return e;
+    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+    c_device = device;
+    c_per_sm = per_sm;
+  }
+  long long grid = (long long)num_sms * c_per_sm;
+  if (grid > P.nitems) grid = P.nitems;
+  k<<<(unsigned)grid, CW * 32, csmem, stream>>>(P);
+  count_launch();
+  return cudaGetLastError();
+}
+}  // namespace
+
 bool col_eligible(const RowPlan* p, const ColLaunch& a) {
   return p && p->q_col != 0.f && a.C == 4 && a.Cp == 4 && a.frames == 1 && a.blk.enabled && a.panel_in == 0 &&
-         a.w_begin == 0 && (a.w_end == 0 || a.w_end == a.W) && (a.W % 8) == 0 &&
-         (reinterpret_cast<uintptr_t>(a.out) % 8) == 0 && (a.out_pitch % 8) == 0 &&
+         a.w_begin == 0 && (a.w_end == 0 || a.w_end == a.W) && (a.W % 16) == 0 &&
+         (reinterpret_cast<uintptr_t>(a.out) % 16) == 0 && (a.out_pitch % 16) == 0 &&
          (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0 && 2 * a.pad + 1 == p->ksize && a.pad <= kMaxPad && a.T >= 1;
 }
 
@@ -407,32 +436,18 @@ cudaError_t launch_col(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long
   P.pad = a.pad;
   P.L = kNB - 2 * a.pad;
   P.nblk = (rows + P.L - 1) / P.L;
-  P.nquarters = (cols + 1) / 2;
-  P.nitems = (long long)P.nquarters * P.nblk;
   P.cols = cols;
   P.out = a.out;
   P.out_pitch = a.out_pitch;
   P.qc = p->d_qc;
   P.tw = p->d_tw;
   P.gains = p->d_gains;
-  constexpr size_t csmem = tables + (size_t)kColWarps * kExch * 8 + (size_t)kNB * 4 * sizeof(uint16_t);
-  auto k = ols_col_rgba_kernel<128>;
-  static thread_local int c_device = -1, c_per_sm = 0;
-  if (c_device != device) {
-    e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem);
-    if (e != cudaSuccess) return e;
-    int per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kColWarps * 32, csmem);
-    if (e != cudaSuccess) return e;
-    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-    c_device = device;
-    c_per_sm = per_sm;
-  }
-  long long grid = (long long)num_sms * c_per_sm;
-  if (grid > P.nitems) grid = P.nitems;
-  k<<<(unsigned)grid, kColWarps * 32, csmem, stream>>>(P);
-  count_launch();
-  return cudaGetLastError();
+  // GBLUR_OLS_COL_VARIANT: 0 = four warps per quarter panel (4 CTAs per SM), 1 = eight warps per half panel (2 CTAs)
+  static const int variant = [] {
+    const char* v = getenv("GBLUR_OLS_COL_VARIANT");
+    return v ? atoi(v) : 0;
+  }();
+  return variant == 1 ? launch_col_blocks<8>(P, num_sms, stream) : launch_col_blocks<4>(P, num_sms, stream);
 }
 
 }  // namespace ols

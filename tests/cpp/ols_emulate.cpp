@@ -104,11 +104,14 @@ int ols_emulate_rowpass(const uint8_t* in, int rows, int T, float sigma, int ksi
   return 0;
 }
 
+}  // extern "C"
+
 // Whole blur through the emulated kernels: row pass into the panel intermediate, column sums -> synthetic row u ->
 // its row pass -> column terms, then the column pass (four warps per quarter panel, 128 emulated threads).
 // in / out: rows x cols RGBA u8. Returns 0 or a negative code.
-int ols_emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksize, int n_row, int n_col, int padq,
-                     uint8_t* out) {
+template <int CW>
+static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksize, int n_row, int n_col, int padq,
+                        uint8_t* out) {
   const std::vector<float> taps = host::gaussian_taps(sigma, ksize);
   const ols::HostTables tb = ols::build_tables(taps, n_row, n_col);
   const int pad = (ksize - 1) / 2, T = cols;
@@ -138,9 +141,9 @@ int ols_emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksi
   P.qa = qa.data();
   P.tw = tw;
   P.gains = tb.gains.data();
-  std::vector<float4> exbuf((size_t)ols::kColWarps * ols::kExch / 2 + 8);
+  std::vector<float4> exbuf((size_t)CW * ols::kExch / 2 + 8);
   float2* ex_all = reinterpret_cast<float2*>(exbuf.data());
-  static float2 regs[ols::kColWarps][32][ols::kR];
+  static float2 regs[CW][32][ols::kR];
   auto passes = [&](float2 (*rg)[ols::kR], float2* ex) {
     for (int q = 0; q < 4; ++q) {
       for (int lane = 0; lane < 32; ++lane) dft<ols::kR, false>(rg[lane]);
@@ -196,7 +199,7 @@ int ols_emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksi
                          lane, qc.data());
   }
   // ---- column pass ----
-  if (T % 2) return -10;
+  if (T % (CW / 2)) return -10;
   ols::ColParams C{};
   C.inter = inter.data();
   C.panel_stride = (long long)P.blk_np * 32;
@@ -205,30 +208,35 @@ int ols_emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksi
   C.pad = pad;
   C.L = P.L;
   C.nblk = (rows + C.L - 1) / C.L;
-  C.nquarters = (T + 1) / 2;
-  C.nitems = (long long)C.nquarters * C.nblk;
+  C.nunits = (T + CW / 2 - 1) / (CW / 2);
+  C.nitems = (long long)C.nunits * C.nblk;
   C.cols = T;
   C.out = out;
   C.out_pitch = (long long)T * 4;
   C.qc = qc.data();
   C.tw = tw;
   C.gains = tb.gains.data();
-  std::vector<uint64_t> tilebuf(1024);
+  std::vector<uint64_t> tilebuf(1024 * CW / 4);
   uint16_t* tile = reinterpret_cast<uint16_t*>(tilebuf.data());
   for (long long it = 0; it < C.nitems; ++it) {
-    const int j = (int)(it / C.nquarters);
-    const int quarter = (int)(it - (long long)j * C.nquarters);
+    const int j = (int)(it / C.nunits);
+    const int unit = (int)(it - (long long)j * C.nunits);
     const int s = j * C.L;
-    for (int t = 0; t < 128; ++t) ols::col_fetch(C, quarter, s, t, ex_all);
-    for (int w = 0; w < ols::kColWarps; ++w) {
+    for (int t = 0; t < 32 * CW; ++t) ols::col_fetch<CW>(C, unit, s, t, ex_all);
+    for (int w = 0; w < CW; ++w) {
       float2* ex = ex_all + w * ols::kExch;
       for (int lane = 0; lane < 32; ++lane) ols::read_col(regs[w][lane], lane, ex);
       passes(regs[w], ex);
-      for (int lane = 0; lane < 32; ++lane) ols::col_to_tile(regs[w][lane], C.qc[quarter * 4 + w], s, w, lane, tile);
+      for (int lane = 0; lane < 32; ++lane) ols::col_to_tile<CW>(regs[w][lane], C.qc[unit * CW + w], s, w, lane, tile);
     }
-    for (int t = 0; t < 128; ++t) ols::col_store(C, quarter, s, t, tile);
+    for (int t = 0; t < 32 * CW; ++t) ols::col_store<CW>(C, unit, s, t, tile);
   }
   return 0;
 }
 
-}  // extern "C"
+extern "C" int ols_emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksize, int n_row, int n_col,
+                                int padq, int cw, uint8_t* out) {
+  return cw == 8 ? emulate_blur<8>(in, rows, cols, sigma, ksize, n_row, n_col, padq, out)
+                 : emulate_blur<4>(in, rows, cols, sigma, ksize, n_row, n_col, padq, out);
+}
+
