@@ -127,6 +127,20 @@ __device__ __forceinline__ void altsum_lane(const uint32_t* __restrict__ row, in
   for (int x = x_scalar + lane; x < T; x += 32) altsum_acc(GBLUR_OLS_LDG(row + x), x, pad, T, a);
 }
 
+// The same sums split over `nthreads` cooperating threads (row-per-CTA kernel): thread `tid` takes the groups of four
+// pixels tid, tid + nthreads, ...
+__device__ __forceinline__ void altsum_part(const uint32_t* __restrict__ row, int T, int pad, int tid, int nthreads,
+                                            int (&a)[4]) {
+  int x_scalar = 0;
+  if ((reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+    const uint4* row4 = reinterpret_cast<const uint4*>(row);
+    const int n4 = T >> 2;
+    for (int g = tid; g < n4; g += nthreads) altsum_group(GBLUR_OLS_LDG(row4 + g), 4 * g, pad, T, a);
+    x_scalar = 4 * n4;
+  }
+  for (int x = x_scalar + tid; x < T; x += nthreads) altsum_acc(GBLUR_OLS_LDG(row + x), x, pad, T, a);
+}
+
 // bytes (2 * pair, 2 * pair + 1) of an RGBA word as a complex sample
 __device__ __forceinline__ float2 u8_pair(uint32_t w, int pair) {
 #if defined(__CUDA_ARCH__)

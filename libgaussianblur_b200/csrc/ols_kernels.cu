@@ -95,6 +95,64 @@ __global__ void __maxnreg__(MAXREG) ols_row_rgba_kernel(const __grid_constant__ 
   }
 }
 
+// Variant 5 (GBLUR_OLS_VARIANT=5, not measured yet): one CTA per row with one warp per item of the row (2 * nblk <= 20
+// warps), no pre-kernel. The warps first add up the row's alternating sums together (each reads 1 / nwarps of the row,
+// which the block loads touch again right afterwards), one CTA barrier per row, then run their blocks as above.
+__global__ void __maxnreg__(96) ols_row_cta_kernel(const __grid_constant__ RowParams P, float q_row) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float2* tw = reinterpret_cast<float2*>(smem_raw);
+  float* gains = reinterpret_cast<float*>(tw + kNB);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
+  float2* ex = reinterpret_cast<float2*>(gains + kR * kGainStride) + warp * kExch;
+  __shared__ int part[2][20][4];
+  for (int i = threadIdx.x; i < kNB; i += blockDim.x) tw[i] = __ldg(P.tw + i);
+  for (int i = threadIdx.x; i < kR * kGainStride; i += blockDim.x) gains[i] = __ldg(P.gains + i);
+  const long long nrows = P.nitems / (2 * P.nblk);
+  const int pair = warp & 1, s = (warp >> 1) * P.L;
+  int par = 0;
+  for (long long r = blockIdx.x; r < nrows; r += gridDim.x, par ^= 1) {
+    const uint32_t* row = reinterpret_cast<const uint32_t*>(P.in + r * P.in_pitch);
+    int a[4] = {0, 0, 0, 0};
+    altsum_part(row, P.T, P.pad, (int)threadIdx.x, (int)blockDim.x, a);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) a[c] += __shfl_xor_sync(0xffffffffu, a[c], o);
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int c = 0; c < 4; ++c) part[par][warp][c] = a[c];
+    }
+    float2 c[kR];
+    if (s - P.pad >= 0 && s - P.pad + kNB <= P.T)
+      load_block<true>(c, P, row, s, pair, lane);
+    else
+      load_block<false>(c, P, row, s, pair, lane);
+    // the barrier also publishes the tables on the first row; part[par] is rewritten two rows later, after the
+    // barrier of the next row, which every warp reaches only when it is done with this row's sums
+    __syncthreads();
+    int s0 = 0, s1 = 0;
+    for (int w = 0; w < nwarps; ++w) {
+      s0 += part[par][w][2 * pair];
+      s1 += part[par][w][2 * pair + 1];
+    }
+#pragma unroll 1
+    for (int q = 0; q < 4; ++q) {
+      dft<kR, false>(c);
+      if ((q & 1) == 0) {
+        tw_write_col(c, lane, ex, tw);
+        __syncwarp();
+        read_row(c, lane, ex);
+        __syncwarp();
+      } else if (q == 1) {
+        mid_gains(c, lane, gains);
+      }
+    }
+    const RowDst d = make_row_dst(P, r);
+    store_block(c, P, d, make_float2(q_row * (float)s0, q_row * (float)s1), s, pair, lane);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // column pass
 // ---------------------------------------------------------------------------------------------------------------
@@ -315,6 +373,32 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
   P.tw = p->d_tw;
   P.gains = p->d_gains;
 
+  // warps per CTA / register cap; resident warps per SM: 20 in two CTAs (default: 0.362 ms on 8K RGBA against 0.375
+  // for 16 in one CTA and 0.38 for 16 in two or four, profiles/r01/ols_rowpass_v2_check.jsonl), 16, 16, 24, 16;
+  // 5 = one CTA per row without the pre-kernel (rows of at most 10 blocks)
+  static const int variant = [] {
+    const char* v = getenv("GBLUR_OLS_VARIANT");
+    return v ? atoi(v) : 1;
+  }();
+  if (variant == 5 && 2 * P.nblk <= 20) {
+    const int nwarps = 2 * P.nblk;
+    const size_t smem = (size_t)kNB * 8 + (size_t)kR * kGainStride * 4 + (size_t)nwarps * kExch * 8;
+    static thread_local int cta_device = -1;
+    int device = 0;
+    cudaGetDevice(&device);
+    if (cta_device != device) {
+      cudaError_t ea = cudaFuncSetAttribute(ols_row_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)((size_t)kNB * 8 + (size_t)kR * kGainStride * 4 + (size_t)20 * kExch * 8));
+      if (ea != cudaSuccess) return ea;
+      cta_device = device;
+    }
+    long long grid = num_sms;
+    if (grid > a.rows_total) grid = a.rows_total;
+    ols_row_cta_kernel<<<(unsigned)grid, nwarps * 32, smem, stream>>>(P, p->q);
+    count_launch();
+    return cudaGetLastError();
+  }
+
   // timing aid only: GBLUR_OLS_NO_ALTSUM=1 reuses the sums of the previous call on this plan (same input assumed)
   static const bool reuse_sums = getenv("GBLUR_OLS_NO_ALTSUM") != nullptr;
   cudaError_t e = cudaSuccess;
@@ -327,12 +411,6 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
     p->qa_valid = true;
   }
 
-  // warps per CTA / register cap; resident warps per SM: 20 in two CTAs (default: 0.362 ms on 8K RGBA against 0.375
-  // for 16 in one CTA and 0.38 for 16 in two or four, profiles/r01/ols_rowpass_v2_check.jsonl), 16, 16, 24, 16
-  static const int variant = [] {
-    const char* v = getenv("GBLUR_OLS_VARIANT");
-    return v ? atoi(v) : 1;
-  }();
   switch (variant) {
     case 0:
       return launch_blocks<8, 128>(P, num_sms, stream);

@@ -53,6 +53,13 @@ int ols_emulate_rowpass(const uint8_t* in, int rows, int T, float sigma, int ksi
       for (int ch = 0; ch < 4; ++ch) chk[ch] += ols::altsum_weight(x, pad, T) * (int)in[((size_t)r * T + x) * 4 + ch];
     for (int ch = 0; ch < 4; ++ch)
       if (chk[ch] != a[ch]) return -3;
+    // the row-per-CTA kernel's split of the same sums over 2 * nblk warps
+    int b[4] = {0, 0, 0, 0};
+    const int nthreads = 64 * P.nblk;
+    for (int tid = 0; tid < nthreads; ++tid)
+      ols::altsum_part(reinterpret_cast<const uint32_t*>(in + (size_t)r * T * 4), T, pad, tid, nthreads, b);
+    for (int ch = 0; ch < 4; ++ch)
+      if (chk[ch] != b[ch]) return -4;
     qa[(size_t)r] = make_float4(tb.q * (float)a[0], tb.q * (float)a[1], tb.q * (float)a[2], tb.q * (float)a[3]);
   }
   P.qa = qa.data();

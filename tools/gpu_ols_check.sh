@@ -10,3 +10,6 @@ GBLUR_OLS_COL_VARIANT=1 run 4320 7680 20 auto 1
 run 1500 4100 7 1 1
 GBLUR_OLS_COL_VARIANT=1 run 1500 4100 7 1 1
 run 160 7680 20 1 1
+# row variants: 5 = one CTA per row, alternating sums inside the block kernel (no pre-kernel)
+run 4320 7680 20 5 0
+run 1500 4100 7 5 0
