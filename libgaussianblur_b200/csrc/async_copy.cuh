@@ -57,6 +57,23 @@ __device__ __forceinline__ void tma_load_3d(void* dst_smem, const void* tensor_m
       : "memory");
 }
 
+// TMA tiled store of a 3-D box from shared memory (bulk async-group completion)
+__device__ __forceinline__ void tma_store_3d(const void* tensor_map, int c0, int c1, int c2, const void* src_smem) {
+  asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.tile.bulk_group [%0, {%1, %2, %3}], [%4];" ::"l"(tensor_map),
+               "r"(c0), "r"(c1), "r"(c2), "r"(smem_addr(src_smem))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// all but the N most recent bulk groups of this thread have finished READING their shared-memory source
+template <int N>
+__device__ __forceinline__ void bulk_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void bulk_wait() {
+  asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory");
+}
+
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   asm volatile(
       "{\n"

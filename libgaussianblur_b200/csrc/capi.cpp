@@ -23,7 +23,7 @@ using namespace gblur;
 namespace {
 
 // default of the overlap-save column pass when GBLUR_COL_OLS is unset: 0 = off, 2 = automatic (ols::col_profitable)
-constexpr int kColOlsAuto = 0;
+constexpr int kColOlsAuto = 2;
 
 thread_local std::string g_err;
 
@@ -135,14 +135,15 @@ int processed_channels(const gblur_plan* p, int apply_to_alpha) {
 long long default_pitch(long long w) { return (w + 3) / 4 * 4; }
 
 // Panel intermediate of the fused run: [panel of 32 float columns][np slots][32 floats].
-BlockedLayout blocked_layout(const gblur_plan* p, int cp) {
+// ols_col: the overlap-save column pass will read it (TMA boxes of consecutive slots): no bank-padding holes.
+BlockedLayout blocked_layout(const gblur_plan* p, int cp, bool ols_col = false) {
   BlockedLayout b;
   const LinePlan& c = p->col.lp;
   b.enabled = 1;
   b.L = 2 * c.nseq;
   // cluster column plans read the panel through their loader: natural slot order, no padding holes
-  b.np = c.cluster > 1 ? c.N : c.exch_elems;
-  b.padq = c.cluster > 1 ? 0 : c.padq;
+  b.np = (c.cluster > 1 || ols_col) ? c.N : c.exch_elems;
+  b.padq = (c.cluster > 1 || ols_col) ? 0 : c.padq;
   b.rows_per_frame = p->full_rows;
   const long long panels = ((long long)p->cols * cp + 31) / 32;
   b.frame_stride = panels * b.np * 32;
@@ -218,6 +219,18 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
   return GBLUR_OK;
 }
 
+// Will the overlap-save column pass (ols.h) take a fused run with `cp` processed channels and `frames` frames? Decided
+// before the row pass, because the panel layout it reads has no bank-padding holes.
+bool ols_col_wanted(const gblur_plan* p, int cp, int frames) {
+  if (!p->ols_row || p->ols_col_mode == 0 || p->band || p->channels != 4 || cp != 4 || frames != 1) return false;
+  if (((long long)p->cols * cp) % 16 || ((long long)p->full_cols * p->channels) % 16) return false;
+  if (p->ols_col_mode == 1) return true;
+  ColLaunch a{};
+  a.T = p->full_rows;
+  a.pad = p->sz.pad;
+  return p->col.lp.cluster == 1 && ols::col_profitable(a, p->sz.n_colpass);
+}
+
 // rows_sub > 0: only rows [row0, row0 + rows_sub) of a single frame (d_in / d_inter still point at row 0)
 int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pitch, int frames, int alpha,
                 cudaStream_t s, const BlockedLayout* blk = nullptr, int split_cols = 0, long long split_stride = 0,
@@ -274,11 +287,12 @@ bool panel_tensor_map(gblur_plan* p, const float* base, const BlockedLayout& b, 
 }
 
 // w_end > 0: only the float columns [w_begin, w_end) (w_begin a multiple of 32) of a single frame
-// ols_in: the u8 image the intermediate was computed from (single-frame fused runs only): lets the overlap-save
-// column pass form the column term of the reference's Nyquist behaviour (ols_core.cuh)
+// ols_in: the u8 image the intermediate was computed from (single-frame fused runs only): the overlap-save column pass
+// forms the column term of the reference's Nyquist behaviour from it (ols_core.cuh); ols_terms = false reuses the terms
+// of the previous launch on this plan (column bands of one image)
 int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d_out, long long out_pitch, int frames,
                 int alpha, cudaStream_t s, const BlockedLayout* blk = nullptr, int w_begin = 0, int w_end = 0,
-                const uint8_t* ols_in = nullptr) {
+                const uint8_t* ols_in = nullptr, bool ols_terms = true) {
   const int cp = processed_channels(p, alpha);
   ColLaunch a{};
   a.inter = d_inter;
@@ -299,17 +313,19 @@ int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d
     a.blk = *blk;
     a.panel_in = p->col.lp.cluster > 1 ? 1 : 0;
     const long long panels = ((long long)p->cols * cp + 31) / 32 * frames;
-    if (p->col.lp.cluster == 1 && panel_tensor_map(p, d_inter, *blk, panels)) {
+    if (p->col.lp.cluster == 1 && blk->padq == p->col.lp.padq && panel_tensor_map(p, d_inter, *blk, panels)) {
       a.tmap = &p->tmap;
       a.tma_rows = p->tmap_rows;
     }
   }
-  if (p->ols_row && ols_in && p->ols_col_mode != 0 && ols::col_eligible(p->ols_row, a) &&
-      (p->ols_col_mode == 1 || (p->col.lp.cluster == 1 && ols::col_profitable(a, p->sz.n_colpass)))) {
-    CU(ols::launch_col(p->ols_row, a, ols_in, (long long)p->full_cols * p->channels, p->num_sms, s));
+  if (ols_in && blk && blk->padq == 0 && ols_col_wanted(p, cp, frames) && ols::col_eligible(p->ols_row, a)) {
+    if (ols_terms) CU(ols::launch_col_terms(p->ols_row, a, ols_in, (long long)p->full_cols * p->channels, s));
+    CU(ols::launch_col(p->ols_row, a, p->num_sms, s));
     p->last_col_kind = 1;
     return GBLUR_OK;
   }
+  if (blk && blk->padq != p->col.lp.padq && p->col.lp.cluster == 1)
+    return fail(GBLUR_E_UNSUPPORTED, "panel layout without padding holes, but the overlap-save column pass is not eligible");
   p->last_col_kind = 0;
   CU(launch_colpass(p->col.lp, a, p->num_sms, s));
   return GBLUR_OK;
@@ -427,7 +443,8 @@ int fused_prepare(gblur_plan* p, int n_frames, int apply_to_alpha, cudaStream_t 
     const char* e = getenv("GBLUR_LAYOUT");
     return e && std::strcmp(e, "rowmajor") == 0;
   }();
-  c.blk = blocked_layout(p, c.cp);
+  const bool ols_col = ols_col_wanted(p, c.cp, n_frames);
+  c.blk = blocked_layout(p, c.cp, ols_col);
   // single-GPU run with a cluster column pass: the row-major intermediate is a little faster (cheaper stores)
   static const bool panel_forced = [] {
     const char* e = getenv("GBLUR_LAYOUT");
@@ -436,7 +453,7 @@ int fused_prepare(gblur_plan* p, int n_frames, int apply_to_alpha, cudaStream_t 
   const bool use_rowmajor = rowmajor || (p->col.lp.cluster > 1 && !panel_forced);
   c.bp = use_rowmajor ? nullptr : &c.blk;
   c.pitch = default_pitch((long long)p->cols * c.cp);
-  const int layout_tag = use_rowmajor ? -c.cp : c.cp;
+  const int layout_tag = use_rowmajor ? -c.cp : (ols_col ? c.cp + 16 : c.cp);
   if (p->inter_cp != 0 && p->inter_cp != layout_tag) {
     // the zero tail / padding slots of the new layout may hold samples of the old one
     CU(cudaMemsetAsync(p->d_inter, 0, p->inter_floats * sizeof(float), s));
@@ -525,7 +542,7 @@ int run_host_single_pipelined(gblur_plan* p, uint8_t* hwc, int alpha, int K) {
                        cudaMemcpyHostToDevice, p->s_in));
     CU(cudaEventRecord(p->events[k], p->s_in));
     CU(cudaStreamWaitEvent(sc, p->events[k], 0));
-    rc = run_rowpass(p, p->d_stage, p->d_inter, c.pitch, 1, alpha, sc, c.bp, 0, 0, r0, r1 - r0);
+    rc = run_rowpass(p, p->d_stage, p->d_inter, c.pitch, 1, alpha, sc, c.bp, 0, 0, r0, r1 - r0, true);
     if (rc != GBLUR_OK) return rc;
   }
   // column bands on 32-pixel boundaries (=> float-column boundaries on multiples of 32 for any Cp)
@@ -533,7 +550,8 @@ int run_host_single_pipelined(gblur_plan* p, uint8_t* hwc, int alpha, int K) {
   int e = K;
   for (int x0 = 0; x0 < p->cols; x0 += px_per_band, ++e) {
     const int x1 = std::min(p->cols, x0 + px_per_band);
-    rc = run_colpass(p, p->d_inter, c.pitch, p->d_stage, (long long)row_bytes, 1, alpha, sc, c.bp, x0 * c.cp, x1 * c.cp);
+    rc = run_colpass(p, p->d_inter, c.pitch, p->d_stage, (long long)row_bytes, 1, alpha, sc, c.bp, x0 * c.cp, x1 * c.cp,
+                     p->d_stage, x0 == 0);
     if (rc != GBLUR_OK) return rc;
     CU(cudaEventRecord(p->events[e], sc));
     CU(cudaStreamWaitEvent(p->s_out, p->events[e], 0));
@@ -803,7 +821,8 @@ int gblur_dump_intermediate(gblur_plan* p, float* host_out, int apply_to_alpha) 
   if (!p->d_inter || p->inter_cp == 0) return fail(GBLUR_E_INVALID, "no run has happened on this plan");
   DeviceGuard guard(p->device);
   const int cp = processed_channels(p, apply_to_alpha);
-  if (cp != p->inter_cp && -cp != p->inter_cp) return fail(GBLUR_E_INVALID, "last run used a different apply_to_alpha");
+  if (cp != p->inter_cp && -cp != p->inter_cp && cp + 16 != p->inter_cp)
+    return fail(GBLUR_E_INVALID, "last run used a different apply_to_alpha");
   if (p->inter_cp < 0) {  // row-major layout
     const long long w = (long long)p->cols * cp, pitch = default_pitch(w);
     CU(cudaDeviceSynchronize());
@@ -811,7 +830,7 @@ int gblur_dump_intermediate(gblur_plan* p, float* host_out, int apply_to_alpha) 
                     (size_t)w * sizeof(float), (size_t)p->rows, cudaMemcpyDeviceToHost));
     return GBLUR_OK;
   }
-  const BlockedLayout b = blocked_layout(p, cp);
+  const BlockedLayout b = blocked_layout(p, cp, p->inter_cp > 16);
   std::vector<float> blk((size_t)b.frame_stride);
   CU(cudaDeviceSynchronize());
   CU(cudaMemcpy(blk.data(), p->d_inter, blk.size() * sizeof(float), cudaMemcpyDeviceToHost));

@@ -56,21 +56,74 @@ __host__ __device__ constexpr int ct_modinv(int a, int m) {  // a^{-1} mod m, gc
 
 // ------------------------------------------------------------------------------------------
 // complex helpers
+//
+// sm_100a issues fp32 either as scalar FADD/FMUL/FFMA or as the packed pair FADD2/FMUL2/FFMA2 (PTX
+// add/mul/fma.rn.f32x2) on a 64-bit register pair. Measured on B200 (profiles/r02/ubench_fp32_v1.jsonl,
+// ubench_issue_v1.jsonl): both forms deliver the same 128 results per clock and SM — a packed instruction holds
+// the fp32 pipe for two cycles — but it takes ONE issue slot for two results, and these kernels are issue-bound
+// (ncu: "not selected" is the top stall reason). A complex value (re, im) is such a pair, so a complex add is one
+// instruction and a real scale one. The catch: ptxas folds a component swap of a packed operand into the
+// instruction (R.F32x2.LO_HI) and that form costs 3.5-4 pipe cycles instead of 2, which made the first all-packed
+// version of these butterflies SLOWER than the scalar one (row blocks 0.317 -> 0.350 ms on 8K RGBA). So every
+// operation that needs the cross term of a complex product or a quarter turn (+-i) is written in scalar form,
+// where the swap is a register renaming, and only the swap-free operations are packed:
+//   cadd / csub / cscale : FADD2 / FMUL2                                  (1 slot,  2 pipe cycles)
+//   a +- (+-i) b         : two scalar FADD                                (2 slots, 2 pipe cycles)
+//   v * (wr + i wi)      : FMUL2 by wr, two scalar FFMA for the wi terms  (3 slots, 4 pipe cycles; scalar: 4 slots)
+// Host builds (tests/cpp/ols_emulate.cpp) take the scalar definitions below.
 // ------------------------------------------------------------------------------------------
-__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
-__device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
-// v * (wr + i wi)
-__device__ __forceinline__ float2 cmul(float2 v, float2 w) {
-  return make_float2(fmaf(v.x, w.x, -v.y * w.y), fmaf(v.x, w.y, v.y * w.x));
+#if defined(__CUDA_ARCH__) && (__CUDA_ARCH__ >= 1000) && !defined(GBLUR_NO_PACKED_F32)
+#define GBLUR_PACKED_F32 1
+__device__ __forceinline__ float2 pk_add(float2 a, float2 b) { return __fadd2_rn(a, b); }
+__device__ __forceinline__ float2 pk_mul(float2 a, float2 b) { return __fmul2_rn(a, b); }
+__device__ __forceinline__ float2 pk_fma(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+#else
+__device__ __forceinline__ float2 pk_add(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
+__device__ __forceinline__ float2 pk_mul(float2 a, float2 b) { return make_float2(a.x * b.x, a.y * b.y); }
+__device__ __forceinline__ float2 pk_fma(float2 a, float2 b, float2 c) {
+  return make_float2(fmaf(a.x, b.x, c.x), fmaf(a.y, b.y, c.y));
 }
-// v * conj(w)
-__device__ __forceinline__ float2 cmulc(float2 v, float2 w) {
-  return make_float2(fmaf(v.x, w.x, v.y * w.y), fmaf(v.y, w.x, -v.x * w.y));
+#endif
+__device__ __forceinline__ float2 pk_bc(float s) { return make_float2(s, s); }  // scalar on both halves
+__device__ __forceinline__ float2 pk_neg(float2 a) { return make_float2(-a.x, -a.y); }
+
+__device__ __forceinline__ float2 cadd(float2 a, float2 b) { return pk_add(a, b); }
+__device__ __forceinline__ float2 csub(float2 a, float2 b) { return pk_add(a, pk_neg(b)); }
+// v * s, s real
+__device__ __forceinline__ float2 cscale(float2 v, float s) { return pk_mul(v, pk_bc(s)); }
+// a + i b, a - i b (scalar on purpose, see above)
+__device__ __forceinline__ float2 cadd_pi(float2 a, float2 b) { return make_float2(a.x - b.y, a.y + b.x); }
+__device__ __forceinline__ float2 cadd_mi(float2 a, float2 b) { return make_float2(a.x + b.y, a.y - b.x); }
+// a + t * (+-i b) with a real factor t: two scalar FFMA
+__device__ __forceinline__ float2 cfma_pi(float2 a, float t, float2 b) {
+  return make_float2(fmaf(-b.y, t, a.x), fmaf(b.x, t, a.y));
 }
-// multiply by -i (forward quarter turn) or +i (inverse)
+__device__ __forceinline__ float2 cfma_mi(float2 a, float t, float2 b) {
+  return make_float2(fmaf(b.y, t, a.x), fmaf(-b.x, t, a.y));
+}
+// v * (wr + i wi) = v wr + (i v) wi
+__device__ __forceinline__ float2 cmul(float2 v, float2 w) { return cfma_pi(cscale(v, w.x), w.y, v); }
+// v * conj(w) = v wr - (i v) wi
+__device__ __forceinline__ float2 cmulc(float2 v, float2 w) { return cfma_mi(cscale(v, w.x), w.y, v); }
+// multiply by -i (forward quarter turn) or +i (inverse): a value whose halves are exchanged; a packed consumer
+// pays for the swap, so the butterflies below avoid it wherever they can (cadd_rot / csub_rot)
 template <bool INV>
 __device__ __forceinline__ float2 rot90(float2 v) {
   return INV ? make_float2(-v.y, v.x) : make_float2(v.y, -v.x);
+}
+// a + rot90<INV>(b), a - rot90<INV>(b)
+template <bool INV>
+__device__ __forceinline__ float2 cadd_rot(float2 a, float2 b) {
+  return INV ? cadd_pi(a, b) : cadd_mi(a, b);
+}
+template <bool INV>
+__device__ __forceinline__ float2 csub_rot(float2 a, float2 b) {
+  return INV ? cadd_mi(a, b) : cadd_pi(a, b);
+}
+// a + t * rot90<INV>(b)
+template <bool INV>
+__device__ __forceinline__ float2 cfma_rot(float2 a, float t, float2 b) {
+  return INV ? cfma_pi(a, t, b) : cfma_mi(a, t, b);
 }
 
 // v * W_R^K with a compile-time twiddle, W_R = exp(-+ 2 pi i / R); trivial turns cost nothing
@@ -82,16 +135,13 @@ __device__ __forceinline__ float2 mul_w(float2 v) {
   } else if constexpr (4 * k == R) {
     return rot90<INV>(v);
   } else if constexpr (2 * k == R) {
-    return make_float2(-v.x, -v.y);
+    return pk_neg(v);
   } else if constexpr (4 * k == 3 * R) {
     return rot90<!INV>(v);
   } else {
     constexpr float c = float(ct_cos2pi(k, R));
     constexpr float s = float(ct_sin2pi(k, R));  // W = c - i s (forward), c + i s (inverse)
-    if constexpr (!INV)
-      return make_float2(fmaf(v.x, c, v.y * s), fmaf(v.y, c, -v.x * s));
-    else
-      return make_float2(fmaf(v.x, c, -v.y * s), fmaf(v.y, c, v.x * s));
+    return cfma_rot<INV>(cscale(v, c), s, v);
   }
 }
 
@@ -121,17 +171,11 @@ struct Dft<3, INV> {
     constexpr float s = float(ct_sin2pi(1, 3));
     float2 t = cadd(c[1], c[2]);
     float2 d = csub(c[1], c[2]);
-    float2 m = make_float2(fmaf(-0.5f, t.x, c[0].x), fmaf(-0.5f, t.y, c[0].y));
+    float2 m = pk_fma(t, pk_bc(-0.5f), c[0]);
     c[0] = cadd(c[0], t);
     // forward: X1 = m - i s d, X2 = m + i s d ; inverse swaps them
-    float2 e = make_float2(s * d.y, -s * d.x);  // -i s d
-    if constexpr (!INV) {
-      c[1] = cadd(m, e);
-      c[2] = csub(m, e);
-    } else {
-      c[1] = csub(m, e);
-      c[2] = cadd(m, e);
-    }
+    c[1] = cfma_rot<INV>(m, s, d);
+    c[2] = cfma_rot<!INV>(m, s, d);
   }
 };
 
@@ -140,11 +184,10 @@ struct Dft<4, INV> {
   static __device__ __forceinline__ void run(float2 (&c)[4]) {
     float2 t0 = cadd(c[0], c[2]), t1 = csub(c[0], c[2]);
     float2 t2 = cadd(c[1], c[3]), t3 = csub(c[1], c[3]);
-    float2 r = rot90<INV>(t3);  // forward: -i t3
     c[0] = cadd(t0, t2);
     c[2] = csub(t0, t2);
-    c[1] = cadd(t1, r);
-    c[3] = csub(t1, r);
+    c[1] = cadd_rot<INV>(t1, t3);  // forward: t1 - i t3
+    c[3] = csub_rot<INV>(t1, t3);
   }
 };
 
@@ -156,24 +199,16 @@ struct Dft<5, INV> {
     float2 t1 = cadd(c[1], c[4]), t2 = cadd(c[2], c[3]);
     float2 t3 = csub(c[1], c[4]), t4 = csub(c[2], c[3]);
     float2 a0 = c[0];
-    c[0] = make_float2(a0.x + t1.x + t2.x, a0.y + t1.y + t2.y);
-    float2 m1 = make_float2(fmaf(c1, t1.x, fmaf(c2, t2.x, a0.x)), fmaf(c1, t1.y, fmaf(c2, t2.y, a0.y)));
-    float2 m2 = make_float2(fmaf(c2, t1.x, fmaf(c1, t2.x, a0.x)), fmaf(c2, t1.y, fmaf(c1, t2.y, a0.y)));
-    float2 u1 = make_float2(fmaf(s1, t3.x, s2 * t4.x), fmaf(s1, t3.y, s2 * t4.y));
-    float2 u2 = make_float2(fmaf(s2, t3.x, -s1 * t4.x), fmaf(s2, t3.y, -s1 * t4.y));
-    // forward: X1 = m1 - i u1, X4 = m1 + i u1, X2 = m2 - i u2, X3 = m2 + i u2
-    float2 e1 = make_float2(u1.y, -u1.x), e2 = make_float2(u2.y, -u2.x);
-    if constexpr (!INV) {
-      c[1] = cadd(m1, e1);
-      c[4] = csub(m1, e1);
-      c[2] = cadd(m2, e2);
-      c[3] = csub(m2, e2);
-    } else {
-      c[1] = csub(m1, e1);
-      c[4] = cadd(m1, e1);
-      c[2] = csub(m2, e2);
-      c[3] = cadd(m2, e2);
-    }
+    c[0] = cadd(cadd(a0, t1), t2);
+    float2 m1 = pk_fma(t1, pk_bc(c1), pk_fma(t2, pk_bc(c2), a0));
+    float2 m2 = pk_fma(t1, pk_bc(c2), pk_fma(t2, pk_bc(c1), a0));
+    float2 u1 = pk_fma(t3, pk_bc(s1), cscale(t4, s2));
+    float2 u2 = pk_fma(t3, pk_bc(s2), cscale(t4, -s1));
+    // forward: X1 = m1 - i u1, X4 = m1 + i u1, X2 = m2 - i u2, X3 = m2 + i u2 ; inverse swaps the signs
+    c[1] = cadd_rot<INV>(m1, u1);
+    c[4] = csub_rot<INV>(m1, u1);
+    c[2] = cadd_rot<INV>(m2, u2);
+    c[3] = csub_rot<INV>(m2, u2);
   }
 };
 

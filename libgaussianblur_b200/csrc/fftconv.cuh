@@ -175,10 +175,7 @@ __device__ __forceinline__ void fused_last_stage(typename SmemElem<NSEQ>::type* 
     for (int j = 0; j < R; ++j) {
       const float g = TSM ? kp[j] : __ldg(kp + j);
 #pragma unroll
-      for (int q = 0; q < NSEQ; ++q) {
-        c[q][j].x *= g;
-        c[q][j].y *= g;
-      }
+      for (int q = 0; q < NSEQ; ++q) c[q][j] = cscale(c[q][j], g);
     }
 #pragma unroll
     for (int q = 0; q < NSEQ; ++q) dft<R, true>(c[q]);

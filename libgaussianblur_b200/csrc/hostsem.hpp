@@ -105,6 +105,18 @@ inline std::vector<double> kernel_gains(const std::vector<float>& taps, int N) {
   return g;
 }
 
+// one gain K[k] of the same sum (the Nyquist coefficient needs only K[0] and K[N/2])
+inline double kernel_gain_at(const std::vector<float>& taps, int N, int k) {
+  const int half = (int)taps.size() / 2;
+  const double step = 2.0 * 3.14159265358979323846264338327950288 / (double)N;
+  double acc = taps[(size_t)half];
+  for (int d = 1; d <= half; ++d) {
+    const long long kd = ((long long)k * d) % N;
+    acc += ((double)taps[(size_t)(half + d)] + (double)taps[(size_t)(half - d)]) * std::cos(step * (double)kd);
+  }
+  return acc;
+}
+
 // pffft "ordered" real-spectrum layout: [K0, K_{N/2}, Re1, Im1, Re2, Im2, ...], Im = 0
 inline std::vector<float> kerf_ordered(const std::vector<double>& gains, int N) {
   std::vector<float> o((size_t)N, 0.0f);

@@ -54,10 +54,11 @@ int find_static_shape(int N, int nseq, int* radices, int* nthreads) {
 
 cudaError_t kernels_init(int) { return cudaSuccess; }
 
-bool make_panel_tensor_map(CUtensorMap* out, const float* base, int np, long long panels, int L, int* box_rows) {
-  typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
-                               const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                               CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+namespace {
+typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                             const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                             CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeFn tensor_map_encoder() {
   static EncodeFn encode = [] {
     void* fn = nullptr;
     cudaDriverEntryPointQueryResult q;
@@ -66,6 +67,29 @@ bool make_panel_tensor_map(CUtensorMap* out, const float* base, int np, long lon
       fn = nullptr;
     return reinterpret_cast<EncodeFn>(fn);
   }();
+  return encode;
+}
+}  // namespace
+
+bool encode_tensor_map(CUtensorMap* out, int elem_bytes, int rank, const void* base, const unsigned long long* dims,
+                       const unsigned long long* strides_bytes, const unsigned* box, int swizzle_bytes) {
+  EncodeFn encode = tensor_map_encoder();
+  if (!encode || rank < 1 || rank > 3) return false;
+  cuuint64_t d[3], st[2];
+  cuuint32_t b[3], es[3] = {1, 1, 1};
+  for (int i = 0; i < rank; ++i) d[i] = dims[i], b[i] = box[i];
+  for (int i = 0; i + 1 < rank; ++i) st[i] = strides_bytes[i];
+  const CUtensorMapSwizzle sw = swizzle_bytes == 128  ? CU_TENSOR_MAP_SWIZZLE_128B
+                                : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                : swizzle_bytes == 32 ? CU_TENSOR_MAP_SWIZZLE_32B
+                                                      : CU_TENSOR_MAP_SWIZZLE_NONE;
+  const CUtensorMapDataType dt = elem_bytes == 1 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  return encode(out, dt, (cuuint32_t)rank, const_cast<void*>(base), d, st, b, es, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+bool make_panel_tensor_map(CUtensorMap* out, const float* base, int np, long long panels, int L, int* box_rows) {
+  EncodeFn encode = tensor_map_encoder();
   if (!encode || getenv("GBLUR_NO_TMA")) return false;
   int rows = 0;
   for (int r = 256; r >= 32; --r)

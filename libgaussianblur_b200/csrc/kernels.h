@@ -82,6 +82,12 @@ int find_static_shape(int N, int nseq, int* radices /*[4]*/, int* nthreads);
 // Returns false when the driver entry point is missing or np has no usable divisor (then cp.async is used).
 bool make_panel_tensor_map(CUtensorMap* out, const float* base, int np, long long panels, int L, int* box_rows);
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link dependency on libcuda). rank <= 3;
+// dims / box fastest dimension first, strides_bytes for dimensions 1 .. rank-1. swizzle_bytes: 0, 32, 64 or 128.
+// elem_bytes: 4 = FLOAT32, 1 = UINT8. Returns false when the entry point is missing or the encode fails.
+bool encode_tensor_map(CUtensorMap* out, int elem_bytes, int rank, const void* base, const unsigned long long* dims,
+                       const unsigned long long* strides_bytes, const unsigned* box, int swizzle_bytes);
+
 // One-time per-process kernel attribute setup (max dynamic smem). Returns cudaSuccess or error.
 cudaError_t kernels_init(int device);
 

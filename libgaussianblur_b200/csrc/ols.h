@@ -30,13 +30,15 @@ bool row_profitable(const RowLaunch& a, int n_ref);
 cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t stream);
 
 // ---- column pass (same plan object) ----
-// RGBA with all four channels processed, one frame, whole width, even pixel count, 8-byte aligned output rows
+// C == Cp == 4, one frame, panel intermediate without bank-padding holes, the float-column range on 16-column
+// boundaries, 16-byte aligned output rows
 bool col_eligible(const RowPlan* p, const ColLaunch& a);
 bool col_profitable(const ColLaunch& a, int n_ref_col);
-// Three launches: column sums of the u8 input (the synthetic row u), the row pass of u (one CTA), the block kernel.
-// d_in / in_pitch: the image the intermediate was computed from.
-cudaError_t launch_col(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long long in_pitch, int num_sms,
-                       cudaStream_t stream);
+// The column terms of the reference's Nyquist behaviour, once per image (two launches: column sums of the u8 input =
+// the synthetic row u, then the row pass of u on one CTA). d_in / in_pitch: the image the intermediate comes from.
+cudaError_t launch_col_terms(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long long in_pitch, cudaStream_t stream);
+// The block kernel over the float columns [a.w_begin, a.w_end) (TMA tile loads and stores, ols_core.cuh).
+cudaError_t launch_col(RowPlan* p, const ColLaunch& a, int num_sms, cudaStream_t stream);
 
 }  // namespace ols
 }  // namespace gblur

@@ -1,4 +1,4 @@
-// ols_core.cuh — overlap-save row pass: the lane-level code of the warp-per-block kernel.
+// ols_core.cuh — overlap-save passes: the lane-level code of the warp-per-block kernels (ols_kernels.cu).
 //
 // Same result as the whole-line transform of the reference
 //   process_channel_tiles              /root/reference/src/gaussianblur.cpp:202-244
@@ -40,6 +40,8 @@ constexpr int kNB = 1024;        // block transform length
 constexpr int kR = 32;           // radix of both stages = lanes per warp = points per lane
 constexpr int kRowStride = 34;   // float2 slots per exchange row: 272 bytes keeps STS.64 columns and LDS.128 rows conflict-free
 constexpr int kExch = kR * kRowStride;  // exchange slots (float2) per warp
+constexpr int kTwStride = 34;    // float2 per lane row of the twiddle table (LDS.128 rows, conflict-free like the exchange)
+constexpr int kTwSlots = kR * kTwStride;
 constexpr int kGainStride = 36;  // floats per row of the gain table (LDS.128 by a quarter warp hits 8 distinct bank groups)
 constexpr int kMaxPad = 256;     // at least half of every block is output
 
@@ -57,7 +59,7 @@ struct RowParams {
   int blk_np, blk_padq;
   long long blk_frame_stride;
   const float4* qa;        // per image row: (K[0] - K[N/2]) / N * alternating sum, one float per channel
-  const float2* tw;        // tw[a * 32 + b] = exp(-2 pi i a b / 1024)
+  const float2* tw;        // tw[lane * kTwStride + k] = exp(-2 pi i lane k / 1024)
   const float* gains;      // gains[k1 * kGainStride + k2] = K_1024[k1 + 32 k2] / 1024
 };
 
@@ -127,20 +129,6 @@ __device__ __forceinline__ void altsum_lane(const uint32_t* __restrict__ row, in
   for (int x = x_scalar + lane; x < T; x += 32) altsum_acc(GBLUR_OLS_LDG(row + x), x, pad, T, a);
 }
 
-// The same sums split over `nthreads` cooperating threads (row-per-CTA kernel): thread `tid` takes the groups of four
-// pixels tid, tid + nthreads, ...
-__device__ __forceinline__ void altsum_part(const uint32_t* __restrict__ row, int T, int pad, int tid, int nthreads,
-                                            int (&a)[4]) {
-  int x_scalar = 0;
-  if ((reinterpret_cast<uintptr_t>(row) & 15) == 0) {
-    const uint4* row4 = reinterpret_cast<const uint4*>(row);
-    const int n4 = T >> 2;
-    for (int g = tid; g < n4; g += nthreads) altsum_group(GBLUR_OLS_LDG(row4 + g), 4 * g, pad, T, a);
-    x_scalar = 4 * n4;
-  }
-  for (int x = x_scalar + tid; x < T; x += nthreads) altsum_acc(GBLUR_OLS_LDG(row + x), x, pad, T, a);
-}
-
 // bytes (2 * pair, 2 * pair + 1) of an RGBA word as a complex sample
 __device__ __forceinline__ float2 u8_pair(uint32_t w, int pair) {
 #if defined(__CUDA_ARCH__)
@@ -148,7 +136,7 @@ __device__ __forceinline__ float2 u8_pair(uint32_t w, int pair) {
   const uint32_t sel = 0x7540u + 2u * (uint32_t)pair;
   const uint32_t lo = __byte_perm(w, 0x4B000000u, sel);
   const uint32_t hi = __byte_perm(w, 0x4B000000u, sel + 1u);
-  return make_float2(__uint_as_float(lo) - 8388608.0f, __uint_as_float(hi) - 8388608.0f);
+  return pk_add(make_float2(__uint_as_float(lo), __uint_as_float(hi)), pk_bc(-8388608.0f));
 #else
   return make_float2((float)((w >> (16 * pair)) & 255u), (float)((w >> (16 * pair + 8)) & 255u));
 #endif
@@ -173,15 +161,17 @@ __device__ __forceinline__ RowDst make_row_dst(const RowParams& P, long long r_g
   return d;
 }
 
-// One item = one 1024-sample block of one channel pair. Per lane, 32 complex values stay in registers:
-//   load_block : c[i] = b[s + lane + 32 i]                                           (lane = l, register = i)
+// One item = one 1024-sample block of one complex sequence (two real lines). Per lane, 32 complex values stay in
+// registers:
+//   load       : c[i] = a[lane + 32 i]                                                (lane = l, register = i)
 //   then four passes q = 0..3 of ONE rolled loop, each starting with the same 32-point DFT over the register index:
 //     q = 0: twiddle w^(lane k), column `lane` of the exchange, __syncwarp, row `lane` back   (lane = k1, register = l)
-//     q = 1: X[lane + 32 k2] is complete: gains, complex conjugate
-//     q = 2: as q = 0 — the inverse transform is conj(DFT(conj(.))) and conj(a conj(w)) = conj(a) w, so the inverse
-//            half is THE SAME CODE on conjugated data                                         (lane = l, register = k1)
-//     q = 3: nothing more: c[i] = conj(1024 y_lin[s + lane + 32 i])
-//   store_block: conjugate back, add the Nyquist term, crop, panel stores
+//     q = 1: A[lane + 32 k2] is complete: gains
+//     q = 2: as q = 0. Passes 0-1 are a complete forward DFT with natural order in (index = lane + 32 register) and
+//            out; running THE SAME CODE on the product B = A G gives C[m] = sum_k B[k] w^(km) = 1024 y[-m mod 1024],
+//            the inverse transform with its index negated — no conjugation and no re/im exchange anywhere.
+//     q = 3: nothing more: lane l, register j hold 1024 y[n], n = (32 - l) + 32 (31 - j)  (mod 1024)
+//   store      : registers in descending order, lanes in descending order of n; add the Nyquist term, crop.
 // The loop is kept rolled on purpose: the warps of an SM run out of phase here, so the instructions of an item must
 // fit the SM's 32 KB instruction cache. The fully unrolled first version (four DFT copies, 44 KB) ran no faster than
 // the whole-line kernel and slowed down with more independent CTAs (profiles/r01/ols_rowpass_v1_check.jsonl).
@@ -204,12 +194,16 @@ __device__ __forceinline__ void load_block(float2 (&c)[kR], const RowParams& P, 
   }
 }
 
-// twiddle w^(lane * k) on register k, then column `lane` of the exchange
+// twiddle w^(lane * k) on register k, then column `lane` of the exchange; twl = this lane's row of the table
 __device__ __forceinline__ void tw_write_col(const float2 (&c)[kR], int lane, float2* __restrict__ ex,
-                                             const float2* __restrict__ tw) {
-  ex[lane] = c[0];
+                                             const float2* __restrict__ twl) {
+  const float4* t4 = reinterpret_cast<const float4*>(twl);
 #pragma unroll
-  for (int k = 1; k < kR; ++k) ex[k * kRowStride + lane] = cmul(c[k], tw[k * kR + lane]);
+  for (int m = 0; m < kR / 2; ++m) {
+    const float4 t = t4[m];  // twiddles of registers 2m, 2m + 1
+    ex[(2 * m) * kRowStride + lane] = m == 0 ? c[0] : cmul(c[2 * m], make_float2(t.x, t.y));
+    ex[(2 * m + 1) * kRowStride + lane] = cmul(c[2 * m + 1], make_float2(t.z, t.w));
+  }
 }
 
 // row `lane` of the exchange
@@ -223,43 +217,66 @@ __device__ __forceinline__ void read_row(float2 (&c)[kR], int lane, const float2
   }
 }
 
-// c[k2] = conj(X[lane + 32 k2] * gain)
+// c[k2] = A[lane + 32 k2] * gain
 __device__ __forceinline__ void mid_gains(float2 (&c)[kR], int lane, const float* __restrict__ gains) {
   const float4* g = reinterpret_cast<const float4*>(gains + lane * kGainStride);
 #pragma unroll
   for (int m = 0; m < kR / 4; ++m) {
     const float4 t = g[m];
-    c[4 * m].x *= t.x, c[4 * m].y *= -t.x;
-    c[4 * m + 1].x *= t.y, c[4 * m + 1].y *= -t.y;
-    c[4 * m + 2].x *= t.z, c[4 * m + 2].y *= -t.z;
-    c[4 * m + 3].x *= t.w, c[4 * m + 3].y *= -t.w;
+    c[4 * m] = cscale(c[4 * m], t.x);
+    c[4 * m + 1] = cscale(c[4 * m + 1], t.y);
+    c[4 * m + 2] = cscale(c[4 * m + 2], t.z);
+    c[4 * m + 3] = cscale(c[4 * m + 3], t.w);
   }
 }
 
-// c[i] = conj(1024 * y_lin[s + lane + 32 i]) (the 1/1024 sits in the gains)
+// The four passes. In: c[i] = a[lane + 32 i]. Out: c[j] = 1024 y[(32 - lane) + 32 (31 - j) mod 1024] (the 1/1024 sits in
+// the gains), y = the circular convolution of the block with the centred taps.
+__device__ __forceinline__ void block_passes(float2 (&c)[kR], int lane, float2* __restrict__ ex,
+                                             const float2* __restrict__ twl, const float* __restrict__ gains) {
+#pragma unroll 1
+  for (int q = 0; q < 4; ++q) {
+    dft<kR, false>(c);
+    if ((q & 1) == 0) {
+      tw_write_col(c, lane, ex, twl);
+#if defined(__CUDA_ARCH__)
+      __syncwarp();
+#endif
+      read_row(c, lane, ex);
+#if defined(__CUDA_ARCH__)
+      __syncwarp();  // every row has been read before the next pass overwrites columns
+#endif
+    } else if (q == 1) {
+      mid_gains(c, lane, gains);
+    }
+  }
+}
+
+// block index of (lane, descending register position i): n = (32 - lane) + 32 i, value in c[31 - i]
 __device__ __forceinline__ void store_block(const float2 (&c)[kR], const RowParams& P, const RowDst& d, float2 qa, int s,
                                             int pair, int lane) {
-  // (-1)^n for n = s + lane + 32 i does not depend on i
-  const float sg = ((s + lane) & 1) ? -1.0f : 1.0f;
+  const int l1 = kR - lane;  // 1 .. 32
+  // (-1)^n for n = s + l1 + 32 i does not depend on i
+  const float sg = ((s + l1) & 1) ? -1.0f : 1.0f;
   const float2 add = make_float2(qa.x * sg, qa.y * sg);
-  // register i holds block index lane + 32 i; outputs are the indices [pad, min(pad + L, T - s + pad))
-  const int lo = P.pad - lane;
-  const int hi = min(P.pad + P.L, P.T - s + P.pad) - lane;
+  // outputs are the block indices [pad, min(pad + L, T - s + pad)); index 1024 (lane 0, i = 31) is index 0
+  const int lo = P.pad - l1;
+  const int hi = min(P.pad + P.L, P.T - s + P.pad) - l1;
   // pixel x = x0 + 32 i lands in panel (x >> 3) = (x0 >> 3) + 4 i at float offset (x0 & 7) * 4 (+ 2 for pair 1)
-  const int x0 = s + lane - P.pad;
+  const int x0 = s + l1 - P.pad;
   float* dp = d.base + 2 * pair + (long long)(x0 >> 3) * d.gstride + ((x0 & 7) << 2);
   const long long step = 4 * d.gstride;
   if ((d.dl | d.dr) == 0) {
 #pragma unroll
     for (int i = 0; i < kR; ++i) {
-      if (kR * i >= lo && kR * i < hi) *reinterpret_cast<float2*>(dp) = make_float2(c[i].x + add.x, add.y - c[i].y);
+      if (kR * i >= lo && kR * i < hi) *reinterpret_cast<float2*>(dp) = pk_add(c[kR - 1 - i], add);
       dp += step;
     }
   } else {  // rows inside the reflect_101 border also fill the column pass's mirrored slots
 #pragma unroll
     for (int i = 0; i < kR; ++i) {
       if (kR * i >= lo && kR * i < hi) {
-        const float2 v = make_float2(c[i].x + add.x, add.y - c[i].y);
+        const float2 v = pk_add(c[kR - 1 - i], add);
         *reinterpret_cast<float2*>(dp) = v;
         if (d.dl) *reinterpret_cast<float2*>(dp + d.dl) = v;
         if (d.dr) *reinterpret_cast<float2*>(dp + d.dr) = v;
@@ -267,115 +284,93 @@ __device__ __forceinline__ void store_block(const float2 (&c)[kR], const RowPara
       dp += step;
     }
   }
+  // pad == 0 (a one-tap window): block index 0 is an output and sits at "index 1024" of lane 0
+  if (P.pad == 0 && lane == 0 && s < P.T) {
+    float* d0 = d.base + 2 * pair + (long long)(s >> 3) * d.gstride + ((s & 7) << 2);
+    const float sg0 = (s & 1) ? -1.0f : 1.0f;
+    *reinterpret_cast<float2*>(d0) = make_float2(c[0].x + qa.x * sg0, c[0].y + qa.y * sg0);
+  }
 }
 
 // ------------------------------------------------------------------------------------------------------------
 // Column pass: fp32 panel intermediate -> u8 image (replaces the second process_channel_tiles call and
 // interleave_channels, /root/reference/src/gaussianblur.cpp:261-305, helpers.hpp:248-274).
-// One CTA of CW = 4 (or 8) warps takes a QUARTER (HALF) PANEL — 8 (16) float columns = 2 (4) RGBA pixels = one (two)
-// 32-byte sectors per slot — and one 1024-slot block of the padded column; warp w transforms column pair w (floats
-// 2w, 2w+1 of the unit) with the same four-pass loop as the row pass. The slots are fetched cooperatively with 16-byte loads straight into the four
-// exchange buffers (column layout, so every lane later reads exactly what it will overwrite), the u8 results are
-// collected in a shared tile and leave as one 8-byte store per image row.
+// One CTA of kColWarps = 8 warps takes a HALF PANEL — 16 float columns = 64 bytes per slot — and one 1024-slot
+// block of the padded column; warp w transforms the column pair (floats 2w, 2w+1 of the unit) with the same four
+// passes as the row pass.
+//   * in : four TMA tile loads {16 floats, 256 slots} with the 64-byte swizzle land the block in the CTA's exchange
+//          region (no LSU instruction, no register staging); a lane reads its 32 samples back with LDS.64 (the swizzle
+//          leaves a 2-way bank conflict, 4 wavefronts per load instead of 2).
+//   * out: the u8 results (F2IP.U8.F32.TRUNC: truncate, saturate and pack two channels in one instruction, the + 0.5
+//          rides on the Nyquist add) are collected in a [row][16 bytes] tile and leave through TMA tile stores —
+//          16 bytes per image row and CTA, no LSU instruction on the global side.
 // The reference's Nyquist term along a column needs sum_n (-1)^n I[n][w] over the padded column of the row-pass
 // result I. By linearity that is the row pass applied to ONE synthetic row u = sum_r weight(r) x[r] (exact integers
 // on u8 input, colsum_lane below), so it costs one more line instead of a pass over the 531 MB intermediate.
 // ------------------------------------------------------------------------------------------------------------
+constexpr int kColWarps = 8;
+constexpr int kColFloats = 2 * kColWarps;          // float columns per unit = bytes per output row of a unit
+constexpr int kColBoxSlots = 256;                  // slots per TMA load box
+constexpr int kColRegion = kColWarps * kExch * 8;  // bytes: exchange slices of the 8 warps; the landing area (64 KB) aliases it
+constexpr int kColTileBytes = kNB * kColFloats;    // u8 tile [1024 rows][16 bytes]
+
 struct ColParams {
-  const float* inter;       // panel intermediate [panel][slot][32 floats]
-  long long panel_stride;   // floats per panel = np * 32
-  int padq;                 // slot holes of the whole-line column kernel's layout (0 = none)
   int T, pad;               // image rows, reflect pad
   int L, nblk;              // outputs per block, blocks per column
-  int nunits;               // units (CW column pairs = CW / 2 pixels) with at least one valid pixel
-  long long nitems;         // nunits * nblk
-  int cols;
-  uint8_t* out;             // HWC u8, 4 channels
-  long long out_pitch;      // bytes per image row
-  const float2* qc;         // per column pair (2x + pair): (K[0] - K[N/2]) / N of the column length * row pass of u
+  int unit0, nunits;        // first unit and unit count of this launch (a unit = 16 float columns)
+  int frames;
+  long long nitems;         // frames * nunits * nblk
+  int panels_per_frame;
+  int st_na, st_rows_a, st_rows_b;  // store boxes: st_na boxes of st_rows_a rows, then one of st_rows_b rows (0 = none)
+  long long qc_frame_stride;        // float2 per frame of qc
+  const float2* qc;         // per column pair: (K[0] - K[N/2]) / N of the column length * row pass of u
   const float2* tw;
   const float* gains;
 };
 
-// CW = warps per CTA = column pairs per unit: 4 (quarter panel, 32 bytes per slot, 8-byte stores) or 8 (half panel,
-// 64 bytes per slot, 16-byte stores: half as many L1 line-operations per byte on both sides)
-// cooperative fetch of one item: CW/2 threads share a slot (16 bytes each); 64 slots per pass, 16 passes
-template <int CW>
-__device__ __forceinline__ void col_fetch(const ColParams& P, int unit, int s, int t, float2* __restrict__ ex_all) {
-  constexpr int TPS = CW / 2;         // threads per slot
-  constexpr int UPP = 16 / CW;        // units per panel
-  const int part = t % TPS, sl = t / TPS;
-  const float* src = P.inter + (long long)(unit / UPP) * P.panel_stride + (unit % UPP) * (2 * CW) + part * 4;
-  float2* e0 = ex_all + (2 * part) * kExch;  // exchange buffers of warps 2 * part and 2 * part + 1
-  float2* e1 = e0 + kExch;
-  const int nvalid = P.T + 2 * P.pad;
-  float4 v[16];
-#pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const int n = s + k * 64 + sl;
-    v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (n < nvalid) v[k] = GBLUR_OLS_LDG(reinterpret_cast<const float4*>(src + (long long)phys_slot(n, P.padq) * 32));
-  }
-#pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    const int nl = k * 64 + sl;
-    const int slot = (nl >> 5) * kRowStride + (nl & 31);
-    e0[slot] = make_float2(v[k].x, v[k].y);
-    e1[slot] = make_float2(v[k].z, v[k].w);
-  }
+// byte offset inside the landing area of (slot n of the block, column pair w) under the 64-byte TMA swizzle:
+// 16-byte chunk index (w >> 1) is XORed with bits 7-8 of the offset = (n >> 1) & 3
+__device__ __forceinline__ int col_landing_offset(int n, int w) {
+  return (n >> 8) * (kColBoxSlots * 64) + (n & 255) * 64 + ((((w >> 1) ^ (n >> 1)) & 3) << 4) + ((w & 1) << 3);
 }
 
-// column `lane` of the exchange: c[i] = sample s + lane + 32 i
-__device__ __forceinline__ void read_col(float2 (&c)[kR], int lane, const float2* __restrict__ ex) {
+// c[i] = sample lane + 32 i of column pair w
+__device__ __forceinline__ void read_col(float2 (&c)[kR], int lane, int w, const unsigned char* __restrict__ landing) {
+  const unsigned char* p = landing + col_landing_offset(lane, w);
 #pragma unroll
-  for (int i = 0; i < kR; ++i) c[i] = ex[i * kRowStride + lane];
+  for (int i = 0; i < kR; ++i) c[i] = *reinterpret_cast<const float2*>(p + i * (kR * 64));  // 32 slots further: + 2048 bytes
 }
 
-// uint8_t(v + 0.5f): fp32 add, truncate (helpers.hpp:251-252,270); clamped to [0, 255]
-__device__ __forceinline__ uint32_t to_u8(float v) {
-  const float f = fminf(fmaxf(v + 0.5f, 0.0f), 255.0f);
+// two channels -> two bytes, each uint8_t(v) (truncation: helpers.hpp:251-252,270; the caller has added 0.5), saturated
+__device__ __forceinline__ uint32_t to_u8x2(float2 v) {
 #if defined(__CUDA_ARCH__)
-  return __float2uint_rz(f);
+  const int a = __float2int_rz(v.x), b = __float2int_rz(v.y);
+  uint32_t r;
+  asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(r) : "r"(b), "r"(a), "r"(0));  // fuses to F2IP.U8.F32.TRUNC
+  return r;
 #else
-  return (uint32_t)f;
+  const float x = std::min(std::max(v.x, 0.0f), 255.0f), y = std::min(std::max(v.y, 0.0f), 255.0f);
+  return (uint32_t)x | ((uint32_t)y << 8);
 #endif
 }
 
-// c[i] = conj(1024 y_lin[s + lane + 32 i]) -> two bytes per block index into the shared tile [1024][CW pairs]
-template <int CW>
-__device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, int s, int w, int lane,
-                                            uint16_t* __restrict__ tile) {
-  const float sg = ((s + lane) & 1) ? -1.0f : 1.0f;
-  const float2 add = make_float2(qc.x * sg, qc.y * sg);
+// lane l, register j hold 1024 y[n], n = (32 - l) + 32 (31 - j): two bytes per output row into tile[n - pad][2w, 2w+1]
+__device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, int s, int pad, int L, int w, int lane,
+                                            unsigned char* __restrict__ tile) {
+  const int l1 = kR - lane;
+  const float sg = ((s + l1) & 1) ? -1.0f : 1.0f;
+  const float2 add = make_float2(fmaf(qc.x, sg, 0.5f), fmaf(qc.y, sg, 0.5f));
+  const int lo = pad - l1, hi = pad + L - l1;
+  unsigned char* tp = tile + (l1 - pad) * kColFloats + 2 * w;
 #pragma unroll
   for (int i = 0; i < kR; ++i) {
-    const uint32_t b0 = to_u8(c[i].x + add.x), b1 = to_u8(add.y - c[i].y);
-    tile[(lane + kR * i) * CW + w] = (uint16_t)(b0 | (b1 << 8));
+    if (kR * i >= lo && kR * i < hi)
+      *reinterpret_cast<uint16_t*>(tp + i * (kR * kColFloats)) = (uint16_t)to_u8x2(pk_add(c[kR - 1 - i], add));
   }
-}
-
-// thread t of 32 CW stores block indices t + 32 CW k: 2 CW bytes (CW / 2 RGBA pixels) per image row
-template <int CW>
-__device__ __forceinline__ void col_store(const ColParams& P, int unit, int s, int t, const uint16_t* __restrict__ tile) {
-  constexpr int PX = CW / 2;  // pixels per unit
-  const int hi = min(P.pad + P.L, P.T - s + P.pad);
-  const int npx = min(PX, P.cols - unit * PX);  // valid pixels of this unit (the last one may be cut)
-  uint8_t* base = P.out + (long long)unit * (4 * PX);
-#pragma unroll
-  for (int k = 0; k < 1024 / (32 * CW); ++k) {
-    const int idx = t + 32 * CW * k;
-    if (idx >= P.pad && idx < hi) {
-      const uint32_t* src = reinterpret_cast<const uint32_t*>(tile + idx * CW);
-      uint8_t* dp = base + (long long)(s + idx - P.pad) * P.out_pitch;
-      if (npx == PX) {
-        if constexpr (CW == 4)
-          *reinterpret_cast<uint2*>(dp) = *reinterpret_cast<const uint2*>(src);
-        else
-          *reinterpret_cast<uint4*>(dp) = *reinterpret_cast<const uint4*>(src);
-      } else {
-        for (int p = 0; p < npx; ++p) reinterpret_cast<uint32_t*>(dp)[p] = src[p];
-      }
-    }
+  if (pad == 0 && lane == 0) {
+    const float sg0 = (s & 1) ? -1.0f : 1.0f;
+    *reinterpret_cast<uint16_t*>(tile + 2 * w) =
+        (uint16_t)to_u8x2(make_float2(c[0].x + fmaf(qc.x, sg0, 0.5f), c[0].y + fmaf(qc.y, sg0, 0.5f)));
   }
 }
 
@@ -407,19 +402,24 @@ __device__ __forceinline__ void load_block_u(float2 (&c)[kR], const int* __restr
   }
 }
 
-// c[i] = conj(1024 * linear convolution of u at s + lane + 32 i): add u's own Nyquist term, scale by the column
-// coefficient and store per column pair (2x + pair)
+// lane l, register j hold 1024 * (linear convolution of u) at block index (32 - l) + 32 (31 - j): add u's own Nyquist
+// term, scale by the column coefficient and store per column pair (2x + pair)
 __device__ __forceinline__ void store_block_u(const float2 (&c)[kR], float2 qa_u, float q_col, int T, int pad, int L, int s,
                                               int pair, int lane, float2* __restrict__ qc) {
-  const float sg = ((s + lane) & 1) ? -1.0f : 1.0f;
+  const int l1 = kR - lane;
+  const float sg = ((s + l1) & 1) ? -1.0f : 1.0f;
   const int hi = min(pad + L, T - s + pad);
 #pragma unroll
   for (int i = 0; i < kR; ++i) {
-    const int idx = lane + kR * i;
+    const int idx = l1 + kR * i;
     if (idx >= pad && idx < hi) {
       const int x = s + idx - pad;
-      qc[2 * x + pair] = make_float2(q_col * (c[i].x + qa_u.x * sg), q_col * (qa_u.y * sg - c[i].y));
+      qc[2 * x + pair] = make_float2(q_col * (c[kR - 1 - i].x + qa_u.x * sg), q_col * (c[kR - 1 - i].y + qa_u.y * sg));
     }
+  }
+  if (pad == 0 && lane == 0 && s < T) {
+    const float sg0 = (s & 1) ? -1.0f : 1.0f;
+    qc[2 * s + pair] = make_float2(q_col * (c[0].x + qa_u.x * sg0), q_col * (c[0].y + qa_u.y * sg0));
   }
 }
 

@@ -12,7 +12,7 @@ namespace gblur {
 namespace ols {
 
 struct HostTables {
-  std::vector<float> tw;     // 1024 complex values, tw[a*32+b] = exp(-2 pi i a b / 1024)
+  std::vector<float> tw;     // 32 rows of 34 complex values, tw[lane*34 + k] = exp(-2 pi i lane k / 1024), k < 32
   std::vector<float> gains;  // 32 rows of 36 floats, gains[k1*36 + k2] = K_1024[k1 + 32 k2] / 1024
   float q = 0.f;             // (K_N[0] - K_N[N/2]) / N for the reference's transform length along a row
   float q_col = 0.f;         // the same for its transform length along a column
@@ -20,15 +20,15 @@ struct HostTables {
 
 // taps.size() must not exceed 1024 - 512 + 1 (pad <= 256)
 inline HostTables build_tables(const std::vector<float>& taps, int n_ref, int n_ref_col = 0) {
-  constexpr int NB = 1024, R = 32, GS = 36;
+  constexpr int NB = 1024, R = 32, GS = 36, TS = 34;
   constexpr double two_pi = 6.28318530717958647692528676655900577;
   HostTables t;
-  t.tw.resize(2 * NB);
+  t.tw.assign((size_t)2 * R * TS, 0.0f);
   for (int a = 0; a < R; ++a)
     for (int b = 0; b < R; ++b) {
       const double ang = two_pi * (double)((a * b) % NB) / (double)NB;
-      t.tw[2 * (a * R + b)] = (float)std::cos(ang);
-      t.tw[2 * (a * R + b) + 1] = (float)(-std::sin(ang));
+      t.tw[2 * (a * TS + b)] = (float)std::cos(ang);
+      t.tw[2 * (a * TS + b) + 1] = (float)(-std::sin(ang));
     }
   const std::vector<double> kb = host::kernel_gains(taps, NB);
   t.gains.assign((size_t)R * GS, 0.0f);
@@ -38,12 +38,10 @@ inline HostTables build_tables(const std::vector<float>& taps, int n_ref, int n_
       const int kk = k <= NB / 2 ? k : NB - k;
       t.gains[(size_t)k1 * GS + k2] = (float)(kb[(size_t)kk] / (double)NB);
     }
-  const std::vector<double> kn = host::kernel_gains(taps, n_ref);
-  t.q = (float)((kn[0] - kn[(size_t)n_ref / 2]) / (double)n_ref);
-  if (n_ref_col > 0) {
-    const std::vector<double> kc = host::kernel_gains(taps, n_ref_col);
-    t.q_col = (float)((kc[0] - kc[(size_t)n_ref_col / 2]) / (double)n_ref_col);
-  }
+  t.q = (float)((host::kernel_gain_at(taps, n_ref, 0) - host::kernel_gain_at(taps, n_ref, n_ref / 2)) / (double)n_ref);
+  if (n_ref_col > 0)
+    t.q_col = (float)((host::kernel_gain_at(taps, n_ref_col, 0) - host::kernel_gain_at(taps, n_ref_col, n_ref_col / 2)) /
+                      (double)n_ref_col);
   return t;
 }
 

@@ -1,13 +1,16 @@
-// ols_kernels.cu — overlap-save row pass for sm_100a: one warp per (row, 1024-sample block, channel pair).
+// ols_kernels.cu — overlap-save passes for sm_100a: one warp per 1024-sample block of one complex sequence.
 // See ols_core.cuh for the algorithm and its relation to the reference (src/gaussianblur.cpp:62-79,202-244).
 //
 // Why: the whole-line kernels (line_kernels.cuh) are issue/latency bound with 13 warps per SM and a CTA
 // barrier per stage (profiles/r01/ncu_full_8k_v3_summary.txt: 2.2 of 4 warp instructions per clock, 17 % of
 // the stall samples on the barrier). Here a transform never leaves its warp: 32 points per lane, two
 // radix-32 stages, one shared-memory transpose per direction ordered by __syncwarp only, 8.7 KB of shared
-// memory per warp, so 16+ independent warps per SM with no CTA-wide synchronisation in the loop.
+// memory per warp. The row pass has no CTA-wide synchronisation in its loop at all; the column pass
+// synchronises its 8 warps three times per item around the TMA transfers they share.
 #include <cstdlib>
+#include <mutex>
 
+#include "async_copy.cuh"
 #include "ols.h"
 #include "ols_core.cuh"
 #include "ols_host.hpp"
@@ -25,13 +28,25 @@ struct RowPlan {
   int ksize = 0;
   float4* d_qa = nullptr;
   long long qa_rows = 0;
-  bool qa_valid = false;
   // column pass
   float q_col = 0.f;
   int* d_u = nullptr;       // synthetic row u: 4 * cols integer sums
   float2* d_qc = nullptr;   // 2 * cols column-pair terms
   int u_cols = 0;
+  // tensor maps of the column pass, rebuilt when the buffers or the geometry change
+  CUtensorMap in_map, out_a, out_b;
+  const void* map_inter = nullptr;
+  const void* map_out = nullptr;
+  long long map_key[6] = {0, 0, 0, 0, 0, 0};
 };
+
+constexpr size_t kTableBytes = (size_t)kTwSlots * 8 + (size_t)kR * kGainStride * 4;
+
+__device__ __forceinline__ void load_tables(float2* tw, float* gains, const float2* g_tw, const float* g_gains, int tid,
+                                            int nthreads) {
+  for (int i = tid; i < kTwSlots; i += nthreads) tw[i] = __ldg(g_tw + i);
+  for (int i = tid; i < kR * kGainStride; i += nthreads) gains[i] = __ldg(g_gains + i);
+}
 
 // (K[0] - K[N/2]) / N * sum over the reflect_101-padded row of (-1)^n b[n], per channel; exact integer sums.
 // One warp per row, 16-byte loads (four in flight per lane) when the row allows them.
@@ -58,12 +73,12 @@ template <int WARPS, int MAXREG>
 __global__ void __maxnreg__(MAXREG) ols_row_rgba_kernel(const __grid_constant__ RowParams P) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float2* tw = reinterpret_cast<float2*>(smem_raw);
-  float* gains = reinterpret_cast<float*>(tw + kNB);
+  float* gains = reinterpret_cast<float*>(tw + kTwSlots);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float2* ex = reinterpret_cast<float2*>(gains + kR * kGainStride) + warp * kExch;
-  for (int i = threadIdx.x; i < kNB; i += WARPS * 32) tw[i] = __ldg(P.tw + i);
-  for (int i = threadIdx.x; i < kR * kGainStride; i += WARPS * 32) gains[i] = __ldg(P.gains + i);
+  load_tables(tw, gains, P.tw, P.gains, threadIdx.x, WARPS * 32);
   __syncthreads();
+  const float2* twl = tw + lane * kTwStride;
   const long long stride = (long long)gridDim.x * WARPS;
   for (long long it = (long long)blockIdx.x * WARPS + warp; it < P.nitems; it += stride) {
     const int pair = (int)(it & 1);
@@ -77,79 +92,10 @@ __global__ void __maxnreg__(MAXREG) ols_row_rgba_kernel(const __grid_constant__ 
       load_block<true>(c, P, row, s, pair, lane);
     else
       load_block<false>(c, P, row, s, pair, lane);
-#pragma unroll 1
-    for (int q = 0; q < 4; ++q) {
-      dft<kR, false>(c);
-      if ((q & 1) == 0) {
-        tw_write_col(c, lane, ex, tw);
-        __syncwarp();
-        read_row(c, lane, ex);
-        __syncwarp();  // every row has been read before the next pass overwrites columns
-      } else if (q == 1) {
-        mid_gains(c, lane, gains);
-      }
-    }
+    block_passes(c, lane, ex, twl, gains);
     const RowDst d = make_row_dst(P, r);
     const float4 q4 = __ldg(P.qa + r);
     store_block(c, P, d, pair ? make_float2(q4.z, q4.w) : make_float2(q4.x, q4.y), s, pair, lane);
-  }
-}
-
-// Variant 5 (GBLUR_OLS_VARIANT=5, not measured yet): one CTA per row with one warp per item of the row (2 * nblk <= 20
-// warps), no pre-kernel. The warps first add up the row's alternating sums together (each reads 1 / nwarps of the row,
-// which the block loads touch again right afterwards), one CTA barrier per row, then run their blocks as above.
-__global__ void __maxnreg__(96) ols_row_cta_kernel(const __grid_constant__ RowParams P, float q_row) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  float2* tw = reinterpret_cast<float2*>(smem_raw);
-  float* gains = reinterpret_cast<float*>(tw + kNB);
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarps = blockDim.x >> 5;
-  float2* ex = reinterpret_cast<float2*>(gains + kR * kGainStride) + warp * kExch;
-  __shared__ int part[2][20][4];
-  for (int i = threadIdx.x; i < kNB; i += blockDim.x) tw[i] = __ldg(P.tw + i);
-  for (int i = threadIdx.x; i < kR * kGainStride; i += blockDim.x) gains[i] = __ldg(P.gains + i);
-  const long long nrows = P.nitems / (2 * P.nblk);
-  const int pair = warp & 1, s = (warp >> 1) * P.L;
-  int par = 0;
-  for (long long r = blockIdx.x; r < nrows; r += gridDim.x, par ^= 1) {
-    const uint32_t* row = reinterpret_cast<const uint32_t*>(P.in + r * P.in_pitch);
-    int a[4] = {0, 0, 0, 0};
-    altsum_part(row, P.T, P.pad, (int)threadIdx.x, (int)blockDim.x, a);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-#pragma unroll
-      for (int c = 0; c < 4; ++c) a[c] += __shfl_xor_sync(0xffffffffu, a[c], o);
-    }
-    if (lane == 0) {
-#pragma unroll
-      for (int c = 0; c < 4; ++c) part[par][warp][c] = a[c];
-    }
-    float2 c[kR];
-    if (s - P.pad >= 0 && s - P.pad + kNB <= P.T)
-      load_block<true>(c, P, row, s, pair, lane);
-    else
-      load_block<false>(c, P, row, s, pair, lane);
-    // the barrier also publishes the tables on the first row; part[par] is rewritten two rows later, after the
-    // barrier of the next row, which every warp reaches only when it is done with this row's sums
-    __syncthreads();
-    int s0 = 0, s1 = 0;
-    for (int w = 0; w < nwarps; ++w) {
-      s0 += part[par][w][2 * pair];
-      s1 += part[par][w][2 * pair + 1];
-    }
-#pragma unroll 1
-    for (int q = 0; q < 4; ++q) {
-      dft<kR, false>(c);
-      if ((q & 1) == 0) {
-        tw_write_col(c, lane, ex, tw);
-        __syncwarp();
-        read_row(c, lane, ex);
-        __syncwarp();
-      } else if (q == 1) {
-        mid_gains(c, lane, gains);
-      }
-    }
-    const RowDst d = make_row_dst(P, r);
-    store_block(c, P, d, make_float2(q_row * (float)s0, q_row * (float)s1), s, pair, lane);
   }
 }
 
@@ -178,13 +124,12 @@ __global__ void __launch_bounds__(kUWarps * 32, 1)
                      const float* __restrict__ g_gains, float2* __restrict__ qc) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float2* tw = reinterpret_cast<float2*>(smem_raw);
-  float* gains = reinterpret_cast<float*>(tw + kNB);
+  float* gains = reinterpret_cast<float*>(tw + kTwSlots);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   float2* ex = reinterpret_cast<float2*>(gains + kR * kGainStride) + warp * kExch;
   __shared__ long long part[kUWarps][4];
   __shared__ float qa_u[4];
-  for (int i = threadIdx.x; i < kNB; i += kUWarps * 32) tw[i] = __ldg(g_tw + i);
-  for (int i = threadIdx.x; i < kR * kGainStride; i += kUWarps * 32) gains[i] = __ldg(g_gains + i);
+  load_tables(tw, gains, g_tw, g_gains, threadIdx.x, kUWarps * 32);
   // u's own alternating sum over its reflect_101-padded line (64-bit integers: exact)
   long long a[4] = {0, 0, 0, 0};
   for (int x = threadIdx.x; x < T; x += kUWarps * 32) {
@@ -210,65 +155,88 @@ __global__ void __launch_bounds__(kUWarps * 32, 1)
   __syncthreads();
   const int L = kNB - 2 * pad;
   const int nitems = ((T + L - 1) / L) * 2;
+  const float2* twl = tw + lane * kTwStride;
   for (int it = warp; it < nitems; it += kUWarps) {
     const int pair = it & 1, s = (it >> 1) * L;
     float2 c[kR];
     load_block_u(c, u, T, pad, s, pair, lane);
-#pragma unroll 1
-    for (int q = 0; q < 4; ++q) {
-      dft<kR, false>(c);
-      if ((q & 1) == 0) {
-        tw_write_col(c, lane, ex, tw);
-        __syncwarp();
-        read_row(c, lane, ex);
-        __syncwarp();
-      } else if (q == 1) {
-        mid_gains(c, lane, gains);
-      }
-    }
+    block_passes(c, lane, ex, twl, gains);
     store_block_u(c, make_float2(qa_u[2 * pair], qa_u[2 * pair + 1]), q_col, T, pad, L, s, pair, lane, qc);
   }
 }
 
-template <int CW, int MAXREG>
-__global__ void __maxnreg__(MAXREG) ols_col_rgba_kernel(const __grid_constant__ ColParams P) {
-  extern __shared__ __align__(16) unsigned char smem_raw[];
-  float2* tw = reinterpret_cast<float2*>(smem_raw);
-  float* gains = reinterpret_cast<float*>(tw + kNB);
-  float2* ex_all = reinterpret_cast<float2*>(gains + kR * kGainStride);
-  uint16_t* tile = reinterpret_cast<uint16_t*>(ex_all + CW * kExch);
-  const int t = threadIdx.x, warp = t >> 5, lane = t & 31;
-  float2* ex = ex_all + warp * kExch;
-  for (int i = t; i < kNB; i += CW * 32) tw[i] = __ldg(P.tw + i);
-  for (int i = t; i < kR * kGainStride; i += CW * 32) gains[i] = __ldg(P.gains + i);
-  // no barrier needed here: the first one inside the loop also publishes the tables
-  for (long long it = blockIdx.x; it < P.nitems; it += gridDim.x) {
-    // consecutive items = neighbouring units of the same block: their sectors share 128-byte lines
-    const int j = (int)(it / P.nunits);
-    const int unit = (int)(it - (long long)j * P.nunits);
-    const int s = j * P.L;
-    col_fetch<CW>(P, unit, s, t, ex_all);
-    __syncthreads();
-    float2 c[kR];
-    read_col(c, lane, ex);
-#pragma unroll 1
-    for (int q = 0; q < 4; ++q) {
-      dft<kR, false>(c);
-      if ((q & 1) == 0) {
-        tw_write_col(c, lane, ex, tw);
-        __syncwarp();
-        read_row(c, lane, ex);
-        __syncwarp();
-      } else if (q == 1) {
-        mid_gains(c, lane, gains);
-      }
-    }
-    col_to_tile<CW>(c, __ldg(P.qc + unit * CW + warp), s, warp, lane, tile);
-    __syncthreads();
-    col_store<CW>(P, unit, s, t, tile);
-    // the next fetch overwrites exchange buffers every warp has finished with (barrier above); the next
-    // col_to_tile comes after the next barrier, when every thread has left this col_store
+struct ColKernelParams {
+  ColParams P;
+  CUtensorMap in_map;  // panel intermediate {32 floats, np slots, panels}, box {16, 256, 1}, 64-byte swizzle
+  CUtensorMap out_a;   // u8 image {row bytes, rows, frames}, box {16, st_rows_a, 1}
+  CUtensorMap out_b;   // same tensor, box {16, st_rows_b, 1}
+};
+
+constexpr size_t kColSmem = (size_t)kColRegion + kColTileBytes + kTableBytes + 16;
+
+__global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid_constant__ ColKernelParams K) {
+  extern __shared__ __align__(1024) unsigned char smem_raw[];
+  unsigned char* region = smem_raw;                 // landing area (first 64 KB), then the warps' exchange slices
+  unsigned char* tile = smem_raw + kColRegion;      // u8 results [row][16 bytes]
+  float2* tw = reinterpret_cast<float2*>(tile + kColTileBytes);
+  float* gains = reinterpret_cast<float*>(tw + kTwSlots);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(gains + kR * kGainStride);
+  const ColParams& P = K.P;
+  const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
+  float2* ex = reinterpret_cast<float2*>(region) + w * kExch;
+
+  auto decode = [&](long long it, int& f, int& unit, int& s) {
+    const long long fj = it / P.nunits;
+    unit = P.unit0 + (int)(it - fj * P.nunits);
+    f = (int)(fj / P.nblk);
+    s = (int)(fj - (long long)f * P.nblk) * P.L;
+  };
+  auto request = [&](long long it) {  // one thread: the four landing boxes of item `it`
+    int f, unit, s;
+    decode(it, f, unit, s);
+    mbar_expect_tx(bar, kNB * kColFloats * 4);
+#pragma unroll
+    for (int q = 0; q < kNB / kColBoxSlots; ++q)
+      tma_load_3d(region + q * (kColBoxSlots * 64), &K.in_map, (unit & 1) * kColFloats, s + q * kColBoxSlots,
+                  f * P.panels_per_frame + (unit >> 1), bar);
+  };
+
+  if (tid == 0) {
+    mbar_init(bar, 1);
+    fence_proxy_async();
   }
+  load_tables(tw, gains, P.tw, P.gains, tid, kColWarps * 32);
+  __syncthreads();
+  long long it = blockIdx.x;
+  if (tid == 0 && it < P.nitems) request(it);
+  const float2* twl = tw + lane * kTwStride;
+  uint32_t parity = 0;
+  for (; it < P.nitems; it += gridDim.x) {
+    int f, unit, s;
+    decode(it, f, unit, s);
+    mbar_wait(bar, parity);
+    parity ^= 1;
+    float2 c[kR];
+    read_col(c, lane, w, region);
+    __syncthreads();  // the landing area is consumed: it becomes the exchange slices
+    block_passes(c, lane, ex, twl, gains);
+    if (tid == 0) bulk_wait_read<0>();  // the previous item's stores have read the tile
+    fence_proxy_async();                // order this thread's exchange traffic before the next TMA writes
+    __syncthreads();                    // exchanges done: the region is free, and so is the tile
+    if (tid == 0 && it + gridDim.x < P.nitems) request(it + gridDim.x);
+    const float2 qc = P.qc ? __ldg(P.qc + f * P.qc_frame_stride + unit * kColWarps + w) : make_float2(0.f, 0.f);
+    col_to_tile(c, qc, s, P.pad, P.L, w, lane, tile);
+    fence_proxy_async();  // the tile writes become visible to the async proxy
+    __syncthreads();
+    if (tid == 0) {
+      const int c0 = unit * kColFloats;
+#pragma unroll 1
+      for (int b = 0; b < P.st_na; ++b) tma_store_3d(&K.out_a, c0, s + b * P.st_rows_a, f, tile + b * P.st_rows_a * kColFloats);
+      if (P.st_rows_b) tma_store_3d(&K.out_b, c0, s + P.st_na * P.st_rows_a, f, tile + P.st_na * P.st_rows_a * kColFloats);
+      bulk_commit();
+    }
+  }
+  if (tid == 0) bulk_wait<0>();
 }
 
 cudaError_t row_plan_create(RowPlan** out, const std::vector<float>& taps, int n_ref, int n_ref_col) {
@@ -318,24 +286,31 @@ bool row_profitable(const RowLaunch& a, int n_ref) {
 
 namespace {
 
+// The dynamic shared-memory limit of a kernel is one attribute per function and device: set once, to the size the
+// kernel always uses, under a process-wide once-flag per device (not per thread: ADVICE r1).
+struct PerDevice {
+  std::once_flag once[64];
+  cudaError_t err[64];
+  int per_sm[64];
+};
+
 template <int WARPS, int MAXREG>
 cudaError_t launch_blocks(const RowParams& P, int num_sms, cudaStream_t stream) {
-  constexpr size_t smem = (size_t)kNB * 8 + (size_t)kR * kGainStride * 4 + (size_t)WARPS * kExch * 8;
+  constexpr size_t smem = kTableBytes + (size_t)WARPS * kExch * 8;
   auto k = ols_row_rgba_kernel<WARPS, MAXREG>;
-  static thread_local int cached_device = -1, cached_per_sm = 0;
+  static PerDevice pd;
   int device = 0;
   cudaGetDevice(&device);
-  if (cached_device != device) {
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (e != cudaSuccess) return e;
-    int per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, WARPS * 32, smem);
-    if (e != cudaSuccess) return e;
-    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-    cached_device = device;
-    cached_per_sm = per_sm;
-  }
-  long long grid = (long long)num_sms * cached_per_sm;
+  device &= 63;
+  std::call_once(pd.once[device], [&] {
+    pd.per_sm[device] = 0;
+    pd.err[device] = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (pd.err[device] == cudaSuccess)
+      pd.err[device] = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pd.per_sm[device], k, WARPS * 32, smem);
+    if (pd.err[device] == cudaSuccess && pd.per_sm[device] < 1) pd.err[device] = cudaErrorLaunchOutOfResources;
+  });
+  if (pd.err[device] != cudaSuccess) return pd.err[device];
+  long long grid = (long long)num_sms * pd.per_sm[device];
   const long long need = (P.nitems + WARPS - 1) / WARPS;
   if (grid > need) grid = need;
   k<<<(unsigned)grid, WARPS * 32, smem, stream>>>(P);
@@ -353,7 +328,6 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
     cudaError_t e = cudaMalloc(&p->d_qa, (size_t)a.rows_total * sizeof(float4));
     if (e != cudaSuccess) return e;
     p->qa_rows = a.rows_total;
-    p->qa_valid = false;
   }
   RowParams P{};
   P.in = a.in;
@@ -373,103 +347,47 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
   P.tw = p->d_tw;
   P.gains = p->d_gains;
 
-  // warps per CTA / register cap; resident warps per SM: 20 in two CTAs (default: 0.362 ms on 8K RGBA against 0.375
-  // for 16 in one CTA and 0.38 for 16 in two or four, profiles/r01/ols_rowpass_v2_check.jsonl), 16, 16, 24, 16;
-  // 5 = one CTA per row without the pre-kernel (rows of at most 10 blocks)
+  const unsigned nb = (unsigned)((a.rows_total + kAltsumWarps - 1) / kAltsumWarps);
+  altsum_rows_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total, p->d_qa);
+  count_launch();
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+
+  // warps per CTA / register cap (process-wide tuning knob, read once): 0 = 2 CTAs x 10 warps x 96 registers (default),
+  // 1 = 2 x 8 x 128, 2 = 1 x 16 x 128, 3 = 2 x 12 x 80
   static const int variant = [] {
     const char* v = getenv("GBLUR_OLS_VARIANT");
-    return v ? atoi(v) : 1;
+    return v ? atoi(v) : 0;
   }();
-  if (variant == 5 && 2 * P.nblk <= 20) {
-    const int nwarps = 2 * P.nblk;
-    const size_t smem = (size_t)kNB * 8 + (size_t)kR * kGainStride * 4 + (size_t)nwarps * kExch * 8;
-    static thread_local int cta_device = -1;
-    int device = 0;
-    cudaGetDevice(&device);
-    if (cta_device != device) {
-      cudaError_t ea = cudaFuncSetAttribute(ols_row_cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            (int)((size_t)kNB * 8 + (size_t)kR * kGainStride * 4 + (size_t)20 * kExch * 8));
-      if (ea != cudaSuccess) return ea;
-      cta_device = device;
-    }
-    long long grid = num_sms;
-    if (grid > a.rows_total) grid = a.rows_total;
-    ols_row_cta_kernel<<<(unsigned)grid, nwarps * 32, smem, stream>>>(P, p->q);
-    count_launch();
-    return cudaGetLastError();
-  }
-
-  // timing aid only: GBLUR_OLS_NO_ALTSUM=1 reuses the sums of the previous call on this plan (same input assumed)
-  static const bool reuse_sums = getenv("GBLUR_OLS_NO_ALTSUM") != nullptr;
-  cudaError_t e = cudaSuccess;
-  if (!(reuse_sums && p->qa_valid)) {
-    const unsigned nb = (unsigned)((a.rows_total + kAltsumWarps - 1) / kAltsumWarps);
-    altsum_rows_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total, p->d_qa);
-    count_launch();
-    e = cudaGetLastError();
-    if (e != cudaSuccess) return e;
-    p->qa_valid = true;
-  }
-
   switch (variant) {
-    case 0:
+    case 1:
       return launch_blocks<8, 128>(P, num_sms, stream);
     case 2:
-      return launch_blocks<4, 128>(P, num_sms, stream);
-    case 3:
-      return launch_blocks<24, 80>(P, num_sms, stream);
-    case 4:
       return launch_blocks<16, 128>(P, num_sms, stream);
+    case 3:
+      return launch_blocks<12, 80>(P, num_sms, stream);
     default:
       return launch_blocks<10, 96>(P, num_sms, stream);
   }
 }
 
-namespace {
-template <int CW>
-cudaError_t launch_col_blocks(ColParams P, int num_sms, cudaStream_t stream) {
-  constexpr size_t tables = (size_t)kNB * 8 + (size_t)kR * kGainStride * 4;
-  constexpr size_t csmem = tables + (size_t)CW * kExch * 8 + (size_t)kNB * CW * sizeof(uint16_t);
-  P.nunits = (P.cols + CW / 2 - 1) / (CW / 2);
-  P.nitems = (long long)P.nunits * P.nblk;
-  auto k = ols_col_rgba_kernel<CW, 128>;
-  static thread_local int c_device = -1, c_per_sm = 0;
-  int device = 0;
-  cudaGetDevice(&device);
-  if (c_device != device) {
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)csmem);
-    if (e != cudaSuccess) return e;
-    int per_sm = 0;
-    e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, CW * 32, csmem);
-    if (e != cudaSuccess) return e;
-    if (per_sm < 1) return cudaErrorLaunchOutOfResources;
-    c_device = device;
-    c_per_sm = per_sm;
-  }
-  long long grid = (long long)num_sms * c_per_sm;
-  if (grid > P.nitems) grid = P.nitems;
-  k<<<(unsigned)grid, CW * 32, csmem, stream>>>(P);
-  count_launch();
-  return cudaGetLastError();
-}
-}  // namespace
-
 bool col_eligible(const RowPlan* p, const ColLaunch& a) {
-  return p && p->q_col != 0.f && a.C == 4 && a.Cp == 4 && a.frames == 1 && a.blk.enabled && a.panel_in == 0 &&
-         a.w_begin == 0 && (a.w_end == 0 || a.w_end == a.W) && (a.W % 16) == 0 &&
-         (reinterpret_cast<uintptr_t>(a.out) % 16) == 0 && (a.out_pitch % 16) == 0 &&
-         (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0 && 2 * a.pad + 1 == p->ksize && a.pad <= kMaxPad && a.T >= 1;
+  const int w_end = a.w_end ? a.w_end : a.W;
+  return p && a.C == a.Cp && a.blk.enabled && a.blk.padq == 0 && a.panel_in == 0 && (a.W % kColFloats) == 0 &&
+         (a.w_begin % kColFloats) == 0 && (w_end % kColFloats) == 0 && w_end > a.w_begin &&
+         (reinterpret_cast<uintptr_t>(a.out) % 16) == 0 && (a.out_pitch % 16) == 0 && (a.out_frame_stride % 16) == 0 &&
+         (reinterpret_cast<uintptr_t>(a.inter) % 128) == 0 && 2 * a.pad + 1 == p->ksize && a.pad <= kMaxPad &&
+         a.T >= 1 && a.frames == 1 && a.C == 4;  // the column Nyquist terms are built from one RGBA frame so far
 }
 
 bool col_profitable(const ColLaunch& a, int n_ref_col) {
   const int L = kNB - 2 * a.pad;
-  if (L < 1 || a.T < 4096) return false;
+  if (L < 1 || a.T < 2048) return false;
   const long long nblk = (a.T + L - 1) / L;
   return nblk * kNB * 5 <= (long long)n_ref_col * 6;
 }
 
-cudaError_t launch_col(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long long in_pitch, int num_sms,
-                       cudaStream_t stream) {
+cudaError_t launch_col_terms(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long long in_pitch, cudaStream_t stream) {
   const int cols = a.W / 4, rows = a.T;
   cudaError_t e;
   if (p->u_cols < cols) {
@@ -491,41 +409,86 @@ cudaError_t launch_col(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long
   e = cudaGetLastError();
   if (e != cudaSuccess) return e;
 
-  constexpr size_t tables = (size_t)kNB * 8 + (size_t)kR * kGainStride * 4;
-  constexpr size_t usmem = tables + (size_t)kUWarps * kExch * 8;
-  static thread_local int u_device = -1;
+  constexpr size_t usmem = kTableBytes + (size_t)kUWarps * kExch * 8;
+  static PerDevice upd;
   int device = 0;
   cudaGetDevice(&device);
-  if (u_device != device) {
-    e = cudaFuncSetAttribute(u_rowpass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)usmem);
-    if (e != cudaSuccess) return e;
-    u_device = device;
-  }
+  device &= 63;
+  std::call_once(upd.once[device], [&] {
+    upd.err[device] = cudaFuncSetAttribute(u_rowpass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)usmem);
+  });
+  if (upd.err[device] != cudaSuccess) return upd.err[device];
   u_rowpass_kernel<<<1, kUWarps * 32, usmem, stream>>>(p->d_u, cols, a.pad, p->q, p->q_col, p->d_tw, p->d_gains, p->d_qc);
   count_launch();
-  e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
+  return cudaGetLastError();
+}
 
-  ColParams P{};
-  P.inter = a.inter;
-  P.panel_stride = (long long)a.blk.np * 32;
-  P.padq = a.blk.padq;
+cudaError_t launch_col(RowPlan* p, const ColLaunch& a, int num_sms, cudaStream_t stream) {
+  const int rows = a.T;
+  static PerDevice cpd;
+  int device = 0;
+  cudaGetDevice(&device);
+  device &= 63;
+  ColKernelParams K{};
+  ColParams& P = K.P;
   P.T = rows;
   P.pad = a.pad;
   P.L = kNB - 2 * a.pad;
   P.nblk = (rows + P.L - 1) / P.L;
-  P.cols = cols;
-  P.out = a.out;
-  P.out_pitch = a.out_pitch;
+  const int w_end = a.w_end ? a.w_end : a.W;
+  P.unit0 = a.w_begin / kColFloats;
+  P.nunits = (w_end - a.w_begin) / kColFloats;
+  P.frames = a.frames;
+  P.nitems = (long long)P.frames * P.nunits * P.nblk;
+  P.panels_per_frame = (int)(a.blk.frame_stride / ((long long)a.blk.np * 32));
+  P.st_rows_a = 256;
+  P.st_na = P.L / 256;
+  P.st_rows_b = P.L % 256;
+  P.qc_frame_stride = 0;
   P.qc = p->d_qc;
   P.tw = p->d_tw;
   P.gains = p->d_gains;
-  // GBLUR_OLS_COL_VARIANT: 0 = four warps per quarter panel (4 CTAs per SM), 1 = eight warps per half panel (2 CTAs)
-  static const int variant = [] {
-    const char* v = getenv("GBLUR_OLS_COL_VARIANT");
-    return v ? atoi(v) : 0;
-  }();
-  return variant == 1 ? launch_col_blocks<8>(P, num_sms, stream) : launch_col_blocks<4>(P, num_sms, stream);
+
+  const long long panels_total = (long long)P.panels_per_frame * a.frames;
+  const long long key[6] = {a.blk.np, panels_total, rows, a.out_pitch, a.out_frame_stride, ((long long)a.frames << 32) | (unsigned)a.W};
+  bool same = p->map_inter == a.inter && p->map_out == a.out;
+  for (int i = 0; i < 6; ++i) same = same && p->map_key[i] == key[i];
+  if (!same) {
+    const unsigned long long idims[3] = {32, (unsigned long long)a.blk.np, (unsigned long long)panels_total};
+    const unsigned long long istr[2] = {128, (unsigned long long)a.blk.np * 128};
+    const unsigned ibox[3] = {(unsigned)kColFloats, (unsigned)kColBoxSlots, 1};
+    const unsigned long long odims[3] = {(unsigned long long)a.W, (unsigned long long)rows, (unsigned long long)a.frames};
+    const unsigned long long ostr[2] = {(unsigned long long)a.out_pitch, (unsigned long long)a.out_frame_stride};
+    const unsigned obox_a[3] = {(unsigned)kColFloats, (unsigned)P.st_rows_a, 1};
+    const unsigned obox_b[3] = {(unsigned)kColFloats, (unsigned)(P.st_rows_b ? P.st_rows_b : 1), 1};
+    if (!encode_tensor_map(&p->in_map, 4, 3, a.inter, idims, istr, ibox, 64) ||
+        !encode_tensor_map(&p->out_a, 1, 3, a.out, odims, ostr, obox_a, 0) ||
+        !encode_tensor_map(&p->out_b, 1, 3, a.out, odims, ostr, obox_b, 0)) {
+      p->map_inter = nullptr;
+      return cudaErrorNotSupported;
+    }
+    p->map_inter = a.inter;
+    p->map_out = a.out;
+    for (int i = 0; i < 6; ++i) p->map_key[i] = key[i];
+  }
+  K.in_map = p->in_map;
+  K.out_a = p->out_a;
+  K.out_b = p->out_b;
+
+  std::call_once(cpd.once[device], [&] {
+    cpd.per_sm[device] = 0;
+    cpd.err[device] = cudaFuncSetAttribute(ols_col_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kColSmem);
+    if (cpd.err[device] == cudaSuccess)
+      cpd.err[device] =
+          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cpd.per_sm[device], ols_col_kernel, kColWarps * 32, kColSmem);
+    if (cpd.err[device] == cudaSuccess && cpd.per_sm[device] < 1) cpd.err[device] = cudaErrorLaunchOutOfResources;
+  });
+  if (cpd.err[device] != cudaSuccess) return cpd.err[device];
+  long long grid = (long long)num_sms * cpd.per_sm[device];
+  if (grid > P.nitems) grid = P.nitems;
+  ols_col_kernel<<<(unsigned)grid, kColWarps * 32, kColSmem, stream>>>(K);
+  count_launch();
+  return cudaGetLastError();
 }
 
 }  // namespace ols
