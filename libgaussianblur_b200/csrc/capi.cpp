@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -64,6 +65,7 @@ struct LineTables {
 }  // namespace
 
 struct gblur_plan {
+  std::mutex host_mu;  // the host-buffer entry points use the plan's own stream, staging buffers and workspace: one at a time
   int device = 0;
   int num_sms = 148;
   int channels = 0;
@@ -85,6 +87,8 @@ struct gblur_plan {
   size_t stage_bytes = 0;
   cudaStream_t stream = nullptr;
   cudaStream_t s_in = nullptr, s_out = nullptr;  // copy streams of the pipelined host path
+  cudaStream_t s_side = nullptr;                 // the column Nyquist terms run here, beside the row pass
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
   std::vector<cudaEvent_t> events;               // reused by the pipelined host path
   uint8_t* d_stage2 = nullptr;                   // second staging buffer (batches)
   size_t stage2_bytes = 0;
@@ -144,6 +148,7 @@ BlockedLayout blocked_layout(const gblur_plan* p, int cp, bool ols_col = false) 
   // cluster column plans read the panel through their loader: natural slot order, no padding holes
   b.np = (c.cluster > 1 || ols_col) ? c.N : c.exch_elems;
   b.padq = (c.cluster > 1 || ols_col) ? 0 : c.padq;
+  b.pair_major = ols_col ? 1 : 0;  // written by the overlap-save row pass, read by the overlap-save column pass
   b.rows_per_frame = p->full_rows;
   const long long panels = ((long long)p->cols * cp + 31) / 32;
   b.frame_stride = panels * b.np * 32;
@@ -225,10 +230,15 @@ bool ols_col_wanted(const gblur_plan* p, int cp, int frames) {
   if (!p->ols_row || p->ols_col_mode == 0 || p->band || p->channels != 4 || cp != 4 || frames != 1) return false;
   if (((long long)p->cols * cp) % 16 || ((long long)p->full_cols * p->channels) % 16) return false;
   if (p->ols_col_mode == 1) return true;
+  // automatic: both passes must gain (the pair-major panel rows tie them together)
   ColLaunch a{};
   a.T = p->full_rows;
   a.pad = p->sz.pad;
-  return p->col.lp.cluster == 1 && ols::col_profitable(a, p->sz.n_colpass);
+  RowLaunch r{};
+  r.T = p->full_cols;
+  r.pad = p->sz.pad;
+  return p->col.lp.cluster == 1 && p->row.lp.cluster == 1 && p->ols_mode != 0 && ols::col_profitable(a, p->sz.n_colpass) &&
+         ols::row_profitable(r, p->sz.n_rowpass);
 }
 
 // rows_sub > 0: only rows [row0, row0 + rows_sub) of a single frame (d_in / d_inter still point at row 0)
@@ -257,8 +267,11 @@ int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pi
     else
       a.inter = d_inter + (long long)row0 * pitch;
   }
+  if (blk && blk->pair_major && !(p->ols_row && ols::row_eligible(p->ols_row, a)))
+    return fail(GBLUR_E_UNSUPPORTED, "pair-major panel layout, but the overlap-save row pass is not eligible");
   if (p->ols_row && ols::row_eligible(p->ols_row, a) &&
-      (p->ols_mode == 1 || (fused_single && p->row.lp.cluster == 1 && ols::row_profitable(a, p->sz.n_rowpass)))) {
+      ((blk && blk->pair_major) || p->ols_mode == 1 ||
+       (fused_single && p->row.lp.cluster == 1 && ols::row_profitable(a, p->sz.n_rowpass)))) {
     CU(ols::launch_row(p->ols_row, a, p->num_sms, s));
     p->last_row_kind = 1;
     return GBLUR_OK;
@@ -375,6 +388,9 @@ void gblur_plan_destroy(gblur_plan* p) {
   if (p->d_stage) cudaFree(p->d_stage);
   if (p->d_stage2) cudaFree(p->d_stage2);
   for (cudaEvent_t e : p->events) cudaEventDestroy(e);
+  if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+  if (p->ev_join) cudaEventDestroy(p->ev_join);
+  if (p->s_side) cudaStreamDestroy(p->s_side);
   if (p->s_in) cudaStreamDestroy(p->s_in);
   if (p->s_out) cudaStreamDestroy(p->s_out);
   for (void* q : p->owned) cudaFree(q);
@@ -473,15 +489,34 @@ static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_f
   FusedCtx c;
   int rc = fused_prepare(p, n_frames, apply_to_alpha, s, c);
   if (rc != GBLUR_OK) return rc;
+  // The column terms of the overlap-save column pass depend on the input image only: in a two-stage run they are
+  // computed on a side stream while the row pass runs (one pass over the u8 input, hidden under a pass that is not
+  // memory-bound), and joined before the column blocks.
+  bool terms_forked = false;
+  if (stages == 3 && n_frames == 1 && c.bp && c.blk.padq == 0 && ols_col_wanted(p, c.cp, n_frames)) {
+    if (!p->s_side) CU(cudaStreamCreateWithFlags(&p->s_side, cudaStreamNonBlocking));
+    if (!p->ev_fork) CU(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+    if (!p->ev_join) CU(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
+    ColLaunch a{};
+    a.T = p->full_rows;
+    a.pad = p->sz.pad;
+    a.W = p->cols * c.cp;
+    CU(cudaEventRecord(p->ev_fork, s));
+    CU(cudaStreamWaitEvent(p->s_side, p->ev_fork, 0));
+    CU(ols::launch_col_terms(p->ols_row, a, d_in, (long long)p->full_cols * p->channels, p->s_side));
+    CU(cudaEventRecord(p->ev_join, p->s_side));
+    terms_forked = true;
+  }
   if (stages & 1) {
     rc = run_rowpass(p, d_in, p->d_inter, c.pitch, n_frames, apply_to_alpha, s, c.bp, 0, 0, 0, 0, n_frames == 1);
     if (rc != GBLUR_OK) return rc;
   }
   if (!(stages & 2)) return GBLUR_OK;
+  if (terms_forked) CU(cudaStreamWaitEvent(s, p->ev_join, 0));
   if (d_in != d_out && c.cp < p->channels)
     CU(launch_copy_channel(d_in, d_out, (long long)p->rows * p->cols * n_frames, p->channels, 3, s));
   return run_colpass(p, p->d_inter, c.pitch, d_out, (long long)p->cols * p->channels, n_frames, apply_to_alpha, s, c.bp,
-                     0, 0, n_frames == 1 ? d_in : nullptr);
+                     0, 0, n_frames == 1 ? d_in : nullptr, !terms_forked);
 }
 
 int gblur_run_batch_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
@@ -598,6 +633,7 @@ int gblur_run_batch_host(gblur_plan* p, uint8_t* hwc, int n_frames, int apply_to
   if (!p || !hwc) return fail(GBLUR_E_INVALID, "null argument");
   if (p->band) return fail(GBLUR_E_INVALID, "band plans run through gblur_rowpass_device / gblur_colpass_device");
   if (n_frames < 1) return fail(GBLUR_E_INVALID, "n_frames %d < 1", n_frames);
+  std::lock_guard<std::mutex> host_lock(p->host_mu);
   DeviceGuard guard(p->device);
   const size_t frame_bytes = (size_t)p->rows * p->cols * p->channels;
   static const int pipe_chunks = [] {
@@ -838,8 +874,11 @@ int gblur_dump_intermediate(gblur_plan* p, float* host_out, int apply_to_alpha) 
   for (int r = 0; r < p->rows; ++r) {
     const int n = p->sz.pad + r;
     const long long slot = b.padq ? n + n / b.padq : n;
-    for (long long x = 0; x < w; ++x)
-      host_out[(size_t)r * w + x] = blk[(size_t)((x / 32) * b.np + slot) * 32 + (size_t)(x % 32)];
+    for (long long x = 0; x < w; ++x) {
+      const int k = (int)(x % 32);  // pixel-major position 4 px + 2 pair + c  ->  pair-major 16 pair + 2 px + c
+      const int kk = b.pair_major ? ((k >> 1) & 1) * 16 + (k >> 2) * 2 + (k & 1) : k;
+      host_out[(size_t)r * w + x] = blk[(size_t)((x / 32) * b.np + slot) * 32 + (size_t)kk];
+    }
   }
   return GBLUR_OK;
 }

@@ -31,33 +31,78 @@ struct PlanKey {
   }
 };
 
-// Small LRU of GPU plans so repeated gaussianblur() calls on one geometry (video) do not rebuild
-// spectra, twiddles and workspaces; the reference recomputes its kernel on every call (:319).
+// Small pool of GPU plans so repeated gaussianblur() calls on one geometry (video) do not rebuild spectra, twiddles
+// and workspaces; the reference recomputes its kernel on every call (:319). A plan owns one workspace, one staging
+// buffer and one stream, so it serves ONE call at a time: a caller checks a plan out exclusively (Lease) and a second
+// thread blurring the same geometry at the same moment gets a second plan — the reference call is re-entrant
+// (no globals, PFFFT_Setup read-only: include/pffft_pommier/pffft.h:100-103) and so is this one.
 class PlanCache {
  public:
-  GblurPlanHandle get(const PlanKey &key) {
-    std::lock_guard<std::mutex> lock(mu_);
-    for (auto it = items_.begin(); it != items_.end(); ++it) {
-      if (it->first == key) {
-        items_.splice(items_.begin(), items_, it);
-        return items_.front().second;
+  struct Entry {
+    PlanKey key;
+    GblurPlanHandle plan;
+    bool busy;
+  };
+  class Lease {
+   public:
+    Lease(PlanCache *c, GblurPlanHandle p) : cache_(c), plan_(std::move(p)) {}
+    Lease(const Lease &) = delete;
+    Lease &operator=(const Lease &) = delete;
+    ~Lease() { cache_->release(plan_.get()); }
+    gblur_plan *get() const { return plan_.get(); }
+    const GblurPlanHandle &handle() const { return plan_; }
+
+   private:
+    PlanCache *cache_;
+    GblurPlanHandle plan_;
+  };
+
+  GblurPlanHandle checkout(const PlanKey &key) {
+    {
+      std::lock_guard<std::mutex> lock(mu_);
+      for (auto it = items_.begin(); it != items_.end(); ++it) {
+        if (it->key == key && !it->busy) {
+          it->busy = true;
+          items_.splice(items_.begin(), items_, it);
+          return items_.front().plan;
+        }
       }
     }
+    // plan creation (device allocations, table uploads) happens outside the lock
     float sigma;
     std::memcpy(&sigma, &key.sigma_bits, sizeof sigma);
     gblur_plan *raw = nullptr;
     const int rc = gblur_plan_create_batch(&raw, key.device, key.rows, key.cols, key.channels, sigma, key.frames);
     if (rc != GBLUR_OK) throw std::runtime_error(std::string("gaussianblur: ") + gblur_last_error());
     GblurPlanHandle h(raw, [](gblur_plan *p) { gblur_plan_destroy(p); });
-    items_.emplace_front(key, h);
-    while (items_.size() > kCapacity) items_.pop_back();
+    std::lock_guard<std::mutex> lock(mu_);
+    items_.push_front(Entry{key, h, true});
+    trim();
     return h;
   }
 
+  void release(const gblur_plan *p) {
+    std::lock_guard<std::mutex> lock(mu_);
+    for (auto &e : items_)
+      if (e.plan.get() == p) e.busy = false;
+    trim();
+  }
+
  private:
+  void trim() {  // drop idle plans from the cold end; busy ones stay until they are released
+    size_t idle = 0;
+    for (auto &e : items_) idle += e.busy ? 0 : 1;
+    for (auto it = items_.end(); idle > kCapacity && it != items_.begin();) {
+      --it;
+      if (!it->busy) {
+        it = items_.erase(it);
+        --idle;
+      }
+    }
+  }
   static constexpr size_t kCapacity = 4;
   std::mutex mu_;
-  std::list<std::pair<PlanKey, GblurPlanHandle>> items_;
+  std::list<Entry> items_;
 };
 
 PlanCache &cache() {
@@ -111,7 +156,7 @@ KernelDFT prepare_kernel_DFT(const ImgGeom image_geometry, const float sigma) {
 
 void gaussianblur_buffer(uint8_t *hwc, const ImgGeom geometry, const float sigma, const bool apply_to_alpha) {
   if (!valid_request(geometry, sigma, true)) return;
-  GblurPlanHandle plan = cache().get(make_key(geometry, sigma, 1));
+  PlanCache::Lease plan(&cache(), cache().checkout(make_key(geometry, sigma, 1)));
   check(gblur_run_host(plan.get(), hwc, apply_to_alpha ? 1 : 0));
 }
 
@@ -119,7 +164,7 @@ void gaussianblur(Image &image, const float sigma, const bool apply_to_alpha) {
   if (!valid_request(image.geom, sigma, false)) return;
   const size_t need = (size_t)image.geom.rows * image.geom.cols * image.geom.channels;
   if (image.data.size() < need) throw std::runtime_error("gaussianblur: image.data smaller than rows*cols*channels");
-  GblurPlanHandle plan = cache().get(make_key(image.geom, sigma, 1));
+  PlanCache::Lease plan(&cache(), cache().checkout(make_key(image.geom, sigma, 1)));
   check(gblur_run_host(plan.get(), image.data.data(), apply_to_alpha ? 1 : 0));
 }
 
@@ -129,11 +174,16 @@ void gaussianblur(Image &image, KernelDFT &kernel, const bool apply_to_alpha) {
     throw std::runtime_error("gaussianblur: KernelDFT was prepared for another geometry");
   const size_t need = (size_t)image.geom.rows * image.geom.cols * image.geom.channels;
   if (image.data.size() < need) throw std::runtime_error("gaussianblur: image.data smaller than rows*cols*channels");
+  // The reference's KernelDFT does not depend on the channel count (src/gaussianblur.cpp:100-172), so one handle may
+  // legitimately serve 3- and 4-channel images, from any thread and device: the spectra live in the handle, the GPU
+  // plan behind it is checked out per call by (device, geometry, channels, sigma). The handle only remembers the first
+  // plan (rows_setup / cols_setup become non-null like the reference's setups).
+  PlanCache::Lease plan(&cache(), cache().checkout(make_key(image.geom, kernel.sigma, 1)));
   if (!kernel.rows_setup) {
-    kernel.rows_setup = cache().get(make_key(image.geom, kernel.sigma, 1));
+    kernel.rows_setup = plan.handle();
     kernel.cols_setup = kernel.rows_setup;
   }
-  check(gblur_run_host(kernel.rows_setup.get(), image.data.data(), apply_to_alpha ? 1 : 0));
+  check(gblur_run_host(plan.get(), image.data.data(), apply_to_alpha ? 1 : 0));
 }
 
 void gaussianblur_batch(uint8_t *frames, const int n_frames, const ImgGeom frame_geometry, const float sigma,
@@ -141,7 +191,7 @@ void gaussianblur_batch(uint8_t *frames, const int n_frames, const ImgGeom frame
   if (n_frames <= 0) return;
   if (!valid_request(frame_geometry, sigma, true)) return;
   // the plan holds workspace for 16 frames; longer batches are streamed through it (H2D || blur || D2H)
-  GblurPlanHandle plan = cache().get(make_key(frame_geometry, sigma, n_frames < 16 ? n_frames : 16));
+  PlanCache::Lease plan(&cache(), cache().checkout(make_key(frame_geometry, sigma, n_frames < 16 ? n_frames : 16)));
   check(gblur_run_batch_host(plan.get(), frames, n_frames, apply_to_alpha ? 1 : 0));
 }
 

@@ -35,6 +35,7 @@ struct BlockedLayout {
   int L = 4;                   // floats per column group = 2 * column nseq
   int np = 0;                  // slots per unit (column FFT length + bank padding slots)
   int padq = 0;                // column plan's padq
+  int pair_major = 0;          // 1: panel rows ordered [pair][pixel][2] (overlap-save row AND column pass, ols_core.cuh)
   int rows_per_frame = 0;
   long long frame_stride = 0;  // floats per frame = panels * np * 32
 };

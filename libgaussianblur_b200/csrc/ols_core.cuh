@@ -57,6 +57,7 @@ struct RowParams {
   int rows_per_frame;
   int row_offset;
   int blk_np, blk_padq;
+  int pair_major;          // 1: the 32 floats of a panel row are ordered [pair][pixel][2] instead of [pixel][pair][2]
   long long blk_frame_stride;
   const float4* qa;        // per image row: (K[0] - K[N/2]) / N * alternating sum, one float per channel
   const float2* tw;        // tw[lane * kTwStride + k] = exp(-2 pi i lane k / 1024)
@@ -194,15 +195,58 @@ __device__ __forceinline__ void load_block(float2 (&c)[kR], const RowParams& P, 
   }
 }
 
-// twiddle w^(lane * k) on register k, then column `lane` of the exchange; twl = this lane's row of the table
+// The same block out of a staged copy of the row's pixels [x_lo, x_lo + kStagePx) in shared memory (the row kernel
+// bulk-copies it there one item ahead, so no global-load latency sits between two items of a warp).
+constexpr int kStagePx = kNB + 4;  // 1024 pixels from a 4-pixel (16-byte) aligned start
+__device__ __forceinline__ int stage_x_lo(int s, int pad) { return (s - pad > 0 ? s - pad : 0) & ~3; }
+template <bool INTERIOR>
+__device__ __forceinline__ void load_block_staged(float2 (&c)[kR], const RowParams& P, const uint32_t* __restrict__ stage,
+                                                  int s, int pair, int lane) {
+  const int x_lo = stage_x_lo(s, P.pad);
+  if constexpr (INTERIOR) {
+    const uint32_t* p = stage + (s - P.pad - x_lo + lane);
+#pragma unroll
+    for (int i = 0; i < kR; ++i) c[i] = u8_pair(p[kR * i], pair);
+  } else {
+#pragma unroll
+    for (int i = 0; i < kR; ++i) {
+      const int x = reflect_src(s + lane + kR * i, P.pad, P.T);
+      const float2 v = u8_pair(stage[x < 0 ? 0 : x - x_lo], pair);
+      c[i] = (x < 0) ? make_float2(0.f, 0.f) : v;
+    }
+  }
+}
+
+// 16 bytes of the twiddle table. On the device this is an ordered (volatile) shared-memory load: left to itself the
+// compiler sinks every table load to its first use, two instructions before the dependent multiply, and the warp then
+// eats the full shared-memory latency sixteen times per exchange (ncu: the hottest short-scoreboard stalls of the kernel)
+__device__ __forceinline__ float4 tw_load(const float4* p) {
+#if defined(__CUDA_ARCH__)
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "r"((uint32_t)__cvta_generic_to_shared(p))
+               : "memory");
+  return v;
+#else
+  return *p;
+#endif
+}
+
+// twiddle w^(lane * k) on register k, then column `lane` of the exchange; twl = this lane's row of the table.
+// The table loads run kTwAhead entries ahead of their use (registers freed by the stores pay for them).
+constexpr int kTwAhead = 4;
 __device__ __forceinline__ void tw_write_col(const float2 (&c)[kR], int lane, float2* __restrict__ ex,
                                              const float2* __restrict__ twl) {
   const float4* t4 = reinterpret_cast<const float4*>(twl);
+  float4 t[kR / 2];
+#pragma unroll
+  for (int m = 0; m < kTwAhead; ++m) t[m] = tw_load(t4 + m);
 #pragma unroll
   for (int m = 0; m < kR / 2; ++m) {
-    const float4 t = t4[m];  // twiddles of registers 2m, 2m + 1
-    ex[(2 * m) * kRowStride + lane] = m == 0 ? c[0] : cmul(c[2 * m], make_float2(t.x, t.y));
-    ex[(2 * m + 1) * kRowStride + lane] = cmul(c[2 * m + 1], make_float2(t.z, t.w));
+    if (m + kTwAhead < kR / 2) t[m + kTwAhead] = tw_load(t4 + m + kTwAhead);  // twiddles of registers 2m, 2m + 1
+    ex[(2 * m) * kRowStride + lane] = m == 0 ? c[0] : cmul(c[2 * m], make_float2(t[m].x, t[m].y));
+    ex[(2 * m + 1) * kRowStride + lane] = cmul(c[2 * m + 1], make_float2(t[m].z, t[m].w));
   }
 }
 
@@ -232,8 +276,15 @@ __device__ __forceinline__ void mid_gains(float2 (&c)[kR], int lane, const float
 
 // The four passes. In: c[i] = a[lane + 32 i]. Out: c[j] = 1024 y[(32 - lane) + 32 (31 - j) mod 1024] (the 1/1024 sits in
 // the gains), y = the circular convolution of the block with the centred taps.
+// after_exchanges(): called once, when this warp has made its last access to the exchange buffer (the column kernel
+// hands the buffer back to the TMA loads of the next item there, one 32-point DFT before the end of the item).
+struct NoHook {
+  __device__ __forceinline__ void operator()() const {}
+};
+template <class Hook = NoHook>
 __device__ __forceinline__ void block_passes(float2 (&c)[kR], int lane, float2* __restrict__ ex,
-                                             const float2* __restrict__ twl, const float* __restrict__ gains) {
+                                             const float2* __restrict__ twl, const float* __restrict__ gains,
+                                             Hook after_exchanges = Hook()) {
 #pragma unroll 1
   for (int q = 0; q < 4; ++q) {
     dft<kR, false>(c);
@@ -246,6 +297,7 @@ __device__ __forceinline__ void block_passes(float2 (&c)[kR], int lane, float2* 
 #if defined(__CUDA_ARCH__)
       __syncwarp();  // every row has been read before the next pass overwrites columns
 #endif
+      if (q == 2) after_exchanges();
     } else if (q == 1) {
       mid_gains(c, lane, gains);
     }
@@ -262,9 +314,13 @@ __device__ __forceinline__ void store_block(const float2 (&c)[kR], const RowPara
   // outputs are the block indices [pad, min(pad + L, T - s + pad)); index 1024 (lane 0, i = 31) is index 0
   const int lo = P.pad - l1;
   const int hi = min(P.pad + P.L, P.T - s + P.pad) - l1;
-  // pixel x = x0 + 32 i lands in panel (x >> 3) = (x0 >> 3) + 4 i at float offset (x0 & 7) * 4 (+ 2 for pair 1)
+  // pixel x = x0 + 32 i lands in panel (x >> 3) = (x0 >> 3) + 4 i at float offset (x0 & 7) * 4 (+ 2 for pair 1), or,
+  // pair-major (the overlap-save column pass reads it): at pair * 16 + (x0 & 7) * 2 — eight lanes then fill two whole
+  // 32-byte sectors, where the pixel-major order leaves every sector half written until the other pair's warp comes
+  // by (measured: 3x the DRAM reads and 1.5x the writes once the two pairs are stored 10 us apart)
   const int x0 = s + l1 - P.pad;
-  float* dp = d.base + 2 * pair + (long long)(x0 >> 3) * d.gstride + ((x0 & 7) << 2);
+  float* dp = d.base + (long long)(x0 >> 3) * d.gstride +
+              (P.pair_major ? 16 * pair + ((x0 & 7) << 1) : 2 * pair + ((x0 & 7) << 2));
   const long long step = 4 * d.gstride;
   if ((d.dl | d.dr) == 0) {
 #pragma unroll
@@ -286,7 +342,7 @@ __device__ __forceinline__ void store_block(const float2 (&c)[kR], const RowPara
   }
   // pad == 0 (a one-tap window): block index 0 is an output and sits at "index 1024" of lane 0
   if (P.pad == 0 && lane == 0 && s < P.T) {
-    float* d0 = d.base + 2 * pair + (long long)(s >> 3) * d.gstride + ((s & 7) << 2);
+    float* d0 = d.base + (long long)(s >> 3) * d.gstride + (P.pair_major ? 16 * pair + ((s & 7) << 1) : 2 * pair + ((s & 7) << 2));
     const float sg0 = (s & 1) ? -1.0f : 1.0f;
     *reinterpret_cast<float2*>(d0) = make_float2(c[0].x + qa.x * sg0, c[0].y + qa.y * sg0);
   }
@@ -295,10 +351,10 @@ __device__ __forceinline__ void store_block(const float2 (&c)[kR], const RowPara
 // ------------------------------------------------------------------------------------------------------------
 // Column pass: fp32 panel intermediate -> u8 image (replaces the second process_channel_tiles call and
 // interleave_channels, /root/reference/src/gaussianblur.cpp:261-305, helpers.hpp:248-274).
-// One CTA of kColWarps = 8 warps takes a HALF PANEL — 16 float columns = 64 bytes per slot — and one 1024-slot
-// block of the padded column; warp w transforms the column pair (floats 2w, 2w+1 of the unit) with the same four
-// passes as the row pass.
-//   * in : four TMA tile loads {16 floats, 256 slots} with the 64-byte swizzle land the block in the CTA's exchange
+// One CTA of kColWarps = 8 warps takes FOUR PIXELS — 16 float columns, 2 x 32 bytes per slot — and one 1024-slot
+// block of the padded column; warp w transforms one channel pair of one pixel with the same four passes as the row
+// pass.
+//   * in : eight TMA tile loads {8 floats, 256 slots} with the 32-byte swizzle land the block in the CTA's exchange
 //          region (no LSU instruction, no register staging); a lane reads its 32 samples back with LDS.64 (the swizzle
 //          leaves a 2-way bank conflict, 4 wavefronts per load instead of 2).
 //   * out: the u8 results (F2IP.U8.F32.TRUNC: truncate, saturate and pack two channels in one instruction, the + 0.5
@@ -309,36 +365,40 @@ __device__ __forceinline__ void store_block(const float2 (&c)[kR], const RowPara
 // on u8 input, colsum_lane below), so it costs one more line instead of a pass over the 531 MB intermediate.
 // ------------------------------------------------------------------------------------------------------------
 constexpr int kColWarps = 8;
-constexpr int kColFloats = 2 * kColWarps;          // float columns per unit = bytes per output row of a unit
+constexpr int kColFloats = 2 * kColWarps;          // float columns per unit = bytes per output row of a unit (4 RGBA pixels)
 constexpr int kColBoxSlots = 256;                  // slots per TMA load box
+constexpr int kColBoxFloats = 8;                   // floats per slot and box: one pair of the unit's four pixels (32 bytes)
 constexpr int kColRegion = kColWarps * kExch * 8;  // bytes: exchange slices of the 8 warps; the landing area (64 KB) aliases it
 constexpr int kColTileBytes = kNB * kColFloats;    // u8 tile [1024 rows][16 bytes]
 
 struct ColParams {
   int T, pad;               // image rows, reflect pad
   int L, nblk;              // outputs per block, blocks per column
-  int unit0, nunits;        // first unit and unit count of this launch (a unit = 16 float columns)
+  int unit0, nunits;        // first unit and unit count of this launch (a unit = 4 pixels = 16 float columns)
   int frames;
   long long nitems;         // frames * nunits * nblk
   int panels_per_frame;
   int st_na, st_rows_a, st_rows_b;  // store boxes: st_na boxes of st_rows_a rows, then one of st_rows_b rows (0 = none)
   long long qc_frame_stride;        // float2 per frame of qc
-  const float2* qc;         // per column pair: (K[0] - K[N/2]) / N of the column length * row pass of u
+  const float2* qc;         // per column pair 2x + pair: (K[0] - K[N/2]) / N of the column length * row pass of u
   const float2* tw;
   const float* gains;
 };
 
-// byte offset inside the landing area of (slot n of the block, column pair w) under the 64-byte TMA swizzle:
-// 16-byte chunk index (w >> 1) is XORed with bits 7-8 of the offset = (n >> 1) & 3
+// The panel rows are pair-major (store_block): floats [16 g + 2 k, + 2) belong to pair g of pixel k. Warp w takes
+// pair g = w >> 2 of the unit's pixel k = w & 3. The landing area holds, per pair, 1024 slots of 32 bytes (the four
+// pixels of the unit) under the 32-byte TMA swizzle: bit 4 of the offset (which 16-byte half) is XORed with bit 7
+// (= bit 2 of the slot index).
 __device__ __forceinline__ int col_landing_offset(int n, int w) {
-  return (n >> 8) * (kColBoxSlots * 64) + (n & 255) * 64 + ((((w >> 1) ^ (n >> 1)) & 3) << 4) + ((w & 1) << 3);
+  const int g = w >> 2, k = w & 3;
+  return g * (kNB * 32) + n * 32 + ((((k >> 1) ^ (n >> 2)) & 1) << 4) + ((k & 1) << 3);
 }
 
-// c[i] = sample lane + 32 i of column pair w
+// c[i] = sample lane + 32 i of warp w's column pair
 __device__ __forceinline__ void read_col(float2 (&c)[kR], int lane, int w, const unsigned char* __restrict__ landing) {
   const unsigned char* p = landing + col_landing_offset(lane, w);
 #pragma unroll
-  for (int i = 0; i < kR; ++i) c[i] = *reinterpret_cast<const float2*>(p + i * (kR * 64));  // 32 slots further: + 2048 bytes
+  for (int i = 0; i < kR; ++i) c[i] = *reinterpret_cast<const float2*>(p + i * (kR * 32));  // 32 slots further: + 1024 bytes
 }
 
 // two channels -> two bytes, each uint8_t(v) (truncation: helpers.hpp:251-252,270; the caller has added 0.5), saturated
@@ -361,7 +421,8 @@ __device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, in
   const float sg = ((s + l1) & 1) ? -1.0f : 1.0f;
   const float2 add = make_float2(fmaf(qc.x, sg, 0.5f), fmaf(qc.y, sg, 0.5f));
   const int lo = pad - l1, hi = pad + L - l1;
-  unsigned char* tp = tile + (l1 - pad) * kColFloats + 2 * w;
+  const int wb = 4 * (w & 3) + 2 * (w >> 2);  // bytes of pixel k = w & 3, channels 2g, 2g + 1
+  unsigned char* tp = tile + (l1 - pad) * kColFloats + wb;
 #pragma unroll
   for (int i = 0; i < kR; ++i) {
     if (kR * i >= lo && kR * i < hi)
@@ -369,7 +430,7 @@ __device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, in
   }
   if (pad == 0 && lane == 0) {
     const float sg0 = (s & 1) ? -1.0f : 1.0f;
-    *reinterpret_cast<uint16_t*>(tile + 2 * w) =
+    *reinterpret_cast<uint16_t*>(tile + wb) =
         (uint16_t)to_u8x2(make_float2(c[0].x + fmaf(qc.x, sg0, 0.5f), c[0].y + fmaf(qc.y, sg0, 0.5f)));
   }
 }

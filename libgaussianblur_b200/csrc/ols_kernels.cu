@@ -99,6 +99,72 @@ __global__ void __maxnreg__(MAXREG) ols_row_rgba_kernel(const __grid_constant__ 
   }
 }
 
+// The same pass with the input staged: one item = one block of one row, BOTH channel pairs, and the block's 4 KB of
+// pixels arrive in the warp's staging buffer by a bulk asynchronous copy (UBLKCP) issued one item ahead — as soon as
+// the second pair has been read out of the buffer — so a warp never waits for a global load between two items
+// (ncu of the kernel above: 16 % of its stall samples sit on the first use of the loaded pixels).
+// Needs 16-byte aligned rows of a multiple of four pixels. 16 warps per SM (12.8 KB of shared memory per warp).
+template <int WARPS, int MAXREG>
+__global__ void __maxnreg__(MAXREG) ols_row_rgba_staged_kernel(const __grid_constant__ RowParams P) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float2* tw = reinterpret_cast<float2*>(smem_raw);
+  float* gains = reinterpret_cast<float*>(tw + kTwSlots);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float2* ex = reinterpret_cast<float2*>(gains + kR * kGainStride) + warp * kExch;
+  uint32_t* stage = reinterpret_cast<uint32_t*>(reinterpret_cast<float2*>(gains + kR * kGainStride) + WARPS * kExch) +
+                    warp * kStagePx;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(reinterpret_cast<uint32_t*>(reinterpret_cast<float2*>(gains + kR * kGainStride) +
+                                                                            WARPS * kExch) +
+                                              WARPS * kStagePx) +
+                  warp;
+  load_tables(tw, gains, P.tw, P.gains, threadIdx.x, WARPS * 32);
+  if (lane == 0) {
+    mbar_init(bar, 1);
+    fence_proxy_async();
+  }
+  __syncthreads();
+  const float2* twl = tw + lane * kTwStride;
+  const int nblocks = (int)(P.nitems >> 1);
+  const int stride = (int)gridDim.x * WARPS;
+  auto issue = [&](int b) {  // one lane: the pixels the block reads, clipped to the row
+    const int r = b / P.nblk, s = (b - r * P.nblk) * P.L;
+    const int x_lo = stage_x_lo(s, P.pad);
+    int x_hi = s - P.pad + kNB;
+    x_hi = ((x_hi < P.T ? x_hi : P.T) + 3) & ~3;
+    const uint32_t bytes = (uint32_t)(x_hi - x_lo) * 4u;
+    mbar_expect_tx(bar, bytes);
+    bulk_g2s(stage, P.in + (long long)r * P.in_pitch + (long long)x_lo * 4, bytes, bar);
+  };
+  int b = (int)blockIdx.x * WARPS + warp;
+  if (lane == 0 && b < nblocks) issue(b);
+  uint32_t parity = 0;
+  for (; b < nblocks; b += stride) {
+    const int r = b / P.nblk;
+    const int s = (b - r * P.nblk) * P.L;
+    const bool interior = s - P.pad >= 0 && s - P.pad + kNB <= P.T;
+    const float4 q4 = __ldg(P.qa + r);
+    const RowDst d = make_row_dst(P, r);
+    mbar_wait(bar, parity);
+    parity ^= 1;
+    // both channel pairs through ONE copy of the code (rolled: the item's instructions must stay inside the SM's
+    // instruction cache, see ols_core.cuh; the first staged version inlined everything twice and ran 25 % slower)
+#pragma unroll 1
+    for (int pair = 0; pair < 2; ++pair) {
+      float2 c[kR];
+      if (interior)
+        load_block_staged<true>(c, P, stage, s, pair, lane);
+      else
+        load_block_staged<false>(c, P, stage, s, pair, lane);
+      if (pair == 1) {
+        __syncwarp();  // every lane has read the staging buffer for the last time
+        if (lane == 0 && b + stride < nblocks) issue(b + stride);
+      }
+      block_passes(c, lane, ex, twl, gains);
+      store_block(c, P, d, pair ? make_float2(q4.z, q4.w) : make_float2(q4.x, q4.y), s, pair, lane);
+    }
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // column pass
 // ---------------------------------------------------------------------------------------------------------------
@@ -167,7 +233,7 @@ __global__ void __launch_bounds__(kUWarps * 32, 1)
 
 struct ColKernelParams {
   ColParams P;
-  CUtensorMap in_map;  // panel intermediate {32 floats, np slots, panels}, box {16, 256, 1}, 64-byte swizzle
+  CUtensorMap in_map;  // panel intermediate {32 floats, np slots, panels}, box {8, 256, 1}, 32-byte swizzle
   CUtensorMap out_a;   // u8 image {row bytes, rows, frames}, box {16, st_rows_a, 1}
   CUtensorMap out_b;   // same tensor, box {16, st_rows_b, 1}
 };
@@ -196,9 +262,11 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
     decode(it, f, unit, s);
     mbar_expect_tx(bar, kNB * kColFloats * 4);
 #pragma unroll
-    for (int q = 0; q < kNB / kColBoxSlots; ++q)
-      tma_load_3d(region + q * (kColBoxSlots * 64), &K.in_map, (unit & 1) * kColFloats, s + q * kColBoxSlots,
-                  f * P.panels_per_frame + (unit >> 1), bar);
+    for (int g = 0; g < 2; ++g)
+#pragma unroll
+      for (int q = 0; q < kNB / kColBoxSlots; ++q)
+        tma_load_3d(region + g * (kNB * 32) + q * (kColBoxSlots * 32), &K.in_map, g * 16 + (unit & 1) * kColBoxFloats,
+                    s + q * kColBoxSlots, f * P.panels_per_frame + (unit >> 1), bar);
   };
 
   if (tid == 0) {
@@ -219,12 +287,14 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
     float2 c[kR];
     read_col(c, lane, w, region);
     __syncthreads();  // the landing area is consumed: it becomes the exchange slices
-    block_passes(c, lane, ex, twl, gains);
-    if (tid == 0) bulk_wait_read<0>();  // the previous item's stores have read the tile
-    fence_proxy_async();                // order this thread's exchange traffic before the next TMA writes
-    __syncthreads();                    // exchanges done: the region is free, and so is the tile
-    if (tid == 0 && it + gridDim.x < P.nitems) request(it + gridDim.x);
-    const float2 qc = P.qc ? __ldg(P.qc + f * P.qc_frame_stride + unit * kColWarps + w) : make_float2(0.f, 0.f);
+    const long long next = it + gridDim.x;
+    block_passes(c, lane, ex, twl, gains, [&] {
+      if (tid == 0) bulk_wait_read<0>();  // the previous item's stores have read the tile
+      fence_proxy_async();                // order this thread's exchange traffic before the next TMA writes
+      __syncthreads();                    // exchanges done: the region is free, and so is the tile
+      if (tid == 0 && next < P.nitems) request(next);  // lands under the last DFT and the epilogue
+    });
+    const float2 qc = P.qc ? __ldg(P.qc + f * P.qc_frame_stride + (unit * 4 + (w & 3)) * 2 + (w >> 2)) : make_float2(0.f, 0.f);
     col_to_tile(c, qc, s, P.pad, P.L, w, lane, tile);
     fence_proxy_async();  // the tile writes become visible to the async proxy
     __syncthreads();
@@ -318,6 +388,30 @@ cudaError_t launch_blocks(const RowParams& P, int num_sms, cudaStream_t stream) 
   return cudaGetLastError();
 }
 
+template <int WARPS, int MAXREG>
+cudaError_t launch_blocks_staged(const RowParams& P, int num_sms, cudaStream_t stream) {
+  constexpr size_t smem = kTableBytes + (size_t)WARPS * (kExch * 8 + kStagePx * 4 + 8);
+  auto k = ols_row_rgba_staged_kernel<WARPS, MAXREG>;
+  static PerDevice pd;
+  int device = 0;
+  cudaGetDevice(&device);
+  device &= 63;
+  std::call_once(pd.once[device], [&] {
+    pd.per_sm[device] = 0;
+    pd.err[device] = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (pd.err[device] == cudaSuccess)
+      pd.err[device] = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pd.per_sm[device], k, WARPS * 32, smem);
+    if (pd.err[device] == cudaSuccess && pd.per_sm[device] < 1) pd.err[device] = cudaErrorLaunchOutOfResources;
+  });
+  if (pd.err[device] != cudaSuccess) return pd.err[device];
+  long long grid = (long long)num_sms * pd.per_sm[device];
+  const long long need = ((P.nitems >> 1) + WARPS - 1) / WARPS;
+  if (grid > need) grid = need;
+  k<<<(unsigned)grid, WARPS * 32, smem, stream>>>(P);
+  count_launch();
+  return cudaGetLastError();
+}
+
 }  // namespace
 
 cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t stream) {
@@ -343,6 +437,7 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
   P.blk_np = a.blk.np;
   P.blk_padq = a.blk.padq;
   P.blk_frame_stride = a.blk.frame_stride;
+  P.pair_major = a.blk.pair_major;
   P.qa = p->d_qa;
   P.tw = p->d_tw;
   P.gains = p->d_gains;
@@ -353,19 +448,31 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;
 
-  // warps per CTA / register cap (process-wide tuning knob, read once): 0 = 2 CTAs x 10 warps x 96 registers (default),
-  // 1 = 2 x 8 x 128, 2 = 1 x 16 x 128, 3 = 2 x 12 x 80
+  // kernel variant (process-wide tuning knob, read once). Staged input (default where the rows allow it): 0 = one CTA of
+  // 16 warps x 128 registers, 1 = 2 x 8 x 128, 2 = 1 x 12 x 168. Direct loads: 10 = 2 CTAs x 10 warps x 96 registers
+  // (the fallback), 11 = 2 x 8 x 128, 12 = 1 x 16 x 128
   static const int variant = [] {
     const char* v = getenv("GBLUR_OLS_VARIANT");
     return v ? atoi(v) : 0;
   }();
+  // the staged kernel wants 16-byte aligned rows of whole 4-pixel groups and block counts that fit an int
+  const bool can_stage = (a.in_pitch % 16) == 0 && (reinterpret_cast<uintptr_t>(a.in) % 16) == 0 && (a.T % 4) == 0 &&
+                         P.nitems < (1LL << 31);
+  if (can_stage && variant >= 0 && variant < 10) {
+    switch (variant) {
+      case 1:
+        return launch_blocks_staged<8, 128>(P, num_sms, stream);  // 2 CTAs x 8 warps
+      case 2:
+        return launch_blocks_staged<12, 168>(P, num_sms, stream);
+      default:
+        return launch_blocks_staged<16, 128>(P, num_sms, stream);
+    }
+  }
   switch (variant) {
-    case 1:
+    case 11:
       return launch_blocks<8, 128>(P, num_sms, stream);
-    case 2:
+    case 12:
       return launch_blocks<16, 128>(P, num_sms, stream);
-    case 3:
-      return launch_blocks<12, 80>(P, num_sms, stream);
     default:
       return launch_blocks<10, 96>(P, num_sms, stream);
   }
@@ -373,7 +480,7 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
 
 bool col_eligible(const RowPlan* p, const ColLaunch& a) {
   const int w_end = a.w_end ? a.w_end : a.W;
-  return p && a.C == a.Cp && a.blk.enabled && a.blk.padq == 0 && a.panel_in == 0 && (a.W % kColFloats) == 0 &&
+  return p && a.C == a.Cp && a.blk.enabled && a.blk.padq == 0 && a.blk.pair_major == 1 && a.panel_in == 0 && (a.W % kColFloats) == 0 &&
          (a.w_begin % kColFloats) == 0 && (w_end % kColFloats) == 0 && w_end > a.w_begin &&
          (reinterpret_cast<uintptr_t>(a.out) % 16) == 0 && (a.out_pitch % 16) == 0 && (a.out_frame_stride % 16) == 0 &&
          (reinterpret_cast<uintptr_t>(a.inter) % 128) == 0 && 2 * a.pad + 1 == p->ksize && a.pad <= kMaxPad &&
@@ -456,12 +563,12 @@ cudaError_t launch_col(RowPlan* p, const ColLaunch& a, int num_sms, cudaStream_t
   if (!same) {
     const unsigned long long idims[3] = {32, (unsigned long long)a.blk.np, (unsigned long long)panels_total};
     const unsigned long long istr[2] = {128, (unsigned long long)a.blk.np * 128};
-    const unsigned ibox[3] = {(unsigned)kColFloats, (unsigned)kColBoxSlots, 1};
+    const unsigned ibox[3] = {(unsigned)kColBoxFloats, (unsigned)kColBoxSlots, 1};
     const unsigned long long odims[3] = {(unsigned long long)a.W, (unsigned long long)rows, (unsigned long long)a.frames};
     const unsigned long long ostr[2] = {(unsigned long long)a.out_pitch, (unsigned long long)a.out_frame_stride};
     const unsigned obox_a[3] = {(unsigned)kColFloats, (unsigned)P.st_rows_a, 1};
     const unsigned obox_b[3] = {(unsigned)kColFloats, (unsigned)(P.st_rows_b ? P.st_rows_b : 1), 1};
-    if (!encode_tensor_map(&p->in_map, 4, 3, a.inter, idims, istr, ibox, 64) ||
+    if (!encode_tensor_map(&p->in_map, 4, 3, a.inter, idims, istr, ibox, 32) ||
         !encode_tensor_map(&p->out_a, 1, 3, a.out, odims, ostr, obox_a, 0) ||
         !encode_tensor_map(&p->out_b, 1, 3, a.out, odims, ostr, obox_b, 0)) {
       p->map_inter = nullptr;

@@ -53,13 +53,6 @@ int ols_emulate_rowpass(const uint8_t* in, int rows, int T, float sigma, int ksi
       for (int ch = 0; ch < 4; ++ch) chk[ch] += ols::altsum_weight(x, pad, T) * (int)in[((size_t)r * T + x) * 4 + ch];
     for (int ch = 0; ch < 4; ++ch)
       if (chk[ch] != a[ch]) return -3;
-    // the row-per-CTA kernel's split of the same sums over 2 * nblk warps
-    int b[4] = {0, 0, 0, 0};
-    const int nthreads = 64 * P.nblk;
-    for (int tid = 0; tid < nthreads; ++tid)
-      ols::altsum_part(reinterpret_cast<const uint32_t*>(in + (size_t)r * T * 4), T, pad, tid, nthreads, b);
-    for (int ch = 0; ch < 4; ++ch)
-      if (chk[ch] != b[ch]) return -4;
     qa[(size_t)r] = make_float4(tb.q * (float)a[0], tb.q * (float)a[1], tb.q * (float)a[2], tb.q * (float)a[3]);
   }
   P.qa = qa.data();
@@ -85,7 +78,7 @@ int ols_emulate_rowpass(const uint8_t* in, int rows, int T, float sigma, int ksi
     for (int q = 0; q < 4; ++q) {
       for (int lane = 0; lane < 32; ++lane) dft<ols::kR, false>(regs[lane]);
       if ((q & 1) == 0) {
-        for (int lane = 0; lane < 32; ++lane) ols::tw_write_col(regs[lane], lane, ex, P.tw);
+        for (int lane = 0; lane < 32; ++lane) ols::tw_write_col(regs[lane], lane, ex, P.tw + lane * ols::kTwStride);
         for (int lane = 0; lane < 32; ++lane) ols::read_row(regs[lane], lane, ex);
       } else if (q == 1) {
         for (int lane = 0; lane < 32; ++lane) ols::mid_gains(regs[lane], lane, P.gains);
@@ -113,12 +106,13 @@ int ols_emulate_rowpass(const uint8_t* in, int rows, int T, float sigma, int ksi
 
 }  // extern "C"
 
-// Whole blur through the emulated kernels: row pass into the panel intermediate, column sums -> synthetic row u ->
-// its row pass -> column terms, then the column pass (four warps per quarter panel, 128 emulated threads).
-// in / out: rows x cols RGBA u8. Returns 0 or a negative code.
-template <int CW>
-static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksize, int n_row, int n_col, int padq,
-                        uint8_t* out) {
+// Whole blur through the emulated kernels: row pass into the panel intermediate (no bank-padding holes), column sums
+// -> synthetic row u -> its row pass -> column terms, then the column pass: the four TMA tile loads of an item are
+// emulated as a copy into the landing area under the 64-byte swizzle (col_landing_offset is the kernel's own map of it),
+// the eight warps run the kernel's lane functions, and the TMA tile stores as a clipped copy of the u8 tile.
+// in / out: rows x cols RGBA u8, cols a multiple of 4. Returns 0 or a negative code.
+static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksize, int n_row, int n_col, uint8_t* out) {
+  constexpr int CW = ols::kColWarps;
   const std::vector<float> taps = host::gaussian_taps(sigma, ksize);
   const ols::HostTables tb = ols::build_tables(taps, n_row, n_col);
   const int pad = (ksize - 1) / 2, T = cols;
@@ -132,8 +126,9 @@ static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int 
   P.nblk = (T + P.L - 1) / P.L;
   P.nitems = (long long)rows * P.nblk * 2;
   P.rows_per_frame = rows;
-  P.blk_padq = padq;
-  P.blk_np = ols::phys_slot(rows + 2 * pad, padq) + 5;
+  P.blk_padq = 0;
+  P.pair_major = 1;
+  P.blk_np = rows + 2 * pad + 5;
   const long long panels = ((long long)T * 4 + 31) / 32;
   P.blk_frame_stride = panels * P.blk_np * 32;
   std::vector<float> inter((size_t)P.blk_frame_stride, 0.0f);
@@ -148,20 +143,21 @@ static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int 
   P.qa = qa.data();
   P.tw = tw;
   P.gains = tb.gains.data();
-  std::vector<float4> exbuf((size_t)CW * ols::kExch / 2 + 8);
-  float2* ex_all = reinterpret_cast<float2*>(exbuf.data());
+  std::vector<float4> regionbuf((size_t)ols::kColRegion / 16 + 8);
+  unsigned char* region = reinterpret_cast<unsigned char*>(regionbuf.data());
   static float2 regs[CW][32][ols::kR];
   auto passes = [&](float2 (*rg)[ols::kR], float2* ex) {
     for (int q = 0; q < 4; ++q) {
       for (int lane = 0; lane < 32; ++lane) dft<ols::kR, false>(rg[lane]);
       if ((q & 1) == 0) {
-        for (int lane = 0; lane < 32; ++lane) ols::tw_write_col(rg[lane], lane, ex, tw);
+        for (int lane = 0; lane < 32; ++lane) ols::tw_write_col(rg[lane], lane, ex, tw + lane * ols::kTwStride);
         for (int lane = 0; lane < 32; ++lane) ols::read_row(rg[lane], lane, ex);
       } else if (q == 1) {
         for (int lane = 0; lane < 32; ++lane) ols::mid_gains(rg[lane], lane, P.gains);
       }
     }
   };
+  float2* ex0 = reinterpret_cast<float2*>(region);
   // ---- row pass ----
   for (long long it = 0; it < P.nitems; ++it) {
     const int pair = (int)(it & 1);
@@ -176,7 +172,7 @@ static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int 
       else
         ols::load_block<false>(regs[0][lane], P, row, s, pair, lane);
     }
-    passes(regs[0], ex_all);
+    passes(regs[0], ex0);
     const ols::RowDst d = ols::make_row_dst(P, r);
     const float4 q4 = P.qa[r];
     for (int lane = 0; lane < 32; ++lane)
@@ -200,50 +196,47 @@ static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int 
   for (int it = 0; it < P.nblk * 2; ++it) {
     const int pair = it & 1, s = (it >> 1) * P.L;
     for (int lane = 0; lane < 32; ++lane) ols::load_block_u(regs[0][lane], u.data(), T, pad, s, pair, lane);
-    passes(regs[0], ex_all);
+    passes(regs[0], ex0);
     for (int lane = 0; lane < 32; ++lane)
       ols::store_block_u(regs[0][lane], make_float2(qa_u[2 * pair], qa_u[2 * pair + 1]), tb.q_col, T, pad, P.L, s, pair,
                          lane, qc.data());
   }
   // ---- column pass ----
-  if (T % (CW / 2)) return -10;
-  ols::ColParams C{};
-  C.inter = inter.data();
-  C.panel_stride = (long long)P.blk_np * 32;
-  C.padq = padq;
-  C.T = rows;
-  C.pad = pad;
-  C.L = P.L;
-  C.nblk = (rows + C.L - 1) / C.L;
-  C.nunits = (T + CW / 2 - 1) / (CW / 2);
-  C.nitems = (long long)C.nunits * C.nblk;
-  C.cols = T;
-  C.out = out;
-  C.out_pitch = (long long)T * 4;
-  C.qc = qc.data();
-  C.tw = tw;
-  C.gains = tb.gains.data();
-  std::vector<uint64_t> tilebuf(1024 * CW / 4);
-  uint16_t* tile = reinterpret_cast<uint16_t*>(tilebuf.data());
-  for (long long it = 0; it < C.nitems; ++it) {
-    const int j = (int)(it / C.nunits);
-    const int unit = (int)(it - (long long)j * C.nunits);
-    const int s = j * C.L;
-    for (int t = 0; t < 32 * CW; ++t) ols::col_fetch<CW>(C, unit, s, t, ex_all);
-    for (int w = 0; w < CW; ++w) {
-      float2* ex = ex_all + w * ols::kExch;
-      for (int lane = 0; lane < 32; ++lane) ols::read_col(regs[w][lane], lane, ex);
-      passes(regs[w], ex);
-      for (int lane = 0; lane < 32; ++lane) ols::col_to_tile<CW>(regs[w][lane], C.qc[unit * CW + w], s, w, lane, tile);
+  if ((T * 4) % ols::kColFloats) return -10;
+  const int L = P.L, nblk = (rows + L - 1) / L, nunits = T * 4 / ols::kColFloats;
+  std::vector<uint64_t> tilebuf(ols::kColTileBytes / 8);
+  unsigned char* tile = reinterpret_cast<unsigned char*>(tilebuf.data());
+  for (int j = 0; j < nblk; ++j)
+    for (int unit = 0; unit < nunits; ++unit) {
+      const int s = j * L;
+      // the landing boxes: {8 floats, 256 slots} x 4 per pair, zero beyond the tensor's np slots. Box of pair g starts
+      // at float 16 g + 8 (unit & 1) of the panel row; float 2 k + c of the box is (pixel k of the unit, component c)
+      for (int n = 0; n < ols::kNB; ++n)
+        for (int w = 0; w < CW; ++w)
+          for (int c = 0; c < 2; ++c) {
+            const int slot = s + n, g = w >> 2, k = w & 3;
+            const float v = slot < P.blk_np ? inter[(size_t)(unit >> 1) * P.blk_np * 32 + (size_t)slot * 32 + 16 * g +
+                                                    8 * (unit & 1) + 2 * k + c]
+                                            : 0.0f;
+            std::memcpy(region + ols::col_landing_offset(n, w) + c * 4, &v, 4);
+          }
+      for (int w = 0; w < CW; ++w)
+        for (int lane = 0; lane < 32; ++lane) ols::read_col(regs[w][lane], lane, w, region);
+      std::memset(tile, 0xEE, ols::kColTileBytes);
+      for (int w = 0; w < CW; ++w) {
+        passes(regs[w], reinterpret_cast<float2*>(region) + w * ols::kExch);
+        for (int lane = 0; lane < 32; ++lane)
+          ols::col_to_tile(regs[w][lane], qc[((size_t)unit * 4 + (w & 3)) * 2 + (w >> 2)], s, pad, L, w, lane, tile);
+      }
+      // the tile stores: rows [s, s + L) clipped to the image
+      for (int k = 0; k < L && s + k < rows; ++k)
+        std::memcpy(out + (size_t)(s + k) * T * 4 + (size_t)unit * ols::kColFloats, tile + (size_t)k * ols::kColFloats,
+                    ols::kColFloats);
     }
-    for (int t = 0; t < 32 * CW; ++t) ols::col_store<CW>(C, unit, s, t, tile);
-  }
   return 0;
 }
 
 extern "C" int ols_emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksize, int n_row, int n_col,
-                                int padq, int cw, uint8_t* out) {
-  return cw == 8 ? emulate_blur<8>(in, rows, cols, sigma, ksize, n_row, n_col, padq, out)
-                 : emulate_blur<4>(in, rows, cols, sigma, ksize, n_row, n_col, padq, out);
+                                uint8_t* out) {
+  return emulate_blur(in, rows, cols, sigma, ksize, n_row, n_col, out);
 }
-

@@ -19,7 +19,7 @@ def test_reference_gtest_intents_through_cpp_api(gb, tmp_path):
     exe = tmp_path / "api_intents"
     libdir = os.path.dirname(build.lib_path())
     cmd = ["g++", "-std=c++17", "-O2", "-I", os.path.join(ROOT, "include"), os.path.join(ROOT, "tests", "cpp", "api_intents.cpp"),
-           "-L", libdir, "-lgblur_b200", f"-Wl,-rpath,{libdir}", "-o", str(exe)]
+           "-pthread", "-L", libdir, "-lgblur_b200", f"-Wl,-rpath,{libdir}", "-o", str(exe)]
     r = subprocess.run(cmd, capture_output=True, text=True)
     assert r.returncode == 0, r.stderr[-3000:]
     r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=600)

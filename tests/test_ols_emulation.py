@@ -111,34 +111,32 @@ def emu_blur(emu, tmp_path_factory):
     lib = ctypes.CDLL(str(so))
     lib.ols_emulate_blur.restype = ctypes.c_int
 
-    def run(img, sigma, padq=0, cw=4):
+    def run(img, sigma):
         rows, cols, _ = img.shape
         ksize, pad, n_rp, n_cp, _, _ = go.plan_sizes(rows, cols, sigma)
         img = np.ascontiguousarray(img)
         out = np.empty_like(img)
         rc = lib.ols_emulate_blur(img.ctypes.data_as(ctypes.c_void_p), rows, cols, ctypes.c_float(sigma), ksize, n_rp, n_cp,
-                                  padq, cw, out.ctypes.data_as(ctypes.c_void_p))
+                                  out.ctypes.data_as(ctypes.c_void_p))
         assert rc == 0, rc
         return out
 
     return run
 
 
-@pytest.mark.parametrize("rows,cols,sigma,padq,cw", [
-    (1100, 70, 20.0, 0, 4),     # two column blocks, last one partial
-    (2000, 68, 20.0, 18, 4),    # three column blocks, panel slots with padding holes
-    (300, 130, 5.0, 16, 4),     # one column block, pixel columns that are not a multiple of 8
-    (1900, 170, 50.0, 0, 4),    # pad = 165
-    (895, 66, 20.0, 0, 4),      # one row into a second column block
-    (1100, 72, 20.0, 18, 8),    # eight warps per half panel
-    (300, 132, 5.0, 16, 8),
-    (1900, 172, 50.0, 0, 8),
+@pytest.mark.parametrize("rows,cols,sigma", [
+    (1100, 72, 20.0),     # two column blocks, last one partial
+    (2000, 68, 20.0),     # three column blocks
+    (300, 132, 5.0),      # one column block
+    (1900, 172, 50.0),    # pad = 165
+    (895, 68, 20.0),      # one row into a second column block
+    (1788, 68, 20.0),     # rows == 2 L: the last block ends exactly at the image
 ])
-def test_emulated_two_pass_blur_matches_oracle(emu_blur, rows, cols, sigma, padq, cw):
-    """row pass + column pass (synthetic-row Nyquist term, quarter-panel fetch, shared u8 tile) against the float64
+def test_emulated_two_pass_blur_matches_oracle(emu_blur, rows, cols, sigma):
+    """row pass + column pass (synthetic-row Nyquist term, swizzled TMA landing area, shared u8 tile) against the float64
     oracle of the whole reference call and the compiled reference: max |delta| <= 1 LSB"""
     img = go.synth_u8((rows, cols, 4), 0x77 + rows)
-    out = emu_blur(img, sigma, padq, cw)
+    out = emu_blur(img, sigma)
     want = go.gaussianblur(img, sigma, True)
     assert np.abs(out.astype(int) - want.astype(int)).max() <= 1
     if ref_lib.available():
