@@ -251,11 +251,13 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   float2* ex = reinterpret_cast<float2*>(region) + w * kExch;
 
+  // consecutive items = the blocks of one unit, then the neighbouring unit: the 2 * pad slots two blocks share and the
+  // 128-byte lines two units share are fetched by CTAs that run at the same time (second reader hits L2)
   auto decode = [&](long long it, int& f, int& unit, int& s) {
-    const long long fj = it / P.nunits;
-    unit = P.unit0 + (int)(it - fj * P.nunits);
-    f = (int)(fj / P.nblk);
-    s = (int)(fj - (long long)f * P.nblk) * P.L;
+    const long long fu = it / P.nblk;
+    s = (int)(it - fu * P.nblk) * P.L;
+    f = (int)(fu / P.nunits);
+    unit = P.unit0 + (int)(fu - (long long)f * P.nunits);
   };
   auto request = [&](long long it) {  // one thread: the four landing boxes of item `it`
     int f, unit, s;

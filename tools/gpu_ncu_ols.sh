@@ -7,10 +7,10 @@ tools/ols_gpu_check 4320 7680 20 auto 0 > gpurun_out/plain_ols.log 2>&1 || { cat
 cat gpurun_out/plain_ols.log
 ncu --metrics gpu__time_duration.sum --clock-control none -c 200 --csv --log-file gpurun_out/launches_8k_ols.csv \
     tools/ols_gpu_check 4320 7680 20 auto 0 > gpurun_out/ncu_launches_ols.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:ols_row_rgba_kernel -s 1 -c 1 -f -o gpurun_out/prof_ols_row \
+ncu --set full --clock-control none --import-source on -k regex:ols_row_rgba -s 1 -c 1 -f -o gpurun_out/prof_ols_row \
     tools/ols_gpu_check 4320 7680 20 auto 0 > gpurun_out/ncu_ols_row.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:ols_col_kernel -s 1 -c 1 -f -o gpurun_out/prof_ols_col \
     tools/ols_gpu_check 4320 7680 20 auto 0 > gpurun_out/ncu_ols_col.log 2>&1
-ncu --set full --clock-control none -k regex:'altsum_rows_kernel|colsum_kernel|u_rowpass_kernel' -s 3 -c 3 -f -o gpurun_out/prof_ols_pre \
+ncu --set full --clock-control none -k regex:'altsum_rows_kernel|colsum_kernel|u_rowpass_kernel' -s 6 -c 3 -f -o gpurun_out/prof_ols_pre \
     tools/ols_gpu_check 4320 7680 20 auto 0 > gpurun_out/ncu_ols_pre.log 2>&1
 tail -2 gpurun_out/ncu_ols_*.log; ls -la gpurun_out/
