@@ -39,4 +39,9 @@ void gaussianblur_buffer(uint8_t *hwc, const ImgGeom geometry, const float sigma
 /** CUDA device used by the calls above for the calling thread (default 0). */
 void set_device(int device);
 
+// Additive: how many GPUs gaussianblur_batch (frames sharded, no exchange) and gaussianblur_buffer on gigapixel images
+// (row bands, NVLink peer stores) fan out over — the reference's hybrid_loop fans out over host threads the same way
+// (helpers.hpp:134-172). 0 = default: GBLUR_DEVICES from the environment, else every visible device; 1 = one device.
+void set_device_count(int n);
+
 }  // namespace gaussianblur

@@ -19,6 +19,7 @@
  *   gblur_rowpass_split_device  the same first call, output laid out per destination rank (additive)
  *   gblur_colpass_device     process_channel_tiles, second call src/gaussianblur.cpp:275-279
  *   gblur_dump_intermediate  (test hook) the fp32 plane after pass 1
+ *   gblur_mg_*               hybrid_loop, the reference's in-library fan-out  include/gaussianblur/helpers.hpp:134-172
  */
 #ifndef GBLUR_CAPI_H_
 #define GBLUR_CAPI_H_
@@ -123,6 +124,29 @@ int gblur_colpass_panel_device(gblur_plan* col_plan, const float* d_panel, uint8
  * IPC mapping of the owner's panel buffer (NVLink). Row chunks can travel while the next chunk is computed. */
 int gblur_panel_push_device(const gblur_plan* col_plan, int apply_to_alpha, const float* src_panel, float* dst_panel,
                             int slot_begin, int slot_end, void* cuda_stream);
+
+/* ---- several GPUs of one box behind ONE handle, single process (csrc/multi_gpu.cpp) ----
+ * The reference fans its passes out over std::threads inside the library (include/gaussianblur/helpers.hpp:134-172,
+ * called from src/gaussianblur.cpp:212); these entry points fan out over GPUs the same way, so a C or C++ caller needs
+ * no torch, no NCCL and no second process to use more than one device.
+ *   gblur_mg_create      n_gpus devices (devices == NULL: 0 .. n_gpus-1), peer access enabled between every pair where
+ *                        the hardware allows; geometry and sigma as in gblur_plan_create. Plans are built lazily.
+ *   gblur_mg_run_frames  n_frames contiguous HWC frames in host memory, blurred in place; frames are cut into
+ *                        contiguous blocks, one per GPU, each GPU streams its block (H2D || blur || D2H): no exchange.
+ *   gblur_mg_run_bands   ONE image in host memory, blurred in place. Row bands: every GPU runs the row pass of its
+ *                        band and stores the fp32 intermediate straight into the panel buffer of the GPU owning those
+ *                        pixel columns (NVLink peer stores — the exchange is the row pass's own store), then every GPU
+ *                        runs the column pass of its column band. Needs peer access, cols % n_gpus == 0 and
+ *                        (cols / n_gpus) * Cp % 32 == 0; otherwise the whole image runs on the first device
+ *                        (gblur_mg_info tells which).
+ * One call at a time per handle (calls on one handle serialise); errors: gblur_mg_last_error(). */
+typedef struct gblur_mg gblur_mg;
+int gblur_mg_create(gblur_mg** out, int n_gpus, const int* devices, int rows, int cols, int channels, float sigma);
+void gblur_mg_destroy(gblur_mg* mg);
+int gblur_mg_info(const gblur_mg* mg, int* n_gpus, int* peer_access, int* bands_sharded_alpha0, int* bands_sharded_alpha1);
+int gblur_mg_run_frames(gblur_mg* mg, uint8_t* hwc_frames_inout, int n_frames, int apply_to_alpha);
+int gblur_mg_run_bands(gblur_mg* mg, uint8_t* hwc_inout, int apply_to_alpha);
+const char* gblur_mg_last_error(void);
 
 /* Test hook: fp32 row-pass output of the last gblur_run_* call on this plan (frame 0), copied to
  * host as [rows][cols*Cp]. */

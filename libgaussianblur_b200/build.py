@@ -131,7 +131,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         o = os.path.join(OBJ, f"static_{sid}.o")
         jobs.append((o, [NVCC, *ARCH, *COMMON, f"-DGBLUR_TU_SHAPE={sid}", "-c",
                          os.path.join(CSRC, "static_impl.cu"), "-o", o], os.path.join(CSRC, "static_impl.cu")))
-    for name in ("capi.cpp", "gaussianblur_api.cpp"):
+    for name in ("capi.cpp", "gaussianblur_api.cpp", "multi_gpu.cpp"):
         o = os.path.join(OBJ, name.replace(".cpp", ".o"))
         jobs.append((o, [NVCC, *COMMON, "-c", os.path.join(CSRC, name), "-o", o],
                      os.path.join(CSRC, name)))  # host-only TU
@@ -140,7 +140,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     # they are (stale but ABI-compatible); the stamp is not written, so the next plain build checks everything again
     only = [t for t in os.environ.get("GBLUR_BUILD_ONLY", "").split(",") if t]
     if only:
-        missing = [o for o, _, _ in jobs if not os.path.exists(o)]
+        missing = [o for o, _, _ in jobs if not os.path.exists(o) and os.path.basename(o)[:-2] not in only]
         if missing:
             raise RuntimeError("GBLUR_BUILD_ONLY needs a complete earlier build; missing " + ", ".join(missing))
         all_jobs = jobs

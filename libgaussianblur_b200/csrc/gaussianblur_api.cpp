@@ -9,7 +9,9 @@
 #include <gaussianblur/gaussianblur.h>
 #include <gblur_capi.h>
 
+#include <algorithm>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <iostream>
 #include <list>
@@ -133,9 +135,57 @@ bool valid_request(const ImgGeom &g, float sigma, bool allow_single_channel) {
   return true;
 }
 
+// ---- several GPUs (gblur_mg_*, csrc/multi_gpu.cpp) ----
+// device count the batch / big-image entry points fan out over: GBLUR_DEVICES, else every visible device
+int mg_device_count() {
+  static const int n = [] {
+    if (const char *e = getenv("GBLUR_DEVICES")) return std::max(1, atoi(e));
+    const int v = gblur_device_count();
+    return v > 8 ? 8 : (v < 1 ? 1 : v);
+  }();
+  return n;
+}
+int g_mg_override = 0;  // set_device_count()
+
+struct MgSlot {
+  std::mutex mu;
+  gblur_mg *mg = nullptr;
+  int n = 0;
+  ImgGeom geom{0, 0, 0};
+  uint32_t sigma_bits = 0;
+  ~MgSlot() {
+    if (mg) gblur_mg_destroy(mg);
+  }
+};
+MgSlot &mg_slot() {
+  static MgSlot s;
+  return s;
+}
+// the process-wide multi-GPU handle for this geometry (rebuilt when geometry, sigma or device count change);
+// returns with slot.mu held by `lock`
+gblur_mg *mg_acquire(const ImgGeom &g, float sigma, int n, std::unique_lock<std::mutex> &lock) {
+  MgSlot &s = mg_slot();
+  lock = std::unique_lock<std::mutex>(s.mu);
+  uint32_t bits;
+  std::memcpy(&bits, &sigma, sizeof bits);
+  if (s.mg && (s.n != n || s.geom.rows != g.rows || s.geom.cols != g.cols || s.geom.channels != g.channels || s.sigma_bits != bits)) {
+    gblur_mg_destroy(s.mg);
+    s.mg = nullptr;
+  }
+  if (!s.mg) {
+    if (gblur_mg_create(&s.mg, n, nullptr, g.rows, g.cols, g.channels, sigma) != GBLUR_OK)
+      throw std::runtime_error(std::string("gaussianblur: ") + gblur_mg_last_error());
+    s.n = n;
+    s.geom = g;
+    s.sigma_bits = bits;
+  }
+  return s.mg;
+}
+
 }  // namespace
 
 void set_device(int device) { t_device = device; }
+void set_device_count(int n) { g_mg_override = n < 1 ? 0 : (n > 8 ? 8 : n); }
 
 KernelDFT prepare_kernel_DFT(const ImgGeom image_geometry, const float sigma) {
   KernelDFT k{};
@@ -156,6 +206,16 @@ KernelDFT prepare_kernel_DFT(const ImgGeom image_geometry, const float sigma) {
 
 void gaussianblur_buffer(uint8_t *hwc, const ImgGeom geometry, const float sigma, const bool apply_to_alpha) {
   if (!valid_request(geometry, sigma, true)) return;
+  // an image of a gigapixel-channel or more goes over every device as row bands (gblur_mg_run_bands falls back to one
+  // device by itself when the width does not split)
+  const int n = g_mg_override ? g_mg_override : mg_device_count();
+  if (n > 1 && (size_t)geometry.rows * geometry.cols * geometry.channels >= ((size_t)1 << 30)) {
+    std::unique_lock<std::mutex> lock;
+    gblur_mg *mg = mg_acquire(geometry, sigma, n, lock);
+    if (gblur_mg_run_bands(mg, hwc, apply_to_alpha ? 1 : 0) != GBLUR_OK)
+      throw std::runtime_error(std::string("gaussianblur: ") + gblur_mg_last_error());
+    return;
+  }
   PlanCache::Lease plan(&cache(), cache().checkout(make_key(geometry, sigma, 1)));
   check(gblur_run_host(plan.get(), hwc, apply_to_alpha ? 1 : 0));
 }
@@ -190,6 +250,14 @@ void gaussianblur_batch(uint8_t *frames, const int n_frames, const ImgGeom frame
                         const bool apply_to_alpha) {
   if (n_frames <= 0) return;
   if (!valid_request(frame_geometry, sigma, true)) return;
+  const int n = g_mg_override ? g_mg_override : mg_device_count();
+  if (n > 1 && n_frames >= 2 * n) {  // frames shard over the devices, no exchange (BASELINE.json config 3)
+    std::unique_lock<std::mutex> lock;
+    gblur_mg *mg = mg_acquire(frame_geometry, sigma, n, lock);
+    if (gblur_mg_run_frames(mg, frames, n_frames, apply_to_alpha ? 1 : 0) != GBLUR_OK)
+      throw std::runtime_error(std::string("gaussianblur: ") + gblur_mg_last_error());
+    return;
+  }
   // the plan holds workspace for 16 frames; longer batches are streamed through it (H2D || blur || D2H)
   PlanCache::Lease plan(&cache(), cache().checkout(make_key(frame_geometry, sigma, n_frames < 16 ? n_frames : 16)));
   check(gblur_run_batch_host(plan.get(), frames, n_frames, apply_to_alpha ? 1 : 0));

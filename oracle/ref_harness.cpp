@@ -123,4 +123,49 @@ int ref_rowpass_plane(const uint8_t *hwc, int rows, int cols, int channels, int 
   return 0;
 }
 
+// A strip of ncols pixel columns [c0, c0 + ncols) of the blurred plane of a (rows x cols) single-channel image that
+// may be larger than the reference's own envelope (int rows*cols, src/gaussianblur.cpp:177: BASELINE.json config 5 is
+// 32768 x 65536). Every row and every column is an independent line in the reference (src/gaussianblur.cpp:202-244), so
+// the strip of a hypothetical monolithic run is obtained exactly by
+//   pass 1 in row bands of band_rows rows through process_channel_tiles as gaussianblur::pffft drives it (:268-272),
+//          keeping only the strip's columns of each band's (transposed) result, then
+//   pass 2 on those ncols complete columns (:275-279),
+// with the kernel spectra of the FULL geometry (prepare_kernel_DFT never multiplies rows by cols).
+// plane: rows x cols u8, row-major. out: rows x ncols u8. Returns wall seconds.
+double ref_band_strip_u8(const uint8_t *plane, int rows, int cols, float sigma, int c0, int ncols, int band_rows,
+                         uint8_t *out) {
+  KernelDFT k = gaussianblur::prepare_kernel_DFT(ImgGeom{rows, cols, 1}, sigma);
+  AlignedVector<float> tmp, tile, work;
+  const size_t maxsize = std::max(k.kerf_1D_row.size(), k.kerf_1D_col.size());
+  tmp.reserve(maxsize);
+  tile.reserve(maxsize);
+  work.reserve(maxsize);
+  auto t0 = std::chrono::steady_clock::now();
+  std::vector<float> strip_T((size_t)ncols * rows);  // [column of the strip][row]: the orientation pass 2 reads
+  for (int r0 = 0; r0 < rows; r0 += band_rows) {
+    const int br = std::min(band_rows, rows - r0);
+    const size_t n = (size_t)br * cols;
+    DeinterleavedChs chs(1, std::vector<float>(n));
+    const uint8_t *src = plane + (size_t)r0 * cols;
+    for (size_t i = 0; i < n; ++i) chs[0][i] = src[i];
+    AlignedVector<float> resf(n);
+    gaussianblur::process_channel_tiles(0, br, cols, k.pad, k.trailing_zeros.cols, k.cols_setup.get(), k.kerf_1D_col, tmp,
+                                        tile, work, resf, chs, 1.0F / k.kerf_1D_col.size());
+    // chs[0] is now cols x br (transposed)
+    for (int c = 0; c < ncols; ++c)
+      std::memcpy(&strip_T[(size_t)c * rows + r0], &chs[0][(size_t)(c0 + c) * br], (size_t)br * sizeof(float));
+  }
+  {
+    const size_t n = (size_t)ncols * rows;
+    DeinterleavedChs chs(1, std::move(strip_T));
+    AlignedVector<float> resf(n);
+    gaussianblur::process_channel_tiles(0, ncols, rows, k.pad, k.trailing_zeros.rows, k.rows_setup.get(), k.kerf_1D_row, tmp,
+                                        tile, work, resf, chs, 1.0F / k.kerf_1D_row.size());
+    // chs[0] is rows x ncols again
+    for (size_t i = 0; i < n; ++i) out[i] = (uint8_t)(chs[0][i] + 0.5F);
+  }
+  auto t1 = std::chrono::steady_clock::now();
+  return std::chrono::duration<double>(t1 - t0).count();
+}
+
 }  // extern "C"

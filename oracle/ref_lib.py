@@ -107,6 +107,22 @@ def blur_plane_u8(plane: np.ndarray, sigma: float, return_seconds: bool = False)
     return (p, secs) if return_seconds else p
 
 
+def band_strip_u8(plane: np.ndarray, sigma: float, c0: int, ncols: int, band_rows: int = 1024,
+                  return_seconds: bool = False):
+    """Columns [c0, c0 + ncols) of the blurred plane of a single-channel image that may exceed the reference's own
+    int rows*cols envelope (BASELINE.json config 5): pass 1 in row bands, pass 2 on the strip's columns, both through
+    the reference's process_channel_tiles with the spectra of the full geometry (oracle/ref_harness.cpp)."""
+    import ctypes
+
+    p = np.ascontiguousarray(plane, dtype=np.uint8)
+    rows, cols = p.shape
+    out = np.empty((rows, ncols), dtype=np.uint8)
+    fn = _lib().ref_band_strip_u8
+    fn.restype = ctypes.c_double
+    secs = fn(_u8(p), rows, cols, ctypes.c_float(float(sigma)), int(c0), int(ncols), int(band_rows), _u8(out))
+    return (out, secs) if return_seconds else out
+
+
 def rowpass_plane(img: np.ndarray, ch: int, sigma: float) -> np.ndarray:
     """fp32 row-pass intermediate of channel ch, image orientation (rows x cols)."""
     rows, cols, c = img.shape

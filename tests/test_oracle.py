@@ -82,3 +82,15 @@ def test_invalid_inputs_leave_data_untouched():
     if ref_lib.available():
         assert np.array_equal(ref_lib.gaussianblur(img, 2.0, False), img)
         assert np.array_equal(ref_lib.gaussianblur(img3, -1.0, False), img3)
+
+
+def test_band_strip_oracle_equals_monolithic_reference():
+    """oracle/ref_harness.cpp ref_band_strip_u8 (the config-5 oracle: pass 1 in row bands, pass 2 on a column strip)
+    is bit-identical to the monolithic two-pass route where that one fits the reference's envelope."""
+    if not ref_lib.available():
+        pytest.skip("compiled reference not built")
+    img = go.synth_u8((700, 900), 5)
+    full = ref_lib.blur_plane_u8(img, 6.0)
+    for c0, n, band in ((0, 64, 128), (836, 64, 700), (300, 17, 99)):
+        strip = ref_lib.band_strip_u8(img, 6.0, c0, n, band_rows=band)
+        assert np.array_equal(strip, full[:, c0:c0 + n])

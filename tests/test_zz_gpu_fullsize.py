@@ -110,3 +110,44 @@ def test_single_channel_sigma50_long_lines_vs_reference(gb, refcheck, rows, cols
         assert 34560 in sizes
     mx, nd = _cmp(out, want)
     assert mx <= 1, f"max |delta| = {mx} LSB ({nd} bytes differ), FFT lengths {sizes}"
+
+
+def test_config5_own_geometry_strips_vs_reference(gb, refcheck):
+    """BASELINE.json config 5 at its own size: 32768 rows x 65536 columns x RGB, sigma = 150 (pad 498, row FFT 69120,
+    column FFT 34560), outside the reference's int rows*cols envelope. The oracle is oracle/ref_harness.cpp's
+    ref_band_strip_u8: pass 1 in row bands, pass 2 on a strip of columns, through the reference's own
+    process_channel_tiles (src/gaussianblur.cpp:202-244, driven as :261-280) — bit-identical to the monolithic path where
+    that one exists (tests/test_oracle.py). Two 64-column strips of one channel are compared (left border and interior):
+    every pixel of a strip went through a full-length row transform and a full-length column transform."""
+    import torch
+
+    from oracle import ref_lib
+
+    if not refcheck.have_ref:
+        pytest.skip("oracle/_ref did not travel with the repo")
+    free, _ = torch.cuda.mem_get_info()
+    if free < 60e9:
+        pytest.skip("needs ~45 GB of device memory")
+    rows, cols, sigma = 32768, 65536, 150.0
+    rng = np.random.default_rng(0x1234 + 5)
+    plane = rng.integers(0, 256, size=(rows, cols), dtype=np.uint8)
+    d_plane = torch.from_numpy(plane).cuda()
+    d_in = torch.empty((rows, cols, 3), dtype=torch.uint8, device="cuda")
+    d_in[..., 0] = 255 - d_plane          # the other two channels: different content, same statistics
+    d_in[..., 1] = d_plane                # the channel that is checked
+    d_in[..., 2] = torch.roll(d_plane, 7, 1)
+    del d_plane
+    plan = gb.Plan(rows, cols, 3, sigma)
+    assert (plan.pad, plan.n_rowpass, plan.n_colpass) == (498, 69120, 34560)
+    d_out = torch.empty_like(d_in)
+    plan.run_device(d_in, d_out, False)
+    torch.cuda.synchronize()
+    worst = 0
+    for c0 in (0, 40000):
+        got = d_out[:, c0:c0 + 64, 1].cpu().numpy()
+        want = ref_lib.band_strip_u8(plane, sigma, c0, 64, band_rows=1024)
+        mx, nd = _cmp(got, want)
+        worst = max(worst, mx)
+        assert mx <= 1, f"strip at column {c0}: max |delta| = {mx} LSB ({nd} bytes differ)"
+    plan.close()
+    assert worst <= 1
