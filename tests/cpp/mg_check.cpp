@@ -41,11 +41,14 @@ typedef double (*ref_blur_fn)(uint8_t*, int, int, int, float, int);
 typedef double (*ref_plane_fn)(uint8_t*, int, int, float);
 
 int main(int argc, char** argv) {
+  std::setvbuf(stdout, nullptr, _IOLBF, 0);
   const int n = argc > 1 ? std::atoi(argv[1]) : 2;
   ref_blur_fn ref_blur = nullptr;
   ref_plane_fn ref_plane = nullptr;
   if (argc > 2 && argv[2][0]) {
-    void* h = dlopen(argv[2], RTLD_NOW);
+    // RTLD_DEEPBIND: the reference library and this program's libgblur_b200.so both define gaussianblur::gaussianblur
+    // (the drop-in keeps the reference's symbol names); the checker must bind to its own copy
+    void* h = dlopen(argv[2], RTLD_NOW | RTLD_LOCAL | RTLD_DEEPBIND);
     if (h) {
       ref_blur = (ref_blur_fn)dlsym(h, "ref_gaussianblur");
       ref_plane = (ref_plane_fn)dlsym(h, "ref_blur_plane_u8");
