@@ -148,7 +148,8 @@ BlockedLayout blocked_layout(const gblur_plan* p, int cp, bool ols_col = false) 
   // cluster column plans read the panel through their loader: natural slot order, no padding holes
   b.np = (c.cluster > 1 || ols_col) ? c.N : c.exch_elems;
   b.padq = (c.cluster > 1 || ols_col) ? 0 : c.padq;
-  b.pair_major = ols_col ? 1 : 0;  // written by the overlap-save row pass, read by the overlap-save column pass
+  // RGBA: written by the overlap-save row pass, read by the overlap-save column pass (one channel keeps natural order)
+  b.pair_major = (ols_col && p->channels == 4) ? 1 : 0;
   b.rows_per_frame = p->full_rows;
   const long long panels = ((long long)p->cols * cp + 31) / 32;
   b.frame_stride = panels * b.np * 32;
@@ -207,7 +208,7 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
   if (rc == GBLUR_OK) {
     const char* e = getenv("GBLUR_ROW_OLS");
     p->ols_mode = e ? (atoi(e) > 0 ? 1 : 0) : 2;
-    if (p->ols_mode != 0 && channels == 4 && !band) {
+    if (p->ols_mode != 0 && (channels == 4 || channels == 1) && !band) {
       const char* ec = getenv("GBLUR_COL_OLS");
       p->ols_col_mode = ec ? (atoi(ec) > 0 ? 1 : 0) : kColOlsAuto;
       const cudaError_t ce = ols::row_plan_create(&p->ols_row, taps, sz.n_rowpass, sz.n_colpass);
@@ -227,7 +228,9 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
 // Will the overlap-save column pass (ols.h) take a fused run with `cp` processed channels and `frames` frames? Decided
 // before the row pass, because the panel layout it reads has no bank-padding holes.
 bool ols_col_wanted(const gblur_plan* p, int cp, int frames) {
-  if (!p->ols_row || p->ols_col_mode == 0 || p->band || p->channels != 4 || cp != 4 || frames != 1) return false;
+  if (!p->ols_row || p->ols_col_mode == 0 || p->band || (p->channels != 4 && p->channels != 1) || cp != p->channels ||
+      frames != 1)
+    return false;
   if (((long long)p->cols * cp) % 16 || ((long long)p->full_cols * p->channels) % 16) return false;
   if (p->ols_col_mode == 1) return true;
   // automatic: both passes must gain (the pair-major panel rows tie them together)
@@ -237,8 +240,7 @@ bool ols_col_wanted(const gblur_plan* p, int cp, int frames) {
   RowLaunch r{};
   r.T = p->full_cols;
   r.pad = p->sz.pad;
-  return p->col.lp.cluster == 1 && p->row.lp.cluster == 1 && p->ols_mode != 0 && ols::col_profitable(a, p->sz.n_colpass) &&
-         ols::row_profitable(r, p->sz.n_rowpass);
+  return p->ols_mode != 0 && ols::col_profitable(a, p->sz.n_colpass) && ols::row_profitable(r, p->sz.n_rowpass);
 }
 
 // rows_sub > 0: only rows [row0, row0 + rows_sub) of a single frame (d_in / d_inter still point at row 0)
@@ -270,8 +272,7 @@ int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pi
   if (blk && blk->pair_major && !(p->ols_row && ols::row_eligible(p->ols_row, a)))
     return fail(GBLUR_E_UNSUPPORTED, "pair-major panel layout, but the overlap-save row pass is not eligible");
   if (p->ols_row && ols::row_eligible(p->ols_row, a) &&
-      ((blk && blk->pair_major) || p->ols_mode == 1 ||
-       (fused_single && p->row.lp.cluster == 1 && ols::row_profitable(a, p->sz.n_rowpass)))) {
+      ((blk && blk->pair_major) || p->ols_mode == 1 || (fused_single && ols::row_profitable(a, p->sz.n_rowpass)))) {
     CU(ols::launch_row(p->ols_row, a, p->num_sms, s));
     p->last_row_kind = 1;
     return GBLUR_OK;
@@ -466,7 +467,7 @@ int fused_prepare(gblur_plan* p, int n_frames, int apply_to_alpha, cudaStream_t 
     const char* e = getenv("GBLUR_LAYOUT");
     return e && std::strcmp(e, "panel") == 0;
   }();
-  const bool use_rowmajor = rowmajor || (p->col.lp.cluster > 1 && !panel_forced);
+  const bool use_rowmajor = !ols_col && (rowmajor || (p->col.lp.cluster > 1 && !panel_forced));
   c.bp = use_rowmajor ? nullptr : &c.blk;
   c.pitch = default_pitch((long long)p->cols * c.cp);
   const int layout_tag = use_rowmajor ? -c.cp : (ols_col ? c.cp + 16 : c.cp);
@@ -501,6 +502,8 @@ static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_f
     a.T = p->full_rows;
     a.pad = p->sz.pad;
     a.W = p->cols * c.cp;
+    a.C = p->channels;
+    a.Cp = c.cp;
     CU(cudaEventRecord(p->ev_fork, s));
     CU(cudaStreamWaitEvent(p->s_side, p->ev_fork, 0));
     CU(ols::launch_col_terms(p->ols_row, a, d_in, (long long)p->full_cols * p->channels, p->s_side));

@@ -217,6 +217,109 @@ __device__ __forceinline__ void load_block_staged(float2 (&c)[kR], const RowPara
   }
 }
 
+// ---- one-channel images: a complex sequence carries image rows r (real part) and r + 1 (imaginary part) ----
+// staged copies of both rows' bytes [x_lo, x_lo + kStageC1) (16-byte aligned start)
+constexpr int kStageC1 = kNB + 32;
+__device__ __forceinline__ int stage_x_lo_c1(int s, int pad) { return (s - pad > 0 ? s - pad : 0) & ~15; }
+__device__ __forceinline__ float2 u8x2_to_f32(uint32_t a, uint32_t b) {
+#if defined(__CUDA_ARCH__)
+  return pk_add(make_float2(__uint_as_float(0x4B000000u | a), __uint_as_float(0x4B000000u | b)), pk_bc(-8388608.0f));
+#else
+  return make_float2((float)a, (float)b);
+#endif
+}
+template <bool INTERIOR>
+__device__ __forceinline__ void load_block_staged_c1(float2 (&c)[kR], const RowParams& P, const uint8_t* __restrict__ st0,
+                                                     const uint8_t* __restrict__ st1, int s, int lane) {
+  const int x_lo = stage_x_lo_c1(s, P.pad);
+  if constexpr (INTERIOR) {
+    const int o = s - P.pad - x_lo + lane;
+#pragma unroll
+    for (int i = 0; i < kR; ++i) c[i] = u8x2_to_f32(st0[o + kR * i], st1[o + kR * i]);
+  } else {
+#pragma unroll
+    for (int i = 0; i < kR; ++i) {
+      const int x = reflect_src(s + lane + kR * i, P.pad, P.T);
+      const int o = x < 0 ? 0 : x - x_lo;
+      const float2 v = u8x2_to_f32(st0[o], st1[o]);
+      c[i] = (x < 0) ? make_float2(0.f, 0.f) : v;
+    }
+  }
+}
+
+// lane l, register j hold 1024 (y_r[n] + i y_{r+1}[n]), n = (32 - l) + 32 (31 - j): two scalar stores per sample, one
+// into each row's slot (32 lanes = 128 contiguous bytes of a panel row). second = false: row r + 1 does not exist.
+__device__ __forceinline__ void store_block_c1(const float2 (&c)[kR], const RowParams& P, const RowDst& d0, const RowDst& d1,
+                                               float qa0, float qa1, int s, int lane, bool second) {
+  const int l1 = kR - lane;
+  const float sg = ((s + l1) & 1) ? -1.0f : 1.0f;
+  const float2 add = make_float2(qa0 * sg, qa1 * sg);
+  const int lo = P.pad - l1;
+  const int hi = min(P.pad + P.L, P.T - s + P.pad) - l1;
+  const int x0 = s + l1 - P.pad;  // pixel x = x0 + 32 i: panel (x0 >> 5) + i, float x0 & 31
+  const long long off = (long long)(x0 >> 5) * d0.gstride + (x0 & 31);
+  float* p0 = d0.base + off;
+  float* p1 = d1.base + off;
+#pragma unroll
+  for (int i = 0; i < kR; ++i) {
+    if (kR * i >= lo && kR * i < hi) {
+      const float2 v = pk_add(c[kR - 1 - i], add);
+      *p0 = v.x;
+      if (d0.dl) p0[d0.dl] = v.x;
+      if (d0.dr) p0[d0.dr] = v.x;
+      if (second) {
+        *p1 = v.y;
+        if (d1.dl) p1[d1.dl] = v.y;
+        if (d1.dr) p1[d1.dr] = v.y;
+      }
+    }
+    p0 += d0.gstride;
+    p1 += d0.gstride;
+  }
+  if (P.pad == 0 && lane == 0 && s < P.T) {  // a one-tap window: block index 0 sits at "index 1024" of lane 0
+    const float sg0 = (s & 1) ? -1.0f : 1.0f;
+    const long long o0 = (long long)(s >> 5) * d0.gstride + (s & 31);
+    d0.base[o0] = c[0].x + qa0 * sg0;
+    if (second) d1.base[o0] = c[0].y + qa1 * sg0;
+  }
+}
+
+// one lane's share of a one-channel row's alternating sum: 16 pixels per load; groups without a mirrored pixel are
+// four DP4A with the byte weights (+1, -1, +1, -1)
+__device__ __forceinline__ int altsum_lane_c1(const uint8_t* __restrict__ row, int T, int pad, int lane) {
+  int a = 0;
+  int x_scalar = 0;
+  if ((reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+    const uint4* row4 = reinterpret_cast<const uint4*>(row);
+    const int n16 = T >> 4;
+    for (int g = lane; g < n16; g += 32) {
+      const uint4 v = GBLUR_OLS_LDG(row4 + g);
+      const int x = 16 * g;
+      if (x > pad && x + 15 < T - 1 - pad) {
+        const int sgn = ((pad + x) & 1) ? -1 : 1;
+        int t = 0;
+#if defined(__CUDA_ARCH__)
+        // unsigned pixel bytes times signed weights
+        asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(t) : "r"(v.x), "r"(0xFF01FF01));
+        asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(t) : "r"(v.y), "r"(0xFF01FF01));
+        asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(t) : "r"(v.z), "r"(0xFF01FF01));
+        asm("dp4a.u32.s32 %0, %1, %2, %0;" : "+r"(t) : "r"(v.w), "r"(0xFF01FF01));
+#else
+        const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+        for (int k = 0; k < 16; ++k) t += ((k & 1) ? -1 : 1) * (int)((w4[k >> 2] >> (8 * (k & 3))) & 255u);
+#endif
+        a += sgn * t;
+      } else {
+        const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+        for (int k = 0; k < 16; ++k) a += altsum_weight(x + k, pad, T) * (int)((w4[k >> 2] >> (8 * (k & 3))) & 255u);
+      }
+    }
+    x_scalar = 16 * n16;
+  }
+  for (int x = x_scalar + lane; x < T; x += 32) a += altsum_weight(x, pad, T) * (int)row[x];
+  return a;
+}
+
 // 16 bytes of the twiddle table. On the device this is an ordered (volatile) shared-memory load: left to itself the
 // compiler sinks every table load to its first use, two instructions before the dependent multiply, and the warp then
 // eats the full shared-memory latency sixteen times per exchange (ncu: the hottest short-scoreboard stalls of the kernel)
@@ -401,6 +504,18 @@ __device__ __forceinline__ void read_col(float2 (&c)[kR], int lane, int w, const
   for (int i = 0; i < kR; ++i) c[i] = *reinterpret_cast<const float2*>(p + i * (kR * 32));  // 32 slots further: + 1024 bytes
 }
 
+// Natural column order (any channel count with C == Cp; used for one-channel images): the unit's 16 float columns are
+// 64 contiguous bytes of the panel row, warp w takes floats 2w, 2w + 1, and the landing area holds 1024 slots of 64
+// bytes under the 64-byte TMA swizzle: the 16-byte chunk index (w >> 1) is XORed with bits 7-8 of the offset.
+__device__ __forceinline__ int col_landing_offset_nat(int n, int w) {
+  return n * 64 + ((((w >> 1) ^ (n >> 1)) & 3) << 4) + ((w & 1) << 3);
+}
+__device__ __forceinline__ void read_col_nat(float2 (&c)[kR], int lane, int w, const unsigned char* __restrict__ landing) {
+  const unsigned char* p = landing + col_landing_offset_nat(lane, w);
+#pragma unroll
+  for (int i = 0; i < kR; ++i) c[i] = *reinterpret_cast<const float2*>(p + i * (kR * 64));
+}
+
 // two channels -> two bytes, each uint8_t(v) (truncation: helpers.hpp:251-252,270; the caller has added 0.5), saturated
 __device__ __forceinline__ uint32_t to_u8x2(float2 v) {
 #if defined(__CUDA_ARCH__)
@@ -415,13 +530,14 @@ __device__ __forceinline__ uint32_t to_u8x2(float2 v) {
 }
 
 // lane l, register j hold 1024 y[n], n = (32 - l) + 32 (31 - j): two bytes per output row into tile[n - pad][2w, 2w+1]
-__device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, int s, int pad, int L, int w, int lane,
+// wb: byte offset of the warp's two outputs in the 16-byte tile row (pair-major RGBA: 4 (w & 3) + 2 (w >> 2): pixel
+// w & 3, channels 2g, 2g + 1; natural order: 2 w)
+__device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, int s, int pad, int L, int wb, int lane,
                                             unsigned char* __restrict__ tile) {
   const int l1 = kR - lane;
   const float sg = ((s + l1) & 1) ? -1.0f : 1.0f;
   const float2 add = make_float2(fmaf(qc.x, sg, 0.5f), fmaf(qc.y, sg, 0.5f));
   const int lo = pad - l1, hi = pad + L - l1;
-  const int wb = 4 * (w & 3) + 2 * (w >> 2);  // bytes of pixel k = w & 3, channels 2g, 2g + 1
   unsigned char* tp = tile + (l1 - pad) * kColFloats + wb;
 #pragma unroll
   for (int i = 0; i < kR; ++i) {

@@ -165,6 +165,83 @@ __global__ void __maxnreg__(MAXREG) ols_row_rgba_staged_kernel(const __grid_cons
   }
 }
 
+// ---- one-channel images (BASELINE.json config 4) ----
+__global__ void __launch_bounds__(kAltsumWarps * 32)
+    altsum_rows_c1_kernel(const uint8_t* __restrict__ in, long long in_pitch, int T, int pad, float q, long long rows_total,
+                          float* __restrict__ qa) {
+  const int lane = threadIdx.x & 31;
+  const long long r = (long long)blockIdx.x * kAltsumWarps + (threadIdx.x >> 5);
+  if (r >= rows_total) return;
+  int a = altsum_lane_c1(in + r * in_pitch, T, pad, lane);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+  if (lane == 0) qa[r] = q * (float)a;
+}
+
+// One item = one block of a PAIR of image rows (row r is the real part of the complex sequence, row r + 1 the imaginary
+// part); both rows' bytes are staged by bulk copies one item ahead, as in the RGBA kernel above.
+template <int WARPS, int MAXREG>
+__global__ void __maxnreg__(MAXREG) ols_row_c1_kernel(const __grid_constant__ RowParams P, long long rows_total) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float2* tw = reinterpret_cast<float2*>(smem_raw);
+  float* gains = reinterpret_cast<float*>(tw + kTwSlots);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float2* ex0 = reinterpret_cast<float2*>(gains + kR * kGainStride);
+  float2* ex = ex0 + warp * kExch;
+  uint8_t* stage_all = reinterpret_cast<uint8_t*>(ex0 + WARPS * kExch);
+  uint8_t* st0 = stage_all + warp * (2 * kStageC1);
+  uint8_t* st1 = st0 + kStageC1;
+  uint64_t* bar = reinterpret_cast<uint64_t*>(stage_all + WARPS * (2 * kStageC1)) + warp;
+  load_tables(tw, gains, P.tw, P.gains, threadIdx.x, WARPS * 32);
+  if (lane == 0) {
+    mbar_init(bar, 1);
+    fence_proxy_async();
+  }
+  __syncthreads();
+  const float2* twl = tw + lane * kTwStride;
+  const float* qa = reinterpret_cast<const float*>(P.qa);
+  const long long npairs = (rows_total + 1) >> 1;
+  const long long nitems = npairs * P.nblk;
+  const long long stride = (long long)gridDim.x * WARPS;
+  auto issue = [&](long long b) {  // one lane: the bytes the block reads from both rows, clipped to the row
+    const long long rp = b / P.nblk;
+    const int s = (int)(b - rp * P.nblk) * P.L;
+    const int x_lo = stage_x_lo_c1(s, P.pad);
+    int x_hi = s - P.pad + kNB;
+    x_hi = ((x_hi < P.T ? x_hi : P.T) + 15) & ~15;
+    const uint32_t bytes = (uint32_t)(x_hi - x_lo);
+    const bool second = 2 * rp + 1 < rows_total;
+    mbar_expect_tx(bar, second ? 2 * bytes : bytes);
+    const uint8_t* src = P.in + 2 * rp * P.in_pitch + x_lo;
+    bulk_g2s(st0, src, bytes, bar);
+    if (second) bulk_g2s(st1, src + P.in_pitch, bytes, bar);
+  };
+  long long b = (long long)blockIdx.x * WARPS + warp;
+  if (lane == 0 && b < nitems) issue(b);
+  uint32_t parity = 0;
+  for (; b < nitems; b += stride) {
+    const long long rp = b / P.nblk;
+    const int s = (int)(b - rp * P.nblk) * P.L;
+    const long long r = 2 * rp;
+    const bool second = r + 1 < rows_total;
+    const bool interior = s - P.pad >= 0 && s - P.pad + kNB <= P.T;
+    const float qa0 = __ldg(qa + r), qa1 = second ? __ldg(qa + r + 1) : 0.f;
+    const RowDst d0 = make_row_dst(P, r), d1 = make_row_dst(P, second ? r + 1 : r);
+    mbar_wait(bar, parity);
+    parity ^= 1;
+    float2 c[kR];
+    // without a second row its staging buffer holds stale bytes: the imaginary part is computed and dropped
+    if (interior)
+      load_block_staged_c1<true>(c, P, st0, st1, s, lane);
+    else
+      load_block_staged_c1<false>(c, P, st0, st1, s, lane);
+    __syncwarp();  // every lane has read the staging buffers
+    if (lane == 0 && b + stride < nitems) issue(b + stride);
+    block_passes(c, lane, ex, twl, gains);
+    store_block_c1(c, P, d0, d1, qa0, qa1, s, lane, second);
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // column pass
 // ---------------------------------------------------------------------------------------------------------------
@@ -231,6 +308,55 @@ __global__ void __launch_bounds__(kUWarps * 32, 1)
   }
 }
 
+// One-channel variant: u is ONE real line (u[x], x < T); it rides as the real part of a complex sequence with a zero
+// imaginary part. Writes the column terms V[x] (the block kernel reads them as float2 per column pair).
+__global__ void __launch_bounds__(kUWarps * 32, 1)
+    u_rowpass_c1_kernel(const int* __restrict__ u, int T, int pad, float q_row, float q_col, const float2* __restrict__ g_tw,
+                        const float* __restrict__ g_gains, float* __restrict__ V) {
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  float2* tw = reinterpret_cast<float2*>(smem_raw);
+  float* gains = reinterpret_cast<float*>(tw + kTwSlots);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float2* ex = reinterpret_cast<float2*>(gains + kR * kGainStride) + warp * kExch;
+  __shared__ long long part[kUWarps];
+  __shared__ float qa_u;
+  load_tables(tw, gains, g_tw, g_gains, threadIdx.x, kUWarps * 32);
+  long long a = 0;
+  for (int x = threadIdx.x; x < T; x += kUWarps * 32) a += (long long)altsum_weight(x, pad, T) * (long long)u[x];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+  if (lane == 0) part[warp] = a;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    long long t = 0;
+    for (int w = 0; w < kUWarps; ++w) t += part[w];
+    qa_u = q_row * (float)t;
+  }
+  __syncthreads();
+  const int L = kNB - 2 * pad;
+  const int nblk = (T + L - 1) / L;
+  const float2* twl = tw + lane * kTwStride;
+  for (int j = warp; j < nblk; j += kUWarps) {
+    const int s = j * L;
+    float2 c[kR];
+#pragma unroll
+    for (int i = 0; i < kR; ++i) {
+      const int x = reflect_src(s + lane + kR * i, pad, T);
+      c[i] = make_float2(x < 0 ? 0.f : (float)u[x], 0.f);
+    }
+    block_passes(c, lane, ex, twl, gains);
+    const int l1 = kR - lane;
+    const float sg = ((s + l1) & 1) ? -1.0f : 1.0f;
+    const int hi = min(pad + L, T - s + pad);
+#pragma unroll
+    for (int i = 0; i < kR; ++i) {
+      const int idx = l1 + kR * i;
+      if (idx >= pad && idx < hi) V[s + idx - pad] = q_col * (c[kR - 1 - i].x + qa_u * sg);
+    }
+    if (pad == 0 && lane == 0 && s < T) V[s] = q_col * (c[0].x + qa_u * ((s & 1) ? -1.0f : 1.0f));
+  }
+}
+
 struct ColKernelParams {
   ColParams P;
   CUtensorMap in_map;  // panel intermediate {32 floats, np slots, panels}, box {8, 256, 1}, 32-byte swizzle
@@ -240,6 +366,7 @@ struct ColKernelParams {
 
 constexpr size_t kColSmem = (size_t)kColRegion + kColTileBytes + kTableBytes + 16;
 
+template <bool PAIR_MAJOR>
 __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid_constant__ ColKernelParams K) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* region = smem_raw;                 // landing area (first 64 KB), then the warps' exchange slices
@@ -263,12 +390,19 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
     int f, unit, s;
     decode(it, f, unit, s);
     mbar_expect_tx(bar, kNB * kColFloats * 4);
+    if constexpr (PAIR_MAJOR) {
 #pragma unroll
-    for (int g = 0; g < 2; ++g)
+      for (int g = 0; g < 2; ++g)
+#pragma unroll
+        for (int q = 0; q < kNB / kColBoxSlots; ++q)
+          tma_load_3d(region + g * (kNB * 32) + q * (kColBoxSlots * 32), &K.in_map, g * 16 + (unit & 1) * kColBoxFloats,
+                      s + q * kColBoxSlots, f * P.panels_per_frame + (unit >> 1), bar);
+    } else {
 #pragma unroll
       for (int q = 0; q < kNB / kColBoxSlots; ++q)
-        tma_load_3d(region + g * (kNB * 32) + q * (kColBoxSlots * 32), &K.in_map, g * 16 + (unit & 1) * kColBoxFloats,
-                    s + q * kColBoxSlots, f * P.panels_per_frame + (unit >> 1), bar);
+        tma_load_3d(region + q * (kColBoxSlots * 64), &K.in_map, (unit & 1) * kColFloats, s + q * kColBoxSlots,
+                    f * P.panels_per_frame + (unit >> 1), bar);
+    }
   };
 
   if (tid == 0) {
@@ -287,7 +421,10 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
     mbar_wait(bar, parity);
     parity ^= 1;
     float2 c[kR];
-    read_col(c, lane, w, region);
+    if constexpr (PAIR_MAJOR)
+      read_col(c, lane, w, region);
+    else
+      read_col_nat(c, lane, w, region);
     __syncthreads();  // the landing area is consumed: it becomes the exchange slices
     const long long next = it + gridDim.x;
     block_passes(c, lane, ex, twl, gains, [&] {
@@ -296,8 +433,9 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
       __syncthreads();                    // exchanges done: the region is free, and so is the tile
       if (tid == 0 && next < P.nitems) request(next);  // lands under the last DFT and the epilogue
     });
-    const float2 qc = P.qc ? __ldg(P.qc + f * P.qc_frame_stride + (unit * 4 + (w & 3)) * 2 + (w >> 2)) : make_float2(0.f, 0.f);
-    col_to_tile(c, qc, s, P.pad, P.L, w, lane, tile);
+    const int pairidx = PAIR_MAJOR ? (unit * 4 + (w & 3)) * 2 + (w >> 2) : unit * kColWarps + w;
+    const float2 qc = P.qc ? __ldg(P.qc + f * P.qc_frame_stride + pairidx) : make_float2(0.f, 0.f);
+    col_to_tile(c, qc, s, P.pad, P.L, PAIR_MAJOR ? 4 * (w & 3) + 2 * (w >> 2) : 2 * w, lane, tile);
     fence_proxy_async();  // the tile writes become visible to the async proxy
     __syncthreads();
     if (tid == 0) {
@@ -343,16 +481,23 @@ void row_plan_destroy(RowPlan* p) {
 }
 
 bool row_eligible(const RowPlan* p, const RowLaunch& a) {
-  return p && a.C == 4 && a.Cp == 4 && a.blk.enabled && a.blk.L == 4 && a.npeers == 0 && a.split_cols == 0 &&
-         (a.in_pitch % 4) == 0 && (reinterpret_cast<uintptr_t>(a.in) % 4) == 0 &&
-         (reinterpret_cast<uintptr_t>(a.inter) % 16) == 0 && 2 * a.pad + 1 == p->ksize && a.pad <= kMaxPad &&
-         a.T >= 1 && a.rows_total >= 1;
+  if (!p || !a.blk.enabled || a.npeers != 0 || a.split_cols != 0 || 2 * a.pad + 1 != p->ksize || a.pad > kMaxPad || a.T < 1 ||
+      a.rows_total < 1 || (reinterpret_cast<uintptr_t>(a.inter) % 16) != 0)
+    return false;
+  if (a.C == 4 && a.Cp == 4)
+    return a.blk.L == 4 && (a.in_pitch % 4) == 0 && (reinterpret_cast<uintptr_t>(a.in) % 4) == 0;
+  if (a.C == 1 && a.Cp == 1)  // one channel: staged rows only (16-byte aligned rows of whole 16-pixel groups), natural order
+    return a.blk.pair_major == 0 && (a.in_pitch % 16) == 0 && (reinterpret_cast<uintptr_t>(a.in) % 16) == 0 && (a.T % 16) == 0;
+  return false;
 }
 
 bool row_profitable(const RowLaunch& a, int n_ref) {
   const int L = kNB - 2 * a.pad;
   if (L < 1 || a.T < 4096) return false;
   const long long nblk = (a.T + L - 1) / L;
+  // lines that need a thread-block cluster (n_ref > ~14000 points as two sequences) run at a tenth of the roofline as
+  // whole lines: the blocks win there even when they transform 50 % more points
+  if (n_ref > 14000) return nblk * kNB * 2 <= (long long)n_ref * 3;
   return nblk * kNB * 5 <= (long long)n_ref * 6;
 }
 
@@ -416,6 +561,32 @@ cudaError_t launch_blocks_staged(const RowParams& P, int num_sms, cudaStream_t s
 
 }  // namespace
 
+namespace {
+template <int WARPS, int MAXREG>
+cudaError_t launch_blocks_c1(const RowParams& P, long long rows_total, int num_sms, cudaStream_t stream) {
+  constexpr size_t smem = kTableBytes + (size_t)WARPS * (kExch * 8 + 2 * kStageC1 + 8);
+  auto k = ols_row_c1_kernel<WARPS, MAXREG>;
+  static PerDevice pd;
+  int device = 0;
+  cudaGetDevice(&device);
+  device &= 63;
+  std::call_once(pd.once[device], [&] {
+    pd.per_sm[device] = 0;
+    pd.err[device] = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (pd.err[device] == cudaSuccess)
+      pd.err[device] = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&pd.per_sm[device], k, WARPS * 32, smem);
+    if (pd.err[device] == cudaSuccess && pd.per_sm[device] < 1) pd.err[device] = cudaErrorLaunchOutOfResources;
+  });
+  if (pd.err[device] != cudaSuccess) return pd.err[device];
+  long long grid = (long long)num_sms * pd.per_sm[device];
+  const long long need = (((rows_total + 1) >> 1) * P.nblk + WARPS - 1) / WARPS;
+  if (grid > need) grid = need;
+  k<<<(unsigned)grid, WARPS * 32, smem, stream>>>(P, rows_total);
+  count_launch();
+  return cudaGetLastError();
+}
+}  // namespace
+
 cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t stream) {
   if (p->qa_rows < a.rows_total) {
     if (p->d_qa) cudaFree(p->d_qa);
@@ -445,6 +616,14 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
   P.gains = p->d_gains;
 
   const unsigned nb = (unsigned)((a.rows_total + kAltsumWarps - 1) / kAltsumWarps);
+  if (a.C == 1) {
+    altsum_rows_c1_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total,
+                                                                reinterpret_cast<float*>(p->d_qa));
+    count_launch();
+    const cudaError_t e1 = cudaGetLastError();
+    if (e1 != cudaSuccess) return e1;
+    return launch_blocks_c1<16, 128>(P, a.rows_total, num_sms, stream);
+  }
   altsum_rows_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total, p->d_qa);
   count_launch();
   cudaError_t e = cudaGetLastError();
@@ -482,21 +661,25 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
 
 bool col_eligible(const RowPlan* p, const ColLaunch& a) {
   const int w_end = a.w_end ? a.w_end : a.W;
-  return p && a.C == a.Cp && a.blk.enabled && a.blk.padq == 0 && a.blk.pair_major == 1 && a.panel_in == 0 && (a.W % kColFloats) == 0 &&
+  const bool layout_ok = (a.C == 4 && a.blk.pair_major == 1) || (a.C == 1 && a.blk.pair_major == 0);
+  return p && a.C == a.Cp && layout_ok && a.blk.enabled && a.blk.padq == 0 && (a.W % kColFloats) == 0 &&
          (a.w_begin % kColFloats) == 0 && (w_end % kColFloats) == 0 && w_end > a.w_begin &&
          (reinterpret_cast<uintptr_t>(a.out) % 16) == 0 && (a.out_pitch % 16) == 0 && (a.out_frame_stride % 16) == 0 &&
          (reinterpret_cast<uintptr_t>(a.inter) % 128) == 0 && 2 * a.pad + 1 == p->ksize && a.pad <= kMaxPad &&
-         a.T >= 1 && a.frames == 1 && a.C == 4;  // the column Nyquist terms are built from one RGBA frame so far
+         a.T >= 1 && a.frames == 1;  // the column Nyquist terms are built from one frame so far
 }
 
 bool col_profitable(const ColLaunch& a, int n_ref_col) {
   const int L = kNB - 2 * a.pad;
   if (L < 1 || a.T < 2048) return false;
   const long long nblk = (a.T + L - 1) / L;
+  if (n_ref_col > 14000) return nblk * kNB * 2 <= (long long)n_ref_col * 3;
   return nblk * kNB * 5 <= (long long)n_ref_col * 6;
 }
 
 cudaError_t launch_col_terms(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long long in_pitch, cudaStream_t stream) {
+  // the column sums run over BYTE columns in groups of four (a.W = cols * C bytes per row, a multiple of 16): for RGBA
+  // a group is a pixel, for one channel four pixels — the sums are the same either way
   const int cols = a.W / 4, rows = a.T;
   cudaError_t e;
   if (p->u_cols < cols) {
@@ -525,8 +708,16 @@ cudaError_t launch_col_terms(RowPlan* p, const ColLaunch& a, const uint8_t* d_in
   device &= 63;
   std::call_once(upd.once[device], [&] {
     upd.err[device] = cudaFuncSetAttribute(u_rowpass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)usmem);
+    if (upd.err[device] == cudaSuccess)
+      upd.err[device] = cudaFuncSetAttribute(u_rowpass_c1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)usmem);
   });
   if (upd.err[device] != cudaSuccess) return upd.err[device];
+  if (a.C == 1) {
+    u_rowpass_c1_kernel<<<1, kUWarps * 32, usmem, stream>>>(p->d_u, a.W, a.pad, p->q, p->q_col, p->d_tw, p->d_gains,
+                                                            reinterpret_cast<float*>(p->d_qc));
+    count_launch();
+    return cudaGetLastError();
+  }
   u_rowpass_kernel<<<1, kUWarps * 32, usmem, stream>>>(p->d_u, cols, a.pad, p->q, p->q_col, p->d_tw, p->d_gains, p->d_qc);
   count_launch();
   return cudaGetLastError();
@@ -559,18 +750,19 @@ cudaError_t launch_col(RowPlan* p, const ColLaunch& a, int num_sms, cudaStream_t
   P.gains = p->d_gains;
 
   const long long panels_total = (long long)P.panels_per_frame * a.frames;
-  const long long key[6] = {a.blk.np, panels_total, rows, a.out_pitch, a.out_frame_stride, ((long long)a.frames << 32) | (unsigned)a.W};
+  const long long key[6] = {a.blk.np, panels_total, rows, a.out_pitch, a.out_frame_stride,
+                            ((long long)a.frames << 40) | ((long long)a.blk.pair_major << 36) | (unsigned)a.W};
   bool same = p->map_inter == a.inter && p->map_out == a.out;
   for (int i = 0; i < 6; ++i) same = same && p->map_key[i] == key[i];
   if (!same) {
     const unsigned long long idims[3] = {32, (unsigned long long)a.blk.np, (unsigned long long)panels_total};
     const unsigned long long istr[2] = {128, (unsigned long long)a.blk.np * 128};
-    const unsigned ibox[3] = {(unsigned)kColBoxFloats, (unsigned)kColBoxSlots, 1};
+    const unsigned ibox[3] = {(unsigned)(a.blk.pair_major ? kColBoxFloats : kColFloats), (unsigned)kColBoxSlots, 1};
     const unsigned long long odims[3] = {(unsigned long long)a.W, (unsigned long long)rows, (unsigned long long)a.frames};
     const unsigned long long ostr[2] = {(unsigned long long)a.out_pitch, (unsigned long long)a.out_frame_stride};
     const unsigned obox_a[3] = {(unsigned)kColFloats, (unsigned)P.st_rows_a, 1};
     const unsigned obox_b[3] = {(unsigned)kColFloats, (unsigned)(P.st_rows_b ? P.st_rows_b : 1), 1};
-    if (!encode_tensor_map(&p->in_map, 4, 3, a.inter, idims, istr, ibox, 32) ||
+    if (!encode_tensor_map(&p->in_map, 4, 3, a.inter, idims, istr, ibox, a.blk.pair_major ? 32 : 64) ||
         !encode_tensor_map(&p->out_a, 1, 3, a.out, odims, ostr, obox_a, 0) ||
         !encode_tensor_map(&p->out_b, 1, 3, a.out, odims, ostr, obox_b, 0)) {
       p->map_inter = nullptr;
@@ -586,16 +778,21 @@ cudaError_t launch_col(RowPlan* p, const ColLaunch& a, int num_sms, cudaStream_t
 
   std::call_once(cpd.once[device], [&] {
     cpd.per_sm[device] = 0;
-    cpd.err[device] = cudaFuncSetAttribute(ols_col_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kColSmem);
+    cpd.err[device] = cudaFuncSetAttribute(ols_col_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kColSmem);
+    if (cpd.err[device] == cudaSuccess)
+      cpd.err[device] = cudaFuncSetAttribute(ols_col_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kColSmem);
     if (cpd.err[device] == cudaSuccess)
       cpd.err[device] =
-          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cpd.per_sm[device], ols_col_kernel, kColWarps * 32, kColSmem);
+          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cpd.per_sm[device], ols_col_kernel<true>, kColWarps * 32, kColSmem);
     if (cpd.err[device] == cudaSuccess && cpd.per_sm[device] < 1) cpd.err[device] = cudaErrorLaunchOutOfResources;
   });
   if (cpd.err[device] != cudaSuccess) return cpd.err[device];
   long long grid = (long long)num_sms * cpd.per_sm[device];
   if (grid > P.nitems) grid = P.nitems;
-  ols_col_kernel<<<(unsigned)grid, kColWarps * 32, kColSmem, stream>>>(K);
+  if (a.blk.pair_major)
+    ols_col_kernel<true><<<(unsigned)grid, kColWarps * 32, kColSmem, stream>>>(K);
+  else
+    ols_col_kernel<false><<<(unsigned)grid, kColWarps * 32, kColSmem, stream>>>(K);
   count_launch();
   return cudaGetLastError();
 }
