@@ -125,6 +125,24 @@ int gblur_colpass_panel_device(gblur_plan* col_plan, const float* d_panel, uint8
 int gblur_panel_push_device(const gblur_plan* col_plan, int apply_to_alpha, const float* src_panel, float* dst_panel,
                             int slot_begin, int slot_end, void* cuda_stream);
 
+/* ---- halo sharding: row bands for BOTH passes, no exchange of the fp32 intermediate (third row) ----
+ * The column pass runs as overlap-save blocks (1024 slots, L = 1024 - 2 pad outputs each), so a rank that owns whole
+ * blocks of the padded column needs from the others only `pad` input rows on either side of its band and one integer
+ * per byte column: the weighted column sums behind the reference's Nyquist term (src/gaussianblur.cpp:62-79), which are
+ * summed over the ranks (e.g. ncclAllReduce of cols*channels int32). Every row and column stays an independent line as
+ * in the reference (src/gaussianblur.cpp:202-244). 1 or 4 channels (all blurred), pad <= 256, cols*channels % 16 == 0.
+ *   gblur_halo_partition      rows this rank writes [out_row0, out_row1) and reads [in_row0, in_row1) (host only)
+ *   gblur_plan_create_halo    plan + local panel buffer for that rank
+ *   gblur_halo_colsum_device  adds the rank's own rows into d_u (cols*channels ints, zeroed by the caller)
+ *   gblur_halo_run_device     row pass over rows + halo, column terms from the SUMMED d_u, column blocks -> d_out */
+int gblur_halo_partition(int rows, int cols, float sigma, int n_ranks, int rank, int* out_row0, int* out_row1, int* in_row0,
+                         int* in_row1);
+int gblur_plan_create_halo(gblur_plan** out, int device, int full_rows, int full_cols, int channels, float sigma, int n_ranks,
+                           int rank);
+int gblur_halo_info(const gblur_plan* plan, int* out_row0, int* out_row1, int* in_row0, int* in_row1);
+int gblur_halo_colsum_device(gblur_plan* plan, const uint8_t* d_in_rows, int* d_u, void* cuda_stream);
+int gblur_halo_run_device(gblur_plan* plan, const uint8_t* d_in_rows, const int* d_u_total, uint8_t* d_out, void* cuda_stream);
+
 /* ---- several GPUs of one box behind ONE handle, single process (csrc/multi_gpu.cpp) ----
  * The reference fans its passes out over std::threads inside the library (include/gaussianblur/helpers.hpp:134-172,
  * called from src/gaussianblur.cpp:212); these entry points fan out over GPUs the same way, so a C or C++ caller needs

@@ -81,6 +81,17 @@ def lib():
         "gblur_rowpass_peer_device": (C.c_int, [vp, u8p, C.POINTER(C.c_void_p), C.c_int, C.c_int, C.c_int, vp]),
         "gblur_colpass_panel_device": (C.c_int, [vp, vp, u8p, ll, C.c_int, vp]),
         "gblur_panel_push_device": (C.c_int, [vp, C.c_int, vp, vp, C.c_int, C.c_int, vp]),
+        "gblur_halo_partition": (C.c_int, [C.c_int, C.c_int, C.c_float, C.c_int, C.c_int, ip, ip, ip, ip]),
+        "gblur_plan_create_halo": (C.c_int, [pp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int]),
+        "gblur_halo_info": (C.c_int, [vp, ip, ip, ip, ip]),
+        "gblur_halo_colsum_device": (C.c_int, [vp, u8p, vp, vp]),
+        "gblur_halo_run_device": (C.c_int, [vp, u8p, vp, u8p, vp]),
+        "gblur_mg_create": (C.c_int, [pp, C.c_int, ip, C.c_int, C.c_int, C.c_int, C.c_float]),
+        "gblur_mg_destroy": (None, [vp]),
+        "gblur_mg_info": (C.c_int, [vp, ip, ip, ip, ip]),
+        "gblur_mg_run_frames": (C.c_int, [vp, u8p, C.c_int, C.c_int]),
+        "gblur_mg_run_bands": (C.c_int, [vp, u8p, C.c_int]),
+        "gblur_mg_last_error": (C.c_char_p, []),
         "gblur_dump_intermediate": (C.c_int, [vp, fp, C.c_int]),
         "gblur_launch_count": (C.c_ulonglong, []),
         "gblur_last_error": (C.c_char_p, []),
@@ -285,6 +296,42 @@ class Plan:
         _check(lib().gblur_dump_intermediate(self._h, out.ctypes.data_as(C.POINTER(C.c_float)),
                                              int(bool(apply_to_alpha))))
         return out
+
+
+def halo_partition(rows: int, cols: int, sigma: float, n_ranks: int, rank: int) -> dict:
+    """Rows a rank writes / reads under halo sharding (gblur_halo_partition; host only)."""
+    v = [C.c_int() for _ in range(4)]
+    _check(lib().gblur_halo_partition(rows, cols, sigma, n_ranks, rank, *[C.byref(x) for x in v]))
+    return dict(zip(("out_row0", "out_row1", "in_row0", "in_row1"), (x.value for x in v)))
+
+
+class HaloPlan:
+    """One rank's share of a halo-sharded blur (include/gblur_capi.h: row bands for both passes, overlap-save column
+    blocks; the ranks exchange `pad` input rows and one all-reduce of cols * channels integers)."""
+
+    def __init__(self, rows: int, cols: int, channels: int, sigma: float, n_ranks: int, rank: int, device: int = 0):
+        self._h = C.c_void_p()
+        _check(lib().gblur_plan_create_halo(C.byref(self._h), device, rows, cols, channels, sigma, n_ranks, rank))
+        self.rows, self.cols, self.channels, self.sigma, self.device = rows, cols, channels, float(sigma), device
+        v = [C.c_int() for _ in range(4)]
+        _check(lib().gblur_halo_info(self._h, *[C.byref(x) for x in v]))
+        self.out_row0, self.out_row1, self.in_row0, self.in_row1 = [x.value for x in v]
+        w = [C.c_int() for _ in range(6)]
+        _check(lib().gblur_plan_info(self._h, *[C.byref(x) for x in w]))
+        self.pad = w[1].value
+
+    def colsum(self, d_in_rows, d_u, stream=None):
+        _check(lib().gblur_halo_colsum_device(self._h, _ptr(d_in_rows), _ptr(d_u), _stream_ptr(stream)))
+
+    def run(self, d_in_rows, d_u_total, d_out, stream=None):
+        _check(lib().gblur_halo_run_device(self._h, _ptr(d_in_rows), _ptr(d_u_total), _ptr(d_out), _stream_ptr(stream)))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h.value:
+            lib().gblur_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+    __del__ = close
 
 
 def ipc_export(d_ptr: int) -> bytes:

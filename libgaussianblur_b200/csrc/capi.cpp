@@ -102,6 +102,13 @@ struct gblur_plan {
   // overlap-save column pass, same plan object. GBLUR_COL_OLS: 1 = wherever eligible, 0 = never, unset = kColOlsAuto
   int ols_col_mode = 0;
   int last_row_kind = 0, last_col_kind = 0;  // kernels of the last pass launched: 0 = whole line, 1 = overlap-save
+  // halo-sharded plan (gblur_plan_create_halo): this rank owns the column-pass blocks [blk0, blk1) of the padded column
+  bool halo = false;
+  int h_L = 0, h_blk0 = 0, h_blk1 = 0;
+  int h_out0 = 0, h_out1 = 0;  // image rows this rank writes
+  int h_in0 = 0, h_in1 = 0;    // image rows this rank reads (its own plus the halo of pad rows on either side)
+  int h_np = 0;                // slots of the local panel buffer
+  float* d_halo_panel = nullptr;
 };
 
 namespace {
@@ -386,6 +393,7 @@ void gblur_plan_destroy(gblur_plan* p) {
   free_tables(p->col);
   ols::row_plan_destroy(p->ols_row);
   if (p->d_inter) cudaFree(p->d_inter);
+  if (p->d_halo_panel) cudaFree(p->d_halo_panel);
   if (p->d_stage) cudaFree(p->d_stage);
   if (p->d_stage2) cudaFree(p->d_stage2);
   for (cudaEvent_t e : p->events) cudaEventDestroy(e);
@@ -852,6 +860,148 @@ int gblur_colpass_panel_device(gblur_plan* p, const float* d_panel, uint8_t* d_o
     a.tma_rows = p->tmap_rows;
   }
   CU(launch_colpass(p->col.lp, a, p->num_sms, static_cast<cudaStream_t>(cuda_stream)));
+  return GBLUR_OK;
+}
+
+/* ---- halo sharding: row bands for BOTH passes (third row) ----
+ * With overlap-save column blocks a rank needs nothing from the others but pad input rows on either side of its band
+ * and one integer per byte column (the column sums behind the reference's Nyquist term, src/gaussianblur.cpp:62-79):
+ * it runs the row pass on its rows plus the halo, then the column blocks whose outputs it owns. No fp32 intermediate
+ * crosses a link. Rank boundaries sit on block boundaries (multiples of L = 1024 - 2 pad rows). */
+int gblur_halo_partition(int rows, int cols, float sigma, int n_ranks, int rank, int* out_row0, int* out_row1, int* in_row0,
+                         int* in_row1) {
+  if (rows < 1 || cols < 1 || !(sigma > 0.f) || n_ranks < 1 || rank < 0 || rank >= n_ranks)
+    return fail(GBLUR_E_INVALID, "bad halo partition query");
+  const host::Sizes sz = host::plan_sizes(rows, cols, sigma);
+  const int L = 1024 - 2 * sz.pad;
+  if (L < 512) return fail(GBLUR_E_UNSUPPORTED, "pad %d too wide for 1024-slot blocks", sz.pad);
+  const int nblk = (rows + L - 1) / L;
+  const int q = nblk / n_ranks, r = nblk % n_ranks;
+  const int b0 = rank * q + std::min(rank, r), b1 = b0 + q + (rank < r ? 1 : 0);
+  const int o0 = std::min(rows, b0 * L), o1 = std::min(rows, b1 * L);
+  const int np = (b1 - b0) * L + 2 * sz.pad;
+  if (out_row0) *out_row0 = o0;
+  if (out_row1) *out_row1 = o1;
+  if (in_row0) *in_row0 = b1 > b0 ? std::max(0, b0 * L - sz.pad) : 0;
+  if (in_row1) *in_row1 = b1 > b0 ? std::min(rows, b0 * L + np - sz.pad) : 0;
+  return GBLUR_OK;
+}
+
+int gblur_plan_create_halo(gblur_plan** out, int device, int full_rows, int full_cols, int channels, float sigma, int n_ranks,
+                           int rank) {
+  int o0, o1, i0, i1;
+  int rc = gblur_halo_partition(full_rows, full_cols, sigma, n_ranks, rank, &o0, &o1, &i0, &i1);
+  if (rc != GBLUR_OK) return rc;
+  if (channels != 1 && channels != 4) return fail(GBLUR_E_UNSUPPORTED, "halo sharding: 1 or 4 channels");
+  if (((long long)full_cols * channels) % 16) return fail(GBLUR_E_UNSUPPORTED, "halo sharding: cols * channels must be a multiple of 16");
+  rc = create_common(out, device, full_rows, full_cols, channels, sigma, std::max(1, i1 - i0), full_cols, 1, true);
+  if (rc != GBLUR_OK) return rc;
+  gblur_plan* p = *out;
+  if (!p->ols_row) {
+    const std::vector<float> taps = host::gaussian_taps(sigma, p->sz.ksize);
+    const cudaError_t ce = ols::row_plan_create(&p->ols_row, taps, p->sz.n_rowpass, p->sz.n_colpass);
+    if (ce != cudaSuccess || !p->ols_row) {
+      gblur_plan_destroy(p);
+      *out = nullptr;
+      return fail(GBLUR_E_UNSUPPORTED, "halo sharding needs the overlap-save kernels (pad <= 256)");
+    }
+  }
+  p->halo = true;
+  p->h_L = 1024 - 2 * p->sz.pad;
+  p->h_blk0 = o0 / p->h_L;
+  p->h_blk1 = o1 > o0 ? (o1 + p->h_L - 1) / p->h_L : p->h_blk0;
+  p->h_out0 = o0;
+  p->h_out1 = o1;
+  p->h_in0 = i0;
+  p->h_in1 = i1;
+  p->h_np = (p->h_blk1 - p->h_blk0) * p->h_L + 2 * p->sz.pad;
+  if (o1 > o0) {
+    DeviceGuard guard(device);
+    const long long panels = ((long long)full_cols * channels + 31) / 32;
+    const size_t bytes = (size_t)panels * p->h_np * 32 * sizeof(float);
+    CU(cudaMalloc(&p->d_halo_panel, bytes));
+    CU(cudaMemset(p->d_halo_panel, 0, bytes));  // the zero tail beyond the padded column stays zero for ever
+    CU(cudaDeviceSynchronize());
+  }
+  return GBLUR_OK;
+}
+
+int gblur_halo_info(const gblur_plan* p, int* out_row0, int* out_row1, int* in_row0, int* in_row1) {
+  if (!p || !p->halo) return fail(GBLUR_E_INVALID, "not a halo plan");
+  if (out_row0) *out_row0 = p->h_out0;
+  if (out_row1) *out_row1 = p->h_out1;
+  if (in_row0) *in_row0 = p->h_in0;
+  if (in_row1) *in_row1 = p->h_in1;
+  return GBLUR_OK;
+}
+
+namespace {
+ColLaunch halo_col_launch(const gblur_plan* p, uint8_t* d_out) {
+  ColLaunch a{};
+  const int C = p->channels;
+  const long long panels = ((long long)p->full_cols * C + 31) / 32;
+  a.inter = p->d_halo_panel;
+  a.frames = 1;
+  a.T = p->h_out1 - p->h_out0;
+  a.pad = p->sz.pad;
+  a.W = p->full_cols * C;
+  a.out = d_out;
+  a.out_pitch = (long long)p->full_cols * C;
+  a.out_frame_stride = (long long)std::max(1, a.T) * a.out_pitch;
+  a.C = a.Cp = C;
+  a.blk.enabled = 1;
+  a.blk.L = 4;
+  a.blk.np = p->h_np;
+  a.blk.padq = 0;
+  a.blk.pair_major = C == 4 ? 1 : 0;
+  a.blk.slot_origin = p->h_blk0 * p->h_L;
+  a.blk.rows_per_frame = p->full_rows;
+  a.blk.frame_stride = panels * p->h_np * 32;
+  a.row_origin = p->h_out0;
+  return a;
+}
+}  // namespace
+
+/* d_in_rows: the image rows [in_row0, in_row1) of this rank, HWC u8, pitch cols * channels. d_u: cols * channels ints the
+ * caller zeroed; this rank's OWNED rows are added (integer atomics). Sum d_u over the ranks (all-reduce) before
+ * gblur_halo_run_device. */
+int gblur_halo_colsum_device(gblur_plan* p, const uint8_t* d_in_rows, int* d_u, void* cuda_stream) {
+  if (!p || !p->halo || !d_u) return fail(GBLUR_E_INVALID, "bad halo colsum call");
+  if (p->h_out1 <= p->h_out0) return GBLUR_OK;
+  if (!d_in_rows) return fail(GBLUR_E_INVALID, "null input");
+  DeviceGuard guard(p->device);
+  const ColLaunch a = halo_col_launch(p, nullptr);
+  CU(ols::launch_colsum(a, d_in_rows, (long long)p->full_cols * p->channels, d_u, p->h_out0, p->h_out1, p->h_in0,
+                        p->full_rows, static_cast<cudaStream_t>(cuda_stream)));
+  return GBLUR_OK;
+}
+
+/* Row pass over the rank's rows and halo, column terms from the summed d_u_total, column blocks of the owned rows into
+ * d_out ([out_row1 - out_row0][cols * channels] u8). All channels are blurred (apply_to_alpha semantics: true). */
+int gblur_halo_run_device(gblur_plan* p, const uint8_t* d_in_rows, const int* d_u_total, uint8_t* d_out, void* cuda_stream) {
+  if (!p || !p->halo) return fail(GBLUR_E_INVALID, "not a halo plan");
+  if (p->h_out1 <= p->h_out0) return GBLUR_OK;
+  if (!d_in_rows || !d_u_total || !d_out) return fail(GBLUR_E_INVALID, "null argument");
+  DeviceGuard guard(p->device);
+  cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+  const int C = p->channels;
+  ColLaunch c = halo_col_launch(p, d_out);
+  RowLaunch a{};
+  a.in = d_in_rows;
+  a.in_pitch = (long long)p->full_cols * C;
+  a.C = a.Cp = C;
+  a.T = p->full_cols;
+  a.pad = p->sz.pad;
+  a.rows_total = p->h_in1 - p->h_in0;
+  a.inter = p->d_halo_panel;
+  a.blk = c.blk;
+  a.row_offset = p->h_in0;
+  if (!ols::row_eligible(p->ols_row, a) || !ols::col_eligible(p->ols_row, c))
+    return fail(GBLUR_E_UNSUPPORTED, "halo sharding: geometry not eligible for the overlap-save kernels (alignment)");
+  CU(ols::launch_row(p->ols_row, a, p->num_sms, s));
+  CU(ols::launch_col_terms_from_u(p->ols_row, c, d_u_total, s));
+  CU(ols::launch_col(p->ols_row, c, p->num_sms, s));
+  p->last_row_kind = p->last_col_kind = 1;
   return GBLUR_OK;
 }
 

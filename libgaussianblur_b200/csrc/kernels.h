@@ -36,6 +36,7 @@ struct BlockedLayout {
   int np = 0;                  // slots per unit (column FFT length + bank padding slots)
   int padq = 0;                // column plan's padq
   int pair_major = 0;          // 1: panel rows ordered [pair][pixel][2] (overlap-save row AND column pass, ols_core.cuh)
+  int slot_origin = 0;         // halo-sharded runs: the buffer holds the padded-column slots [slot_origin, slot_origin + np)
   int rows_per_frame = 0;
   long long frame_stride = 0;  // floats per frame = panels * np * 32
 };
@@ -72,6 +73,7 @@ struct ColLaunch {
   int C, Cp;
   BlockedLayout blk;
   int panel_in = 0;  // the column pass of a cluster plan reads the panel layout through its loader
+  int row_origin = 0;  // halo-sharded runs: image row of the first row of `out` (and of slot blk.slot_origin + pad)
   const CUtensorMap* tmap = nullptr;  // host copy of the tensor map over the panel intermediate (TMA gather), or null
   int tma_rows = 0;
 };

@@ -37,6 +37,11 @@ bool col_profitable(const ColLaunch& a, int n_ref_col);
 // The column terms of the reference's Nyquist behaviour, once per image (two launches: column sums of the u8 input =
 // the synthetic row u, then the row pass of u on one CTA). d_in / in_pitch: the image the intermediate comes from.
 cudaError_t launch_col_terms(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long long in_pitch, cudaStream_t stream);
+// The two halves of launch_col_terms for halo-sharded runs: the column sums of image rows [row_begin, row_end) (d_in
+// points at image row row_base; rows = the image's row count) ADDED into d_u, and the terms from a complete d_u.
+cudaError_t launch_colsum(const ColLaunch& a, const uint8_t* d_in, long long in_pitch, int* d_u, int row_begin, int row_end,
+                          int row_base, int rows, cudaStream_t stream);
+cudaError_t launch_col_terms_from_u(RowPlan* p, const ColLaunch& a, const int* d_u, cudaStream_t stream);
 // The block kernel over the float columns [a.w_begin, a.w_end) (TMA tile loads and stores, ols_core.cuh).
 cudaError_t launch_col(RowPlan* p, const ColLaunch& a, int num_sms, cudaStream_t stream);
 

@@ -58,6 +58,7 @@ struct RowParams {
   int row_offset;
   int blk_np, blk_padq;
   int pair_major;          // 1: the 32 floats of a panel row are ordered [pair][pixel][2] instead of [pixel][pair][2]
+  int slot_origin;         // the panel buffer starts at this slot of the padded column (halo-sharded runs), else 0
   long long blk_frame_stride;
   const float4* qa;        // per image row: (K[0] - K[N/2]) / N * alternating sum, one float per channel
   const float2* tw;        // tw[lane * kTwStride + k] = exp(-2 pi i lane k / 1024)
@@ -154,11 +155,16 @@ __device__ __forceinline__ RowDst make_row_dst(const RowParams& P, long long r_g
   const long long f = (r_global + P.row_offset) / P.rows_per_frame;
   const int r = (int)(r_global + P.row_offset - f * P.rows_per_frame);
   const int Tc = P.rows_per_frame, pad = P.pad;
-  const int p1 = phys_slot(pad + r, P.blk_padq);
+  const int p1 = phys_slot(pad + r, P.blk_padq) - P.slot_origin;
   d.base = P.inter + f * P.blk_frame_stride + (long long)p1 * 32;
   d.gstride = (long long)P.blk_np * 32;
-  d.dl = (r >= 1 && r <= pad) ? (phys_slot(pad - r, P.blk_padq) - p1) * 32 : 0;
-  d.dr = (r >= Tc - 1 - pad && r <= Tc - 2) ? (phys_slot(pad + 2 * Tc - 2 - r, P.blk_padq) - p1) * 32 : 0;
+  d.dl = (r >= 1 && r <= pad) ? (phys_slot(pad - r, P.blk_padq) - P.slot_origin - p1) * 32 : 0;
+  d.dr = (r >= Tc - 1 - pad && r <= Tc - 2) ? (phys_slot(pad + 2 * Tc - 2 - r, P.blk_padq) - P.slot_origin - p1) * 32 : 0;
+  if (P.slot_origin) {  // a halo-sharded buffer holds only its own slots: mirrors outside it belong to another rank
+    const int ml = p1 + d.dl / 32, mr = p1 + d.dr / 32;
+    if (ml < 0 || ml >= P.blk_np) d.dl = 0;
+    if (mr < 0 || mr >= P.blk_np) d.dr = 0;
+  }
   return d;
 }
 
@@ -482,6 +488,7 @@ struct ColParams {
   long long nitems;         // frames * nunits * nblk
   int panels_per_frame;
   int st_na, st_rows_a, st_rows_b;  // store boxes: st_na boxes of st_rows_a rows, then one of st_rows_b rows (0 = none)
+  int sign_origin;          // parity offset of the block positions (halo-sharded runs: the buffer's first slot), else 0
   long long qc_frame_stride;        // float2 per frame of qc
   const float2* qc;         // per column pair 2x + pair: (K[0] - K[N/2]) / N of the column length * row pass of u
   const float2* tw;
@@ -532,10 +539,10 @@ __device__ __forceinline__ uint32_t to_u8x2(float2 v) {
 // lane l, register j hold 1024 y[n], n = (32 - l) + 32 (31 - j): two bytes per output row into tile[n - pad][2w, 2w+1]
 // wb: byte offset of the warp's two outputs in the 16-byte tile row (pair-major RGBA: 4 (w & 3) + 2 (w >> 2): pixel
 // w & 3, channels 2g, 2g + 1; natural order: 2 w)
-__device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, int s, int pad, int L, int wb, int lane,
-                                            unsigned char* __restrict__ tile) {
+__device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, int s, int sign_origin, int pad, int L, int wb,
+                                            int lane, unsigned char* __restrict__ tile) {
   const int l1 = kR - lane;
-  const float sg = ((s + l1) & 1) ? -1.0f : 1.0f;
+  const float sg = ((s + sign_origin + l1) & 1) ? -1.0f : 1.0f;
   const float2 add = make_float2(fmaf(qc.x, sg, 0.5f), fmaf(qc.y, sg, 0.5f));
   const int lo = pad - l1, hi = pad + L - l1;
   unsigned char* tp = tile + (l1 - pad) * kColFloats + wb;
@@ -545,7 +552,7 @@ __device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, in
       *reinterpret_cast<uint16_t*>(tp + i * (kR * kColFloats)) = (uint16_t)to_u8x2(pk_add(c[kR - 1 - i], add));
   }
   if (pad == 0 && lane == 0) {
-    const float sg0 = (s & 1) ? -1.0f : 1.0f;
+    const float sg0 = ((s + sign_origin) & 1) ? -1.0f : 1.0f;
     *reinterpret_cast<uint16_t*>(tile + wb) =
         (uint16_t)to_u8x2(make_float2(c[0].x + fmaf(qc.x, sg0, 0.5f), c[0].y + fmaf(qc.y, sg0, 0.5f)));
   }

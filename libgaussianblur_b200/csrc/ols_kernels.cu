@@ -247,14 +247,15 @@ __global__ void __maxnreg__(MAXREG) ols_row_c1_kernel(const __grid_constant__ Ro
 // ---------------------------------------------------------------------------------------------------------------
 constexpr int kColsumRows = 64;  // image rows per thread of the column-sum kernel
 
+// rows [row_begin, row_end) of an image of `rows` rows; `in` points at image row row_base
 __global__ void __launch_bounds__(128) colsum_kernel(const uint8_t* __restrict__ in, long long in_pitch, int cols, int rows,
-                                                     int pad, int* __restrict__ u) {
+                                                     int pad, int* __restrict__ u, int row_begin, int row_end, int row_base) {
   const int x = blockIdx.x * 128 + threadIdx.x;
   if (x >= cols) return;
-  const int r0 = blockIdx.y * kColsumRows;
-  const int r1 = min(rows, r0 + kColsumRows);
+  const int r0 = row_begin + blockIdx.y * kColsumRows;
+  const int r1 = min(row_end, r0 + kColsumRows);
   int a[4] = {0, 0, 0, 0};
-  colsum_lane(in, in_pitch, x, r0, r1, pad, rows, a);
+  colsum_lane(in - (long long)row_base * in_pitch, in_pitch, x, r0, r1, pad, rows, a);
 #pragma unroll
   for (int c = 0; c < 4; ++c) atomicAdd(u + 4 * x + c, a[c]);  // integer atomics: exact, order-independent
 }
@@ -435,7 +436,7 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
     });
     const int pairidx = PAIR_MAJOR ? (unit * 4 + (w & 3)) * 2 + (w >> 2) : unit * kColWarps + w;
     const float2 qc = P.qc ? __ldg(P.qc + f * P.qc_frame_stride + pairidx) : make_float2(0.f, 0.f);
-    col_to_tile(c, qc, s, P.pad, P.L, PAIR_MAJOR ? 4 * (w & 3) + 2 * (w >> 2) : 2 * w, lane, tile);
+    col_to_tile(c, qc, s, P.sign_origin, P.pad, P.L, PAIR_MAJOR ? 4 * (w & 3) + 2 * (w >> 2) : 2 * w, lane, tile);
     fence_proxy_async();  // the tile writes become visible to the async proxy
     __syncthreads();
     if (tid == 0) {
@@ -611,6 +612,7 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
   P.blk_padq = a.blk.padq;
   P.blk_frame_stride = a.blk.frame_stride;
   P.pair_major = a.blk.pair_major;
+  P.slot_origin = a.blk.slot_origin;
   P.qa = p->d_qa;
   P.tw = p->d_tw;
   P.gains = p->d_gains;
@@ -677,30 +679,35 @@ bool col_profitable(const ColLaunch& a, int n_ref_col) {
   return nblk * kNB * 5 <= (long long)n_ref_col * 6;
 }
 
-cudaError_t launch_col_terms(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long long in_pitch, cudaStream_t stream) {
-  // the column sums run over BYTE columns in groups of four (a.W = cols * C bytes per row, a multiple of 16): for RGBA
-  // a group is a pixel, for one channel four pixels — the sums are the same either way
-  const int cols = a.W / 4, rows = a.T;
-  cudaError_t e;
-  if (p->u_cols < cols) {
-    if (p->d_u) cudaFree(p->d_u);
-    if (p->d_qc) cudaFree(p->d_qc);
-    p->d_u = nullptr;
-    p->d_qc = nullptr;
-    p->u_cols = 0;
-    e = cudaMalloc(&p->d_u, (size_t)cols * 4 * sizeof(int));
-    if (e == cudaSuccess) e = cudaMalloc(&p->d_qc, (size_t)cols * 2 * sizeof(float2));
-    if (e != cudaSuccess) return e;
-    p->u_cols = cols;
-  }
-  e = cudaMemsetAsync(p->d_u, 0, (size_t)cols * 4 * sizeof(int), stream);
-  if (e != cudaSuccess) return e;
-  const dim3 cgrid((unsigned)((cols + 127) / 128), (unsigned)((rows + kColsumRows - 1) / kColsumRows));
-  colsum_kernel<<<cgrid, 128, 0, stream>>>(d_in, in_pitch, cols, rows, a.pad, p->d_u);
+cudaError_t launch_colsum(const ColLaunch& a, const uint8_t* d_in, long long in_pitch, int* d_u, int row_begin, int row_end,
+                          int row_base, int rows, cudaStream_t stream) {
+  const int cols = a.W / 4;
+  if (row_end <= row_begin) return cudaSuccess;
+  const dim3 cgrid((unsigned)((cols + 127) / 128), (unsigned)((row_end - row_begin + kColsumRows - 1) / kColsumRows));
+  colsum_kernel<<<cgrid, 128, 0, stream>>>(d_in, in_pitch, cols, rows, a.pad, d_u, row_begin, row_end, row_base);
   count_launch();
-  e = cudaGetLastError();
-  if (e != cudaSuccess) return e;
+  return cudaGetLastError();
+}
 
+namespace {
+cudaError_t ensure_terms_buffers(RowPlan* p, int cols) {
+  if (p->u_cols >= cols) return cudaSuccess;
+  if (p->d_u) cudaFree(p->d_u);
+  if (p->d_qc) cudaFree(p->d_qc);
+  p->d_u = nullptr;
+  p->d_qc = nullptr;
+  p->u_cols = 0;
+  cudaError_t e = cudaMalloc(&p->d_u, (size_t)cols * 4 * sizeof(int));
+  if (e == cudaSuccess) e = cudaMalloc(&p->d_qc, (size_t)cols * 2 * sizeof(float2));
+  if (e != cudaSuccess) return e;
+  p->u_cols = cols;
+  return cudaSuccess;
+}
+}  // namespace
+
+cudaError_t launch_col_terms_from_u(RowPlan* p, const ColLaunch& a, const int* d_u, cudaStream_t stream) {
+  cudaError_t e = ensure_terms_buffers(p, a.W / 4);
+  if (e != cudaSuccess) return e;
   constexpr size_t usmem = kTableBytes + (size_t)kUWarps * kExch * 8;
   static PerDevice upd;
   int device = 0;
@@ -712,15 +719,26 @@ cudaError_t launch_col_terms(RowPlan* p, const ColLaunch& a, const uint8_t* d_in
       upd.err[device] = cudaFuncSetAttribute(u_rowpass_c1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)usmem);
   });
   if (upd.err[device] != cudaSuccess) return upd.err[device];
-  if (a.C == 1) {
-    u_rowpass_c1_kernel<<<1, kUWarps * 32, usmem, stream>>>(p->d_u, a.W, a.pad, p->q, p->q_col, p->d_tw, p->d_gains,
+  if (a.C == 1)
+    u_rowpass_c1_kernel<<<1, kUWarps * 32, usmem, stream>>>(d_u, a.W, a.pad, p->q, p->q_col, p->d_tw, p->d_gains,
                                                             reinterpret_cast<float*>(p->d_qc));
-    count_launch();
-    return cudaGetLastError();
-  }
-  u_rowpass_kernel<<<1, kUWarps * 32, usmem, stream>>>(p->d_u, cols, a.pad, p->q, p->q_col, p->d_tw, p->d_gains, p->d_qc);
+  else
+    u_rowpass_kernel<<<1, kUWarps * 32, usmem, stream>>>(d_u, a.W / 4, a.pad, p->q, p->q_col, p->d_tw, p->d_gains, p->d_qc);
   count_launch();
   return cudaGetLastError();
+}
+
+cudaError_t launch_col_terms(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long long in_pitch, cudaStream_t stream) {
+  // the column sums run over BYTE columns in groups of four (a.W = cols * C bytes per row, a multiple of 16): for RGBA
+  // a group is a pixel, for one channel four pixels — the sums are the same either way
+  const int cols = a.W / 4, rows = a.T;
+  cudaError_t e = ensure_terms_buffers(p, cols);
+  if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(p->d_u, 0, (size_t)cols * 4 * sizeof(int), stream);
+  if (e != cudaSuccess) return e;
+  e = launch_colsum(a, d_in, in_pitch, p->d_u, 0, rows, 0, rows, stream);
+  if (e != cudaSuccess) return e;
+  return launch_col_terms_from_u(p, a, p->d_u, stream);
 }
 
 cudaError_t launch_col(RowPlan* p, const ColLaunch& a, int num_sms, cudaStream_t stream) {
@@ -745,6 +763,7 @@ cudaError_t launch_col(RowPlan* p, const ColLaunch& a, int num_sms, cudaStream_t
   P.st_na = P.L / 256;
   P.st_rows_b = P.L % 256;
   P.qc_frame_stride = 0;
+  P.sign_origin = a.blk.slot_origin;
   P.qc = p->d_qc;
   P.tw = p->d_tw;
   P.gains = p->d_gains;

@@ -226,8 +226,8 @@ static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int 
       for (int w = 0; w < CW; ++w) {
         passes(regs[w], reinterpret_cast<float2*>(region) + w * ols::kExch);
         for (int lane = 0; lane < 32; ++lane)
-          ols::col_to_tile(regs[w][lane], qc[((size_t)unit * 4 + (w & 3)) * 2 + (w >> 2)], s, pad, L, 4 * (w & 3) + 2 * (w >> 2),
-                           lane, tile);
+          ols::col_to_tile(regs[w][lane], qc[((size_t)unit * 4 + (w & 3)) * 2 + (w >> 2)], s, 0, pad, L,
+                           4 * (w & 3) + 2 * (w >> 2), lane, tile);
       }
       // the tile stores: rows [s, s + L) clipped to the image
       for (int k = 0; k < L && s + k < rows; ++k)
