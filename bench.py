@@ -324,6 +324,23 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier, steps=Non
         e2e_step = lambda: plan.run_host(h_pin, alpha)
         h2d = d2h = band.numel()
         closer = plan.close
+    elif args.exchange == "halo":
+        from libgaussianblur_b200.multi import HaloShardedBlur
+
+        bs = HaloShardedBlur.cuda(rows, cols, ch, sigma, device=local)
+        bs.fused_run = None
+        step = lambda: bs.run(band)
+        h_out = torch.empty((max(bs.out_rows[1] - bs.out_rows[0], 1), cols, ch), dtype=torch.uint8).pin_memory() if want_e2e else None
+
+        def e2e_step():
+            d = h_pin.cuda(non_blocking=True)
+            o = bs.run(d)
+            if o.numel():
+                h_out[:o.shape[0]].copy_(o, non_blocking=True)
+            torch.cuda.synchronize()
+
+        h2d, d2h = band.numel(), (h_out.numel() if want_e2e else 0)
+        closer = bs.close
     else:
         bs = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, device=local,
                                   fused=(args.exchange if args.exchange in ("staged", "hybrid") else args.exchange == "fused"),
@@ -338,6 +355,8 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier, steps=Non
 
         h2d, d2h = band.numel(), (h_out.numel() if want_e2e else 0)
         closer = bs.close
+    if not single and args.exchange == "halo" and want_e2e:
+        h2d, d2h = band.numel(), h_out.numel()
     for _ in range(warmup):
         step()
     barrier()
@@ -371,6 +390,8 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier, steps=Non
             bs.profile = False
         phases["exchange"] = bs.exchange_kind
         sent = (r1 - r0) * (cols - cols // world) * ch * 4
+        if args.exchange == "halo":
+            sent = int(bs.exchanged_bytes) + cols * ch * 4  # halo rows sent to the neighbours + the int32 all-reduce
         phases["exchanged_bytes_per_rank"] = sent
         # the exchange hides under the row pass where it can: the honest NVLink figure is the bytes that had to leave
         # this GPU divided by the whole step (a lower bound on the link rate while the exchange was in flight) and,
@@ -412,16 +433,27 @@ def band_check(args, torch, dist, gb, world, rank, local):
 
     rows = cols = 2048
     sigma = 80.0
+    if args.exchange == "halo":  # the overlap-save blocks take pad <= 256: sigma 70 (pad 232), 8 column blocks of 560 rows
+        rows, sigma = 4096, 70.0
     img = synth_u8((rows, cols), 0x77)
     r0, r1 = shard_range(rows, world, rank)
     band = torch.from_numpy(img[r0:r1].copy()).cuda().reshape(r1 - r0, cols, 1)
-    bs = BandShardedBlur.cuda(rows, cols, 1, sigma, False, device=local,
-                              fused=(args.exchange if args.exchange in ("staged", "hybrid") else args.exchange == "fused"),
-                              pipeline_chunks=(args.pipeline_chunks if args.exchange in ("nccl_pipelined", "staged", "hybrid") else 0))
-    out = bs.run(band)
-    torch.cuda.synchronize()
-    c0, c1 = bs.my_cols
-    got = out.cpu().numpy().reshape(rows, c1 - c0)
+    if args.exchange == "halo":
+        from libgaussianblur_b200.multi import HaloShardedBlur
+
+        bs = HaloShardedBlur.cuda(rows, cols, 1, sigma, device=local)
+        out = bs.run(band)
+        torch.cuda.synchronize()
+        o0, o1 = bs.out_rows
+        got_rows = out.cpu().numpy().reshape(max(o1 - o0, 0), cols)
+    else:
+        bs = BandShardedBlur.cuda(rows, cols, 1, sigma, False, device=local,
+                                  fused=(args.exchange if args.exchange in ("staged", "hybrid") else args.exchange == "fused"),
+                                  pipeline_chunks=(args.pipeline_chunks if args.exchange in ("nccl_pipelined", "staged", "hybrid") else 0))
+        out = bs.run(band)
+        torch.cuda.synchronize()
+        c0, c1 = bs.my_cols
+        got = out.cpu().numpy().reshape(rows, c1 - c0)
     kind = bs.exchange_kind
     bs.close()
     if ref_lib.available():
@@ -430,7 +462,10 @@ def band_check(args, torch, dist, gb, world, rank, local):
         from oracle import gblur_oracle as go
 
         want, vs = go.gaussianblur(img, sigma, False), "oracle/gblur_oracle.py"
-    d = np.abs(got.astype(np.int16) - want[:, c0:c1].astype(np.int16))
+    if args.exchange == "halo":
+        d = np.abs(got_rows.astype(np.int16) - want[o0:o1].astype(np.int16)) if o1 > o0 else np.zeros(1, np.int16)
+    else:
+        d = np.abs(got.astype(np.int16) - want[:, c0:c1].astype(np.int16))
     t = torch.tensor([int(d.max()), int(np.count_nonzero(d))], dtype=torch.int64, device="cuda")
     mx = t[:1].clone()
     dist.all_reduce(mx, op=dist.ReduceOp.MAX)
@@ -511,7 +546,7 @@ def main():
     ap.add_argument("--chunk-frames", type=int, default=16, help="frames per launch in the video workload")
     ap.add_argument("--force-band", action="store_true", help="band workloads at 1 GPU: run the band-sharded path anyway")
     ap.add_argument("--pipeline-chunks", type=int, default=8)
-    ap.add_argument("--exchange", default="staged", choices=["fused", "staged", "hybrid", "nccl", "nccl_pipelined"],
+    ap.add_argument("--exchange", default="staged", choices=["fused", "staged", "hybrid", "nccl", "nccl_pipelined", "halo"],
                     help="band workloads: row pass stores into peer memory (fused), local row pass in chunks with "
                          "copy-engine pushes into the owners' panel buffers (staged), or NCCL all-to-all")
     args = ap.parse_args()

@@ -361,6 +361,100 @@ class BandShardedBlur:
             p.close()
 
 
+class HaloShardedBlur:
+    """One image sharded by row bands for BOTH passes (SURVEY.md 8e third row; include/gblur_capi.h gblur_halo_*).
+
+    Rank g holds the input rows [row_ranges[g]) — any contiguous partition — and ends up with the blurred rows
+    [out_rows) of the block-aligned partition the kernels want. Per run it
+      1. gathers the input rows it needs beyond its own (`pad` rows on either side, plus the few rows by which the two
+         partitions differ) from the ranks that hold them: point-to-point u8 copies, a few MB;
+      2. adds the column sums of its output rows into a cols*channels int32 vector and all-reduces it (the reference's
+         Nyquist term along columns needs the alternating sum over the WHOLE column, src/gaussianblur.cpp:62-79);
+      3. runs its row pass and its column blocks locally.
+    The fp32 intermediate never leaves the GPU: about 20x fewer NVLink bytes than the all-to-all of BandShardedBlur.
+    `fetch_rows(lo, hi)` / `colsum` / `run` are injectable so the plumbing is testable on CPU under gloo."""
+
+    def __init__(self, rows: int, cols: int, channels: int, out_rows: Tuple[int, int], in_rows: Tuple[int, int],
+                 colsum: Callable, run: Callable, group=None, row_ranges=None):
+        self.rows, self.cols, self.C = rows, cols, channels
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.row_ranges = row_ranges or shard_ranges(rows, self.world)
+        self.out_rows, self.in_rows = out_rows, in_rows
+        self._colsum, self._run = colsum, run
+        # what every rank needs, known to all (the partition is a pure function of the geometry)
+        need = [None] * self.world
+        if self.world > 1:
+            dist.all_gather_object(need, tuple(in_rows), group=group)
+        else:
+            need = [tuple(in_rows)]
+        self.need = need
+        self.exchanged_bytes = 0
+
+    def _assemble(self, band: torch.Tensor) -> torch.Tensor:
+        """rows [in_rows) of the image on this rank: own rows + pieces received from the ranks that hold the rest"""
+        lo, hi = self.in_rows
+        W = self.cols * self.C
+        my0, my1 = self.row_ranges[self.rank]
+        buf = torch.empty((max(hi - lo, 0), W), dtype=band.dtype, device=band.device)
+        flat = band.reshape(my1 - my0, W)
+        ops, self.exchanged_bytes = [], 0
+        for h in range(self.world):
+            h0, h1 = self.row_ranges[h]
+            # rows rank h needs from me
+            n0, n1 = self.need[h]
+            a, b = max(n0, my0), min(n1, my1)
+            if h != self.rank and a < b:
+                piece = flat[a - my0:b - my0].contiguous()
+                ops.append(dist.P2POp(dist.isend, piece, h if self.group is None else dist.get_global_rank(self.group, h), self.group))
+                self.exchanged_bytes += piece.numel()
+            # rows I need from rank h
+            a, b = max(lo, h0), min(hi, h1)
+            if a < b:
+                if h == self.rank:
+                    buf[a - lo:b - lo].copy_(flat[a - my0:b - my0])
+                else:
+                    ops.append(dist.P2POp(dist.irecv, buf[a - lo:b - lo], h if self.group is None else dist.get_global_rank(self.group, h), self.group))
+        if ops:
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+        return buf
+
+    def run(self, band: torch.Tensor) -> torch.Tensor:
+        """band: this rank's rows [row_ranges[rank]) of the image, u8. Returns the blurred rows [out_rows)."""
+        W = self.cols * self.C
+        rows_in = self._assemble(band)
+        u = torch.zeros(W, dtype=torch.int32, device=band.device)
+        self._colsum(rows_in, u)
+        if self.world > 1:
+            dist.all_reduce(u, group=self.group)
+        out = torch.empty((max(self.out_rows[1] - self.out_rows[0], 0), self.cols, self.C), dtype=band.dtype, device=band.device)
+        self._run(rows_in, u, out)
+        return out
+
+    @classmethod
+    def cuda(cls, rows: int, cols: int, channels: int, sigma: float, device: int = 0, group=None) -> "HaloShardedBlur":
+        import libgaussianblur_b200 as gb
+
+        world = dist.get_world_size(group) if dist.is_initialized() else 1
+        rank = dist.get_rank(group) if dist.is_initialized() else 0
+        plan = gb.HaloPlan(rows, cols, channels, sigma, world, rank, device=device)
+        self = cls(rows, cols, channels, (plan.out_row0, plan.out_row1), (plan.in_row0, plan.in_row1),
+                   colsum=lambda rows_in, u: plan.colsum(rows_in, u) if plan.out_row1 > plan.out_row0 else None,
+                   run=lambda rows_in, u, out: plan.run(rows_in, u, out) if plan.out_row1 > plan.out_row0 else None,
+                   group=group)
+        self.plan = plan
+        self.exchange_kind = ("halo: row bands for both passes, pad input rows from the neighbours + one int32 all-reduce "
+                              "(NCCL), no exchange of the fp32 intermediate")
+        return self
+
+    def close(self):
+        if getattr(self, "plan", None) is not None:
+            self.plan.close()
+            self.plan = None
+
+
 class FrameShardedBlur:
     """A batch of equal-geometry frames sharded by contiguous frame blocks; no collective. Every rank
     builds the same plan once (kernel spectrum and twiddles reused for all its frames)."""

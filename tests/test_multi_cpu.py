@@ -98,3 +98,65 @@ def test_band_sharded_exchange_matches_single_process(world, ch, alpha):
         assert sent == (r1 - r0) * (cols - (c1 - c0)) * cp * 4  # fp32 bytes that left this rank
     assert np.array_equal(by_cols, want)
     assert np.array_equal(by_rows, want)
+
+
+def _halo_worker(rank, world, port, rows, cols, ch, sigma, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        img = go.synth_u8((rows, cols, ch), 0x99)
+        want = go.gaussianblur(img, sigma, True)
+        pad = go.plan_sizes(rows, cols, sigma)[1]
+        # a block-aligned output partition that differs from the input partition (blocks of 7 rows)
+        L = 7
+        nblk = (rows + L - 1) // L
+        b0, b1 = multi.shard_range(nblk, world, rank)
+        out_rows = (min(rows, b0 * L), min(rows, b1 * L))
+        in_rows = (max(0, out_rows[0] - pad), min(rows, out_rows[1] + pad)) if out_rows[1] > out_rows[0] else (0, 0)
+        flat = img.reshape(rows, cols * ch)
+        checks = {}
+
+        def colsum(rows_in, u):  # the rank's OWN output rows of the all-ones weight: a checkable integer all-reduce
+            checks["rows_in_ok"] = bool(np.array_equal(rows_in.numpy(), flat[in_rows[0]:in_rows[1]]))
+            u += torch.from_numpy(flat[out_rows[0]:out_rows[1]].astype(np.int32).sum(axis=0).astype(np.int32))
+
+        def run(rows_in, u, out):
+            checks["u_ok"] = bool(np.array_equal(u.numpy(), flat.astype(np.int64).sum(axis=0).astype(np.int32)))
+            out.copy_(torch.from_numpy(want[out_rows[0]:out_rows[1]].copy()))
+
+        h = multi.HaloShardedBlur(rows, cols, ch, out_rows, in_rows, colsum, run)
+        r0, r1 = h.row_ranges[rank]
+        out = h.run(torch.from_numpy(img[r0:r1].copy()))
+        q.put((rank, out_rows, out.numpy(), checks, h.exchanged_bytes))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,ch", [(2, 1), (3, 4)])
+def test_halo_sharded_plumbing_under_gloo(world, ch):
+    """HaloShardedBlur: every rank assembles exactly the rows it needs (own + halo + partition mismatch) and the column
+    sums are all-reduced; the compute callables are stand-ins bound to the oracle"""
+    rows, cols, sigma = 45, 24, 2.0
+    img = go.synth_u8((rows, cols, ch), 0x99)
+    want = go.gaussianblur(img, sigma, True)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_halo_worker, args=(r, world, port, rows, cols, ch, sigma, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    got = [q.get(timeout=180) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    out = np.zeros_like(img)
+    covered = 0
+    for rank, (o0, o1), o, checks, sent in got:
+        out[o0:o1] = o
+        covered += o1 - o0
+        assert checks.get("rows_in_ok", o1 == o0) and checks.get("u_ok", o1 == o0)
+        assert sent <= (2 * go.plan_sizes(rows, cols, sigma)[1] + 16) * cols * ch  # a halo, not the image
+    assert covered == rows
+    assert np.array_equal(out, want)
