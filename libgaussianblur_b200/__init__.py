@@ -15,6 +15,7 @@ import ctypes as C
 import importlib.util
 import os
 import sys
+import threading
 
 import numpy as np
 
@@ -401,21 +402,68 @@ def gaussianblur(img, sigma: float, apply_to_alpha: bool = False, device: int = 
         return img
     if dev:
         ptr, _, index, stream = dev
-        plan = Plan(shape[0], shape[1], ch, sigma, device=device if index is None else index)
-        try:
-            st = C.c_void_p(int(stream)) if isinstance(stream, int) and stream > 2 else \
-                (C.c_void_p(0) if index is None else _stream_ptr(None))
+        dv = device if index is None else index
+        with _cached_plan(shape[0], shape[1], ch, sigma, dv) as plan:
+            if isinstance(stream, int) and stream > 2:
+                st = C.c_void_p(int(stream))
+            elif index is None:
+                st = C.c_void_p(0)
+            else:  # the current stream of the TENSOR's device, not of whatever device happens to be current
+                import torch
+
+                st = C.c_void_p(torch.cuda.current_stream(dv).cuda_stream)
             _check(lib().gblur_run_batch_device(plan._h, C.c_void_p(ptr), C.c_void_p(ptr), 1,
                                                 int(bool(apply_to_alpha)), st))
-        finally:
-            plan.close()  # plan destruction waits for the work queued on it
         return img
-    plan = Plan(shape[0], shape[1], ch, sigma, device=device)
-    try:
+    with _cached_plan(shape[0], shape[1], ch, sigma, device) as plan:
         plan.run_host(img, apply_to_alpha)
-    finally:
-        plan.close()
     return img
+
+
+# A few plans kept between gaussianblur() calls (the C++ layer keeps its own, csrc/gaussianblur_api.cpp): building one
+# costs table generation, a workspace allocation of the size of the fp32 intermediate and its zero fill — far more
+# than a blur. A plan serves one call at a time (its lock is held for the call); work queued on a caller's stream
+# stays valid because cached plans are not destroyed behind it — eviction synchronises the device first.
+_plan_cache: "dict" = {}
+_plan_cache_lock = threading.Lock()
+_PLAN_CACHE_CAP = 4
+
+
+class _PlanLease:
+    def __init__(self, entry):
+        self.entry = entry
+
+    def __enter__(self):
+        self.entry[1].acquire()
+        return self.entry[0]
+
+    def __exit__(self, *exc):
+        self.entry[1].release()
+        return False
+
+
+def _cached_plan(rows, cols, ch, sigma, device):
+    key = (int(device), int(rows), int(cols), int(ch), float(sigma))
+    with _plan_cache_lock:
+        entry = _plan_cache.pop(key, None)
+        if entry is None:
+            entry = (Plan(rows, cols, ch, sigma, device=device), threading.Lock())
+        _plan_cache[key] = entry  # most recently used last
+        while len(_plan_cache) > _PLAN_CACHE_CAP:
+            old_key = next(iter(_plan_cache))
+            old = _plan_cache[old_key]
+            if not old[1].acquire(blocking=False):
+                break  # in use: keep it for now
+            del _plan_cache[old_key]
+            try:
+                import torch
+
+                torch.cuda.synchronize(old_key[0])  # nothing queued on a caller's stream may still use its workspace
+            except Exception:
+                pass
+            old[0].close()
+            old[1].release()
+    return _PlanLease(entry)
 
 
 def gaussianblur_module():

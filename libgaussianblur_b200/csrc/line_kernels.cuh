@@ -1,6 +1,7 @@
 // line_kernels.cuh — the two kernel templates (runtime-radix and compile-time shape) and the
 // persistent-grid launcher shared by every translation unit that instantiates them.
 #pragma once
+#include <mutex>
 #include <cuda_runtime.h>
 
 #include "async_copy.cuh"
@@ -137,16 +138,26 @@ cudaError_t launch_line(const LinePlan& lp_in, const Params& P, int nthreads, in
   if (P.nunits <= 0) return cudaSuccess;
   LinePlan lp = lp_in;
   lp.smem_bytes += extra_smem;
+  // The dynamic shared-memory limit is ONE attribute per function and device, shared by every host thread: it is set
+  // once, to the device's opt-in maximum, so a thread launching this instantiation with a larger FFT length can never
+  // find it lowered by another thread. Only the occupancy result is cached per thread.
+  static std::once_flag attr_once[64];
+  static cudaError_t attr_err[64];
   static thread_local size_t cached_smem = (size_t)-1;
   static thread_local int cached_threads = -1;
   static thread_local int cached_device = -1;
   static thread_local int cached_per_sm = 0;
   int device = 0;
   cudaGetDevice(&device);
+  std::call_once(attr_once[device & 63], [&] {
+    int optin = 0;
+    attr_err[device & 63] = cudaDeviceGetAttribute(&optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+    if (attr_err[device & 63] == cudaSuccess)
+      attr_err[device & 63] = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, optin);
+  });
+  if (attr_err[device & 63] != cudaSuccess) return attr_err[device & 63];
   if (cached_smem != lp.smem_bytes || cached_threads != nthreads || cached_device != device) {
-    cudaError_t e = cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)(lp.smem_bytes > 48 * 1024 ? lp.smem_bytes : 48 * 1024));
-    if (e != cudaSuccess) return e;
+    cudaError_t e;
     int per_sm = 0;
     e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, nthreads, lp.smem_bytes);
     if (e != cudaSuccess) return e;

@@ -210,7 +210,9 @@ class BandShardedBlur:
             self.plans = (p_row, p_col, *chunk_plans)
             self.exchange_kind = f"NCCL all-to-all in {K} row chunks, pipelined under the row pass"
             return self
-        if fused and (cols * cp) % (32 * world) == 0 and world <= 8:
+        # the panel exchange splits the float columns evenly over the owners: the pixel-column bands must be equal and
+        # start on panel boundaries (cols = 64, world = 3, RGB passes the first test alone and would shift columns)
+        if fused and (cols * cp) % (32 * world) == 0 and cols % world == 0 and ((cols // world) * cp) % 32 == 0 and world <= 8:
             # Fused exchange: every rank's row pass stores its lines straight into the panel buffer of the rank
             # that owns those columns (CUDA IPC mapping of the peers' buffers, NVLink stores). Two tiny
             # all-reduces on the compute stream order the passes across ranks: nobody overwrites a panel that
