@@ -22,7 +22,7 @@ import numpy as np
 from . import build as _build
 
 __all__ = ["Plan", "GblurError", "lib", "gaussianblur", "gaussianblur_module", "host_plan_sizes", "host_spectrum",
-           "host_line_plan", "host_kperm", "host_taps", "launch_count", "EXPORTED_SYMBOLS"]
+           "host_line_plan", "host_kperm", "host_taps", "launch_count", "EXPORTED_SYMBOLS", "HaloPlan", "halo_partition"]
 
 # every symbol include/gblur_capi.h declares
 EXPORTED_SYMBOLS = [
@@ -31,6 +31,8 @@ EXPORTED_SYMBOLS = [
     "gblur_run_device", "gblur_run_batch_device", "gblur_run_stage_device", "gblur_rowpass_device", "gblur_rowpass_split_device", "gblur_colpass_device",
     "gblur_plan_panel_geometry", "gblur_band_panel_alloc", "gblur_ipc_export", "gblur_ipc_open", "gblur_ipc_close",
     "gblur_rowpass_peer_device", "gblur_colpass_panel_device", "gblur_panel_push_device",
+    "gblur_halo_partition", "gblur_plan_create_halo", "gblur_halo_info", "gblur_halo_colsum_device", "gblur_halo_run_device",
+    "gblur_mg_create", "gblur_mg_destroy", "gblur_mg_info", "gblur_mg_run_frames", "gblur_mg_run_bands", "gblur_mg_last_error",
     "gblur_dump_intermediate", "gblur_launch_count", "gblur_last_error", "gblur_device_count",
     "gblur_host_plan_sizes", "gblur_host_taps", "gblur_host_spectrum", "gblur_host_line_plan", "gblur_host_kperm",
 ]
