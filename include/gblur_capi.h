@@ -142,6 +142,10 @@ int gblur_plan_create_halo(gblur_plan** out, int device, int full_rows, int full
 int gblur_halo_info(const gblur_plan* plan, int* out_row0, int* out_row1, int* in_row0, int* in_row1);
 int gblur_halo_colsum_device(gblur_plan* plan, const uint8_t* d_in_rows, int* d_u, void* cuda_stream);
 int gblur_halo_run_device(gblur_plan* plan, const uint8_t* d_in_rows, const int* d_u_total, uint8_t* d_out, void* cuda_stream);
+/* the two halves of gblur_halo_run_device: the row pass of a sub-range of the rank's rows (so it can start on the rows
+ * it holds while the halo is on the link), and column terms + column blocks */
+int gblur_halo_rowpass_device(gblur_plan* plan, const uint8_t* d_in_rows, int row_begin, int row_end, void* cuda_stream);
+int gblur_halo_colpass_device(gblur_plan* plan, const int* d_u_total, uint8_t* d_out, void* cuda_stream);
 
 /* ---- several GPUs of one box behind ONE handle, single process (csrc/multi_gpu.cpp) ----
  * The reference fans its passes out over std::threads inside the library (include/gaussianblur/helpers.hpp:134-172,

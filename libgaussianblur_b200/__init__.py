@@ -32,6 +32,7 @@ EXPORTED_SYMBOLS = [
     "gblur_plan_panel_geometry", "gblur_band_panel_alloc", "gblur_ipc_export", "gblur_ipc_open", "gblur_ipc_close",
     "gblur_rowpass_peer_device", "gblur_colpass_panel_device", "gblur_panel_push_device",
     "gblur_halo_partition", "gblur_plan_create_halo", "gblur_halo_info", "gblur_halo_colsum_device", "gblur_halo_run_device",
+    "gblur_halo_rowpass_device", "gblur_halo_colpass_device",
     "gblur_mg_create", "gblur_mg_destroy", "gblur_mg_info", "gblur_mg_run_frames", "gblur_mg_run_bands", "gblur_mg_last_error",
     "gblur_dump_intermediate", "gblur_launch_count", "gblur_last_error", "gblur_device_count",
     "gblur_host_plan_sizes", "gblur_host_taps", "gblur_host_spectrum", "gblur_host_line_plan", "gblur_host_kperm",
@@ -89,6 +90,8 @@ def lib():
         "gblur_halo_info": (C.c_int, [vp, ip, ip, ip, ip]),
         "gblur_halo_colsum_device": (C.c_int, [vp, u8p, vp, vp]),
         "gblur_halo_run_device": (C.c_int, [vp, u8p, vp, u8p, vp]),
+        "gblur_halo_rowpass_device": (C.c_int, [vp, u8p, C.c_int, C.c_int, vp]),
+        "gblur_halo_colpass_device": (C.c_int, [vp, vp, u8p, vp]),
         "gblur_mg_create": (C.c_int, [pp, C.c_int, ip, C.c_int, C.c_int, C.c_int, C.c_float]),
         "gblur_mg_destroy": (None, [vp]),
         "gblur_mg_info": (C.c_int, [vp, ip, ip, ip, ip]),
@@ -328,6 +331,12 @@ class HaloPlan:
 
     def run(self, d_in_rows, d_u_total, d_out, stream=None):
         _check(lib().gblur_halo_run_device(self._h, _ptr(d_in_rows), _ptr(d_u_total), _ptr(d_out), _stream_ptr(stream)))
+
+    def rowpass(self, d_in_rows, row_begin: int, row_end: int, stream=None):
+        _check(lib().gblur_halo_rowpass_device(self._h, _ptr(d_in_rows), row_begin, row_end, _stream_ptr(stream)))
+
+    def colpass(self, d_u_total, d_out, stream=None):
+        _check(lib().gblur_halo_colpass_device(self._h, _ptr(d_u_total), _ptr(d_out), _stream_ptr(stream)))
 
     def close(self):
         if getattr(self, "_h", None) is not None and self._h.value:

@@ -1145,33 +1145,57 @@ int gblur_halo_colsum_device(gblur_plan* p, const uint8_t* d_in_rows, int* d_u, 
   return GBLUR_OK;
 }
 
-/* Row pass over the rank's rows and halo, column terms from the summed d_u_total, column blocks of the owned rows into
- * d_out ([out_row1 - out_row0][cols * channels] u8). All channels are blurred (apply_to_alpha semantics: true). */
-int gblur_halo_run_device(gblur_plan* p, const uint8_t* d_in_rows, const int* d_u_total, uint8_t* d_out, void* cuda_stream) {
+/* Row pass of the image rows [row_begin, row_end) (a sub-range of [in_row0, in_row1); d_in_rows still points at
+ * in_row0) into the rank's panel buffer. A rank can start on the rows it holds while the halo rows are still on the
+ * link and run them in a second call. */
+int gblur_halo_rowpass_device(gblur_plan* p, const uint8_t* d_in_rows, int row_begin, int row_end, void* cuda_stream) {
   if (!p || !p->halo) return fail(GBLUR_E_INVALID, "not a halo plan");
-  if (p->h_out1 <= p->h_out0) return GBLUR_OK;
-  if (!d_in_rows || !d_u_total || !d_out) return fail(GBLUR_E_INVALID, "null argument");
+  if (p->h_out1 <= p->h_out0 || row_end <= row_begin) return GBLUR_OK;
+  if (!d_in_rows) return fail(GBLUR_E_INVALID, "null argument");
+  if (row_begin < p->h_in0 || row_end > p->h_in1) return fail(GBLUR_E_INVALID, "rows outside [in_row0, in_row1)");
   DeviceGuard guard(p->device);
-  cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
   const int C = p->channels;
-  ColLaunch c = halo_col_launch(p, d_out);
+  const ColLaunch c = halo_col_launch(p, nullptr);
   RowLaunch a{};
-  a.in = d_in_rows;
   a.in_pitch = (long long)p->full_cols * C;
+  a.in = d_in_rows + (long long)(row_begin - p->h_in0) * a.in_pitch;
   a.C = a.Cp = C;
   a.T = p->full_cols;
   a.pad = p->sz.pad;
-  a.rows_total = p->h_in1 - p->h_in0;
+  a.rows_total = row_end - row_begin;
   a.inter = p->d_halo_panel;
   a.blk = c.blk;
-  a.row_offset = p->h_in0;
-  if (!ols::row_eligible(p->ols_row, a) || !ols::col_eligible(p->ols_row, c))
+  a.row_offset = row_begin;
+  if (!ols::row_eligible(p->ols_row, a))
     return fail(GBLUR_E_UNSUPPORTED, "halo sharding: geometry not eligible for the overlap-save kernels (alignment)");
-  CU(ols::launch_row(p->ols_row, a, p->num_sms, s));
+  CU(ols::launch_row(p->ols_row, a, p->num_sms, static_cast<cudaStream_t>(cuda_stream)));
+  p->last_row_kind = 1;
+  return GBLUR_OK;
+}
+
+/* Column terms from the summed d_u_total, then the column blocks of the owned rows into d_out
+ * ([out_row1 - out_row0][cols * channels] u8). */
+int gblur_halo_colpass_device(gblur_plan* p, const int* d_u_total, uint8_t* d_out, void* cuda_stream) {
+  if (!p || !p->halo) return fail(GBLUR_E_INVALID, "not a halo plan");
+  if (p->h_out1 <= p->h_out0) return GBLUR_OK;
+  if (!d_u_total || !d_out) return fail(GBLUR_E_INVALID, "null argument");
+  DeviceGuard guard(p->device);
+  cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
+  const ColLaunch c = halo_col_launch(p, d_out);
+  if (!ols::col_eligible(p->ols_row, c))
+    return fail(GBLUR_E_UNSUPPORTED, "halo sharding: geometry not eligible for the overlap-save kernels (alignment)");
   CU(ols::launch_col_terms_from_u(p->ols_row, c, d_u_total, s));
   CU(ols::launch_col(p->ols_row, c, p->num_sms, s));
-  p->last_row_kind = p->last_col_kind = 1;
+  p->last_col_kind = 1;
   return GBLUR_OK;
+}
+
+/* Both of the above over all of the rank's rows. All channels are blurred (apply_to_alpha semantics: true). */
+int gblur_halo_run_device(gblur_plan* p, const uint8_t* d_in_rows, const int* d_u_total, uint8_t* d_out, void* cuda_stream) {
+  if (!p || !p->halo) return fail(GBLUR_E_INVALID, "not a halo plan");
+  const int rc = gblur_halo_rowpass_device(p, d_in_rows, p->h_in0, p->h_in1, cuda_stream);
+  if (rc != GBLUR_OK) return rc;
+  return gblur_halo_colpass_device(p, d_u_total, d_out, cuda_stream);
 }
 
 int gblur_dump_intermediate(gblur_plan* p, float* host_out, int apply_to_alpha) {

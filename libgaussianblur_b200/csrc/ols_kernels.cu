@@ -260,7 +260,8 @@ __global__ void __launch_bounds__(128) colsum_kernel(const uint8_t* __restrict__
   for (int c = 0; c < 4; ++c) atomicAdd(u + 4 * x + c, a[c]);  // integer atomics: exact, order-independent
 }
 
-// The row pass of the synthetic row: one CTA, kUWarps warps over the nblk * 2 items. Writes the column terms qc.
+// The row pass of the synthetic row: a few CTAs of kUWarps warps over the nblk * 2 items (every CTA forms u's own
+// alternating sum itself: T integers). Writes the column terms qc.
 constexpr int kUWarps = 16;
 
 __global__ void __launch_bounds__(kUWarps * 32, 1)
@@ -300,7 +301,7 @@ __global__ void __launch_bounds__(kUWarps * 32, 1)
   const int L = kNB - 2 * pad;
   const int nitems = ((T + L - 1) / L) * 2;
   const float2* twl = tw + lane * kTwStride;
-  for (int it = warp; it < nitems; it += kUWarps) {
+  for (int it = blockIdx.x * kUWarps + warp; it < nitems; it += gridDim.x * kUWarps) {
     const int pair = it & 1, s = (it >> 1) * L;
     float2 c[kR];
     load_block_u(c, u, T, pad, s, pair, lane);
@@ -337,7 +338,7 @@ __global__ void __launch_bounds__(kUWarps * 32, 1)
   const int L = kNB - 2 * pad;
   const int nblk = (T + L - 1) / L;
   const float2* twl = tw + lane * kTwStride;
-  for (int j = warp; j < nblk; j += kUWarps) {
+  for (int j = blockIdx.x * kUWarps + warp; j < nblk; j += gridDim.x * kUWarps) {
     const int s = j * L;
     float2 c[kR];
 #pragma unroll
@@ -719,11 +720,16 @@ cudaError_t launch_col_terms_from_u(RowPlan* p, const ColLaunch& a, const int* d
       upd.err[device] = cudaFuncSetAttribute(u_rowpass_c1_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)usmem);
   });
   if (upd.err[device] != cudaSuccess) return upd.err[device];
-  if (a.C == 1)
-    u_rowpass_c1_kernel<<<1, kUWarps * 32, usmem, stream>>>(d_u, a.W, a.pad, p->q, p->q_col, p->d_tw, p->d_gains,
-                                                            reinterpret_cast<float*>(p->d_qc));
-  else
-    u_rowpass_kernel<<<1, kUWarps * 32, usmem, stream>>>(d_u, a.W / 4, a.pad, p->q, p->q_col, p->d_tw, p->d_gains, p->d_qc);
+  const int L = kNB - 2 * a.pad;
+  if (a.C == 1) {
+    const int items = (a.W + L - 1) / L;
+    u_rowpass_c1_kernel<<<(items + kUWarps - 1) / kUWarps, kUWarps * 32, usmem, stream>>>(
+        d_u, a.W, a.pad, p->q, p->q_col, p->d_tw, p->d_gains, reinterpret_cast<float*>(p->d_qc));
+  } else {
+    const int items = 2 * ((a.W / 4 + L - 1) / L);
+    u_rowpass_kernel<<<(items + kUWarps - 1) / kUWarps, kUWarps * 32, usmem, stream>>>(d_u, a.W / 4, a.pad, p->q, p->q_col, p->d_tw,
+                                                                                       p->d_gains, p->d_qc);
+  }
   count_launch();
   return cudaGetLastError();
 }

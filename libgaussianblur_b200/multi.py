@@ -435,6 +435,73 @@ class HaloShardedBlur:
         self._run(rows_in, u, out)
         return out
 
+    # ---- the fast path: the input partition IS the output partition (out_ranges), buffers persist ----
+    def own_view(self) -> torch.Tensor:
+        """[out rows, cols, C] view into the persistent input buffer: fill it, then call run_aligned()"""
+        o0, o1 = self.out_rows
+        i0 = self.in_rows[0]
+        return self.buf[o0 - i0:o1 - i0].view(o1 - o0, self.cols, self.C)
+
+    def run_aligned(self) -> torch.Tensor:
+        """The rank's rows [out_rows) are in own_view(). Three streams: the halo rows travel (NCCL send/recv) and the
+        column sums are formed and all-reduced WHILE the row pass of the own rows runs; then the row pass of the halo
+        rows, the column terms and the column blocks. Returns the persistent output buffer."""
+        plan, buf = self.plan, self.buf
+        (o0, o1), (i0, i1) = self.out_rows, self.in_rows
+        main = torch.cuda.current_stream()
+        if o1 <= o0:  # an idle rank still takes part in the collectives
+            with torch.cuda.stream(self.side):
+                self.side.wait_stream(main)
+                self.u.zero_()
+                self._halo_exchange()
+                if self.world > 1:
+                    dist.all_reduce(self.u, group=self.group)
+            main.wait_stream(self.side)
+            return self.out
+        with torch.cuda.stream(self.xs):
+            self.xs.wait_stream(main)
+            self._halo_exchange()
+        with torch.cuda.stream(self.side):
+            self.side.wait_stream(main)
+            self.u.zero_()
+            plan.colsum(buf, self.u, stream=self.side)
+        plan.rowpass(buf, o0, o1)
+        # the all-reduce is enqueued after the send/recv on every rank (one communicator: same order everywhere)
+        with torch.cuda.stream(self.side):
+            self.side.wait_stream(self.xs)
+            if self.world > 1:
+                dist.all_reduce(self.u, group=self.group)
+        main.wait_stream(self.xs)
+        if i0 < o0:
+            plan.rowpass(buf, i0, o0)
+        if o1 < i1:
+            plan.rowpass(buf, o1, i1)
+        main.wait_stream(self.side)
+        plan.colpass(self.u, self.out)
+        return self.out
+
+    def _halo_exchange(self):
+        """pad rows above and below from the ranks that own them (out_ranges partition), into the persistent buffer"""
+        (i0, i1) = self.in_rows
+        my0, my1 = self.out_rows
+        ops, self.exchanged_bytes = [], 0
+        for h in range(self.world):
+            if h == self.rank:
+                continue
+            h0, h1 = self.out_ranges[h]
+            n0, n1 = self.need[h]
+            a, b = max(n0, my0), min(n1, my1)  # rows rank h needs from me
+            peer = h if self.group is None else dist.get_global_rank(self.group, h)
+            if a < b and n1 > n0:
+                ops.append(dist.P2POp(dist.isend, self.buf[a - i0:b - i0], peer, self.group))
+                self.exchanged_bytes += (b - a) * self.cols * self.C
+            a, b = max(i0, h0), min(i1, h1)    # rows I need from rank h
+            if a < b and my1 > my0:
+                ops.append(dist.P2POp(dist.irecv, self.buf[a - i0:b - i0], peer, self.group))
+        if ops:
+            for req in dist.batch_isend_irecv(ops):
+                req.wait()
+
     @classmethod
     def cuda(cls, rows: int, cols: int, channels: int, sigma: float, device: int = 0, group=None) -> "HaloShardedBlur":
         import libgaussianblur_b200 as gb
@@ -447,6 +514,14 @@ class HaloShardedBlur:
                    run=lambda rows_in, u, out: plan.run(rows_in, u, out) if plan.out_row1 > plan.out_row0 else None,
                    group=group)
         self.plan = plan
+        dev = torch.device("cuda", device)
+        parts = [gb.halo_partition(rows, cols, sigma, world, r) for r in range(world)]
+        self.out_ranges = [(q["out_row0"], q["out_row1"]) for q in parts]
+        W = cols * channels
+        self.buf = torch.zeros((max(plan.in_row1 - plan.in_row0, 1), W), dtype=torch.uint8, device=dev)
+        self.out = torch.empty((max(plan.out_row1 - plan.out_row0, 0), cols, channels), dtype=torch.uint8, device=dev)
+        self.u = torch.zeros(W, dtype=torch.int32, device=dev)
+        self.side, self.xs = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
         self.exchange_kind = ("halo: row bands for both passes, pad input rows from the neighbours + one int32 all-reduce "
                               "(NCCL), no exchange of the fp32 intermediate")
         return self
