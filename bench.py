@@ -297,6 +297,22 @@ def bench_video(args, wl, torch, dist, gb, world, rank, local, barrier):
                 nvlink=None)
 
 
+def resolve_exchange(args, gb, rows, cols, ch, sigma, alpha, world):
+    """`--exchange auto` (the default): halo sharding wherever the overlap-save kernels take the geometry (1 channel, or 4
+    with alpha blurred; pad <= 256; a byte row that is a multiple of 16) — measured 1.13 ms against 2.8 ms for the staged
+    exchange on 32768^2 sigma=50 at 8 GPUs (profiles/r02/scale/) because no fp32 intermediate crosses a link — else the
+    staged copy-engine exchange (3 channels, pad > 256: BASELINE.json config 5)."""
+    if args.exchange != "auto":
+        return args.exchange
+    ok = (ch == 1 or (ch == 4 and alpha)) and (cols * ch) % 16 == 0
+    if ok:
+        try:
+            gb.halo_partition(rows, cols, sigma, world, 0)
+        except Exception:
+            ok = False
+    return "halo" if ok else "staged"
+
+
 def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier, steps=None, warmup=None, want_e2e=True):
     """Configs 4/5: one big image. 1 GPU: the fused run. N GPUs: row bands, row pass local, exchange of the fp32
     intermediate over NVLink (peer stores / copy-engine pushes / NCCL all-to-all), column pass local (output stays
@@ -306,6 +322,7 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier, steps=Non
     steps = steps or args.steps
     warmup = max(args.warmup, 3) if warmup is None else warmup
     rows, cols, ch, sigma, alpha = WORKLOADS[wl]
+    exchange = resolve_exchange(args, gb, rows, cols, ch, sigma, alpha, world)
     r0, r1 = shard_range(rows, world, rank)
     gen = torch.Generator(device="cuda")
     gen.manual_seed(0x1234 + 3 + rank)  # uniform u8 generated on the device (the bands are GBs)
@@ -324,7 +341,7 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier, steps=Non
         e2e_step = lambda: plan.run_host(h_pin, alpha)
         h2d = d2h = band.numel()
         closer = plan.close
-    elif args.exchange == "halo":
+    elif exchange == "halo":
         from libgaussianblur_b200.multi import HaloShardedBlur
 
         # the rank holds the rows the partition gives it (block-aligned: gblur_halo_partition), in the persistent buffer
@@ -353,8 +370,8 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier, steps=Non
         closer = bs.close
     else:
         bs = BandShardedBlur.cuda(rows, cols, ch, sigma, alpha, device=local,
-                                  fused=(args.exchange if args.exchange in ("staged", "hybrid") else args.exchange == "fused"),
-                                  pipeline_chunks=(args.pipeline_chunks if args.exchange in ("nccl_pipelined", "staged", "hybrid") else 0))
+                                  fused=(exchange if exchange in ("staged", "hybrid") else exchange == "fused"),
+                                  pipeline_chunks=(args.pipeline_chunks if exchange in ("nccl_pipelined", "staged", "hybrid") else 0))
         step = lambda: bs.run(band)
         h_out = torch.empty((rows, bs.my_cols[1] - bs.my_cols[0], ch), dtype=torch.uint8).pin_memory() if want_e2e else None
 
@@ -390,7 +407,7 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier, steps=Non
             torch.cuda.synchronize()
             phases[name] = k0.elapsed_time(k1) / steps
     else:
-        if bs.fused_run is not None and args.exchange in ("fused", "staged", "hybrid"):
+        if bs.fused_run is not None and exchange in ("fused", "staged", "hybrid"):
             bs.profile = True
             step()
             torch.cuda.synchronize()
@@ -398,7 +415,7 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier, steps=Non
             bs.profile = False
         phases["exchange"] = bs.exchange_kind
         sent = (r1 - r0) * (cols - cols // world) * ch * 4
-        if args.exchange == "halo":
+        if exchange == "halo":
             sent = int(bs.exchanged_bytes) + cols * ch * 4  # halo rows sent to the neighbours + the int32 all-reduce
         phases["exchanged_bytes_per_rank"] = sent
         # the exchange hides under the row pass where it can: the honest NVLink figure is the bytes that had to leave
@@ -427,11 +444,11 @@ def bench_band(args, wl, torch, dist, gb, world, rank, local, barrier, steps=Non
     closer()
     npx_step = rows * cols
     return dict(ms_total=ms * (args.steps / steps), e2e_ms=e2e_ms, npx_step=npx_step, launches=launches, scaling="strong",
-                alg_bytes_step=npx_step * 10 * ch, h2d=h2d, d2h=d2h, details={"exchange": None if single else args.exchange},
+                alg_bytes_step=npx_step * 10 * ch, h2d=h2d, d2h=d2h, details={"exchange": None if single else exchange},
                 phases_ms=phases, parity_check=None, nvlink=nvlink, ms_per_step=ms / steps)
 
 
-def band_check(args, torch, dist, gb, world, rank, local):
+def band_check(args, torch, dist, gb, world, rank, local, force=None):
     """Multi-GPU self-check (the driver's test box has one GPU): a 2048 x 2048 one-channel image, sigma = 80
     (pad = 265 > the 256-row bands of 8 ranks, so the mirrored border rows cross rank boundaries), band-sharded with
     the same exchange as the band workloads, every rank's column band against the compiled reference."""
@@ -441,12 +458,13 @@ def band_check(args, torch, dist, gb, world, rank, local):
 
     rows = cols = 2048
     sigma = 80.0
-    if args.exchange == "halo":  # the overlap-save blocks take pad <= 256: sigma 70 (pad 232), 8 column blocks of 560 rows
+    exchange = force or resolve_exchange(args, gb, 4096, cols, 1, 70.0, False, world)
+    if exchange == "halo":  # the overlap-save blocks take pad <= 256: sigma 70 (pad 232), 8 column blocks of 560 rows
         rows, sigma = 4096, 70.0
     img = synth_u8((rows, cols), 0x77)
     r0, r1 = shard_range(rows, world, rank)
     band = torch.from_numpy(img[r0:r1].copy()).cuda().reshape(r1 - r0, cols, 1)
-    if args.exchange == "halo":
+    if exchange == "halo":
         from libgaussianblur_b200.multi import HaloShardedBlur
 
         bs = HaloShardedBlur.cuda(rows, cols, 1, sigma, device=local)
@@ -463,8 +481,8 @@ def band_check(args, torch, dist, gb, world, rank, local):
             got_rows = np.zeros_like(got_rows)  # fails the comparison below
     else:
         bs = BandShardedBlur.cuda(rows, cols, 1, sigma, False, device=local,
-                                  fused=(args.exchange if args.exchange in ("staged", "hybrid") else args.exchange == "fused"),
-                                  pipeline_chunks=(args.pipeline_chunks if args.exchange in ("nccl_pipelined", "staged", "hybrid") else 0))
+                                  fused=(exchange if exchange in ("staged", "hybrid") else exchange == "fused"),
+                                  pipeline_chunks=(args.pipeline_chunks if exchange in ("nccl_pipelined", "staged", "hybrid") else 0))
         out = bs.run(band)
         torch.cuda.synchronize()
         c0, c1 = bs.my_cols
@@ -477,7 +495,7 @@ def band_check(args, torch, dist, gb, world, rank, local):
         from oracle import gblur_oracle as go
 
         want, vs = go.gaussianblur(img, sigma, False), "oracle/gblur_oracle.py"
-    if args.exchange == "halo":
+    if exchange == "halo":
         d = np.abs(got_rows.astype(np.int16) - want[o0:o1].astype(np.int16)) if o1 > o0 else np.zeros(1, np.int16)
     else:
         d = np.abs(got.astype(np.int16) - want[:, c0:c1].astype(np.int16))
@@ -561,9 +579,11 @@ def main():
     ap.add_argument("--chunk-frames", type=int, default=16, help="frames per launch in the video workload")
     ap.add_argument("--force-band", action="store_true", help="band workloads at 1 GPU: run the band-sharded path anyway")
     ap.add_argument("--pipeline-chunks", type=int, default=8)
-    ap.add_argument("--exchange", default="staged", choices=["fused", "staged", "hybrid", "nccl", "nccl_pipelined", "halo"],
-                    help="band workloads: row pass stores into peer memory (fused), local row pass in chunks with "
-                         "copy-engine pushes into the owners' panel buffers (staged), or NCCL all-to-all")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "fused", "staged", "hybrid", "nccl", "nccl_pipelined", "halo"],
+                    help="band workloads: halo sharding (row bands for both passes; pad input rows + one int32 all-reduce "
+                         "cross the links), row pass stores into peer memory (fused), local row pass in chunks with "
+                         "copy-engine pushes into the owners' panel buffers (staged), or NCCL all-to-all; auto = halo "
+                         "where the overlap-save kernels take the geometry, else staged")
     args = ap.parse_args()
     wl = args.workload
     if args.impl == "reference":
@@ -732,6 +752,10 @@ def main():
         if world > 1:
             try:
                 bcheck = band_check(args, torch, dist, gb, world, rank, local)
+                if args.exchange == "auto" and bcheck.get("exchange", "").startswith("halo"):
+                    # auto falls back to the staged exchange for 3 channels / pad > 256: check that path as well
+                    other = band_check(args, torch, dist, gb, world, rank, local, force="staged")
+                    bcheck = {"max_abs": max(bcheck["max_abs"], other["max_abs"]), "checks": [bcheck, other]}
             except Exception as exc:
                 bcheck = {"error": repr(exc)[:300]}
 
