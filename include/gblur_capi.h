@@ -170,6 +170,24 @@ int gblur_mg_run_frames(gblur_mg* mg, uint8_t* hwc_frames_inout, int n_frames, i
 int gblur_mg_run_bands(gblur_mg* mg, uint8_t* hwc_inout, int apply_to_alpha);
 const char* gblur_mg_last_error(void);
 
+/* ---- an entry point that allocates nothing ----
+ * NO counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * gblur_colsum_noalloc computes what gblur_halo_colsum_device computes for a whole image — per byte column w of the
+ * rows x (cols * channels) u8 image, d_colsum[w] = sum over rows r of weight(r) * in[r][w], weight = (-1)^(pad + r) times
+ * the number of reflect_101-padded positions that read row r: the integer sums behind the Nyquist term of the column
+ * pass — but it accumulates in a file-scope static __device__ array (1 MiB + 2 KiB per GPU that loads the library, held
+ * until exit) instead of a buffer the plan allocates. The call makes `device` current for its duration, issues two
+ * cudaMemsetAsync on that array and one kernel on `cuda_stream`, and calls no cudaMalloc / cudaFree / allocating routine.
+ *   limits   cols * channels <= GBLUR_NOALLOC_MAX_ROW_BYTES (GBLUR_E_UNSUPPORTED beyond it, with a message), a multiple
+ *            of 4; d_in 4-byte aligned, d_colsum (cols * channels int32, fully overwritten) 16-byte aligned.
+ *   sharing  every call on a device uses the SAME array, which keeps the last call's contents (each call clears what it
+ *            uses first, in stream order): calls that overlap on the GPU — different streams, different host threads —
+ *            race. Serialise them on one stream or with events. */
+#define GBLUR_NOALLOC_MAX_ROW_BYTES 262144
+int gblur_colsum_noalloc(int device, const uint8_t* d_in, int rows, int cols, int channels, float sigma, int32_t* d_colsum,
+                         void* cuda_stream);
+
 /* Test hook: fp32 row-pass output of the last gblur_run_* call on this plan (frame 0), copied to
  * host as [rows][cols*Cp]. */
 int gblur_dump_intermediate(gblur_plan* plan, float* host_out, int apply_to_alpha);

@@ -22,7 +22,8 @@ import numpy as np
 from . import build as _build
 
 __all__ = ["Plan", "GblurError", "lib", "gaussianblur", "gaussianblur_module", "host_plan_sizes", "host_spectrum",
-           "host_line_plan", "host_kperm", "host_taps", "launch_count", "EXPORTED_SYMBOLS", "HaloPlan", "halo_partition"]
+           "host_line_plan", "host_kperm", "host_taps", "launch_count", "EXPORTED_SYMBOLS", "HaloPlan", "halo_partition",
+           "colsum_noalloc", "NOALLOC_MAX_ROW_BYTES"]
 
 # every symbol include/gblur_capi.h declares
 EXPORTED_SYMBOLS = [
@@ -34,6 +35,7 @@ EXPORTED_SYMBOLS = [
     "gblur_halo_partition", "gblur_plan_create_halo", "gblur_halo_info", "gblur_halo_colsum_device", "gblur_halo_run_device",
     "gblur_halo_rowpass_device", "gblur_halo_colpass_device",
     "gblur_mg_create", "gblur_mg_destroy", "gblur_mg_info", "gblur_mg_run_frames", "gblur_mg_run_bands", "gblur_mg_last_error",
+    "gblur_colsum_noalloc",
     "gblur_dump_intermediate", "gblur_launch_count", "gblur_last_error", "gblur_device_count",
     "gblur_host_plan_sizes", "gblur_host_taps", "gblur_host_spectrum", "gblur_host_line_plan", "gblur_host_kperm",
 ]
@@ -89,6 +91,7 @@ def lib():
         "gblur_plan_create_halo": (C.c_int, [pp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, C.c_int]),
         "gblur_halo_info": (C.c_int, [vp, ip, ip, ip, ip]),
         "gblur_halo_colsum_device": (C.c_int, [vp, u8p, vp, vp]),
+        "gblur_colsum_noalloc": (C.c_int, [C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_float, vp, vp]),
         "gblur_halo_run_device": (C.c_int, [vp, u8p, vp, u8p, vp]),
         "gblur_halo_rowpass_device": (C.c_int, [vp, u8p, C.c_int, C.c_int, vp]),
         "gblur_halo_colpass_device": (C.c_int, [vp, vp, u8p, vp]),
@@ -309,6 +312,16 @@ def halo_partition(rows: int, cols: int, sigma: float, n_ranks: int, rank: int) 
     v = [C.c_int() for _ in range(4)]
     _check(lib().gblur_halo_partition(rows, cols, sigma, n_ranks, rank, *[C.byref(x) for x in v]))
     return dict(zip(("out_row0", "out_row1", "in_row0", "in_row1"), (x.value for x in v)))
+
+
+NOALLOC_MAX_ROW_BYTES = 262144  # include/gblur_capi.h: GBLUR_NOALLOC_MAX_ROW_BYTES
+
+
+def colsum_noalloc(d_in, rows: int, cols: int, channels: int, sigma: float, d_colsum, device: int = 0, stream=None):
+    """gblur_colsum_noalloc: the weighted column sums of a device-resident u8 image into d_colsum (cols * channels int32),
+    accumulated in the library's static device scratch — no allocation on the call path. Calls that overlap on the GPU
+    race (they share the scratch). No counterpart in the reference."""
+    _check(lib().gblur_colsum_noalloc(device, _ptr(d_in), rows, cols, channels, sigma, _ptr(d_colsum), _stream_ptr(stream)))
 
 
 class HaloPlan:

@@ -124,7 +124,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         raise RuntimeError(f"nvcc not found at {NVCC}; cannot build the sm_100a library")
 
     jobs = []  # (object, cmd, source)
-    for name in ("kernels.cu", "generic_row.cu", "generic_col.cu", "cluster_kernels.cu", "ols_kernels.cu"):
+    for name in ("kernels.cu", "generic_row.cu", "generic_col.cu", "cluster_kernels.cu", "ols_kernels.cu", "noalloc.cu"):
         o = os.path.join(OBJ, name.replace(".cu", ".o"))
         jobs.append((o, [NVCC, *ARCH, *COMMON, "-c", os.path.join(CSRC, name), "-o", o], os.path.join(CSRC, name)))
     for sid in _static_ids():

@@ -360,6 +360,11 @@ int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d
 
 }  // namespace
 
+namespace gblur {
+// for entry points that live in other translation units (noalloc.cu): the text gblur_last_error() returns on this thread
+void set_last_error(const char* message) { g_err = message ? message : ""; }
+}  // namespace gblur
+
 extern "C" {
 
 const char* gblur_last_error(void) { return g_err.c_str(); }
