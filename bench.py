@@ -9,8 +9,10 @@ N > 1 (torchrun, one rank per GPU) every rank blurs its own frame — frames sha
 collective — so scaling is weak and `value` is the whole-job pixels / max-over-ranks time.
 
 Prints ONE JSON line. `value` is device-resident throughput (CUDA events on the launch stream);
-`e2e` goes through the host-buffer C-ABI call (pinned host memory, H2D + blur + D2H inside the
-timed region), `e2e.pageable` through the drop-in C++ call on an ordinary (pageable) buffer;
+`e2e` goes through the host-buffer C-ABI calls on pinned host memory, H2D + blur + D2H of every step
+inside the timed region: `e2e.value` streams the K steps' frames through the batch call (consecutive
+steps overlap on the two PCIe directions), `e2e.single_call` is one blocking call per image,
+`e2e.pageable` the drop-in C++ call on an ordinary (pageable) buffer;
 `roofline` is the dominant kernel against the measured HBM copy peak, `roofline.per_kernel` both;
 `cpu_baseline` is the compiled, unmodified reference (oracle/_ref) on the box's host cores;
 `parity_check` compares what the timed loops produced with that reference's output (exit code 3
@@ -691,18 +693,44 @@ def main():
             sustained = {"steps": n_sus, "seconds": sus_ms * 1e-3, "ms_per_step": sus_ms / n_sus,
                          "value": world * npx * n_sus / (sus_ms * 1e-3) / 1e6, "unit": UNIT, "clocks": s2.stop()}
 
-    # ---- end to end through the host-buffer C-ABI call (pinned memory); every step blurs the original input ----
+    # ---- end to end through the host-buffer C-ABI calls (pinned memory); every step blurs the original input ----
+    # (1) one blocking call per image (gblur_run_host): H2D and D2H of ONE image cannot overlap each other (the column
+    #     pass needs every row before the first output byte exists), so this is latency: ~ H2D + D2H of 133 MB each
     for _ in range(2):
         plan.run_host(h_pinned, alpha)
     src_pinned = torch.from_numpy(img.copy()).pin_memory()
     barrier()
-    e2e_s = 0.0
+    e2e_single_s = 0.0
     for _ in range(args.steps):
         h_pinned.copy_(src_pinned)  # restore the input (not timed): the call blurs in place
         t0 = time.perf_counter()
         plan.run_host(h_pinned, alpha)
-        e2e_s += time.perf_counter() - t0
+        e2e_single_s += time.perf_counter() - t0
     out_e2e = h_pinned.numpy().copy()
+    # (2) the same K steps as ONE stream of frames through the batch call (gblur_run_batch_host on a pinned buffer of K
+    #     images; what gaussianblur_batch runs): H2D of step k+1, the blur of step k and the D2H of step k-1 overlap, every
+    #     step's two copies are inside the timed region. This is the throughput figure (`e2e.value`).
+    n_buf = min(args.steps, 32)  # pinned frames held at once (4.2 GB at most); more steps = several calls
+    h_frames = torch.empty((n_buf, rows, cols, ch), dtype=torch.uint8).pin_memory()
+
+    def refill():
+        for f in range(n_buf):
+            h_frames[f].copy_(src_pinned)
+
+    refill()
+    plan.run_host(h_frames, alpha, n_frames=n_buf)  # warm-up: allocates the staging ring
+    e2e_s, left, stream_same, out_stream = 0.0, args.steps, True, None
+    while left > 0:
+        n = min(left, n_buf)
+        refill()
+        barrier()
+        t0 = time.perf_counter()
+        plan.run_host(h_frames[:n], alpha, n_frames=n)
+        e2e_s += time.perf_counter() - t0
+        left -= n
+        out_stream = h_frames[n - 1].numpy().copy()
+        stream_same = stream_same and all(bool(torch.equal(h_frames[f], h_frames[0])) for f in range(1, n))
+    del h_frames
 
     # ---- the drop-in call on an ordinary (pageable) buffer: gaussianblur::gaussianblur_buffer via the pybind module ----
     pageable = None
@@ -723,10 +751,10 @@ def main():
         pageable = {"error": repr(exc)[:200]}
 
     pcie_gbs, pcie_ms = pcie_ceiling(torch, int(img.nbytes))
-    t = torch.tensor([ms_total, e2e_s * 1e3, -pcie_gbs], dtype=torch.float64, device="cuda")
+    t = torch.tensor([ms_total, e2e_s * 1e3, -pcie_gbs, e2e_single_s * 1e3], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms_total, e2e_ms, pcie_min = float(t[0]), float(t[1]), -float(t[2])
+    ms_total, e2e_ms, pcie_min, e2e_single_ms = float(t[0]), float(t[1]), -float(t[2]), float(t[3])
 
     # ---- secondary: the band-sharded 32768^2 case at this N (BASELINE.json config 4), and the multi-GPU check ----
     secondary, bcheck = None, None
@@ -783,6 +811,14 @@ def main():
                                   "in the fused step the column pass's pre-kernels run beside the row pass"},
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(img.nbytes),
                     "d2h_bytes_per_step": int(img.nbytes), "ms_per_step": e2e_ms / args.steps,
+                    "what": f"{args.steps} steps as one stream of frames through gblur_run_batch_host (the call behind "
+                            "gaussianblur_batch) on one pinned host buffer: every step's H2D and D2H are in the timed "
+                            "region, consecutive steps overlap (H2D k+1 || blur k || D2H k-1, ring of 3 device buffers)",
+                    "single_call": {"value": world * npx * args.steps / (e2e_single_ms * 1e-3) / 1e6, "unit": UNIT,
+                                    "ms_per_step": e2e_single_ms / args.steps,
+                                    "what": "one blocking gblur_run_host call per image (latency: the H2D and the D2H of "
+                                            "one image cannot overlap each other)"},
+                    "stream_frames_identical": stream_same,
                     "pcie_peak_gbs": pcie_min, "pcie_peak_what": "concurrent pinned H2D + D2H of one image each way, min over ranks",
                     "frac_of_pcie": (2 * img.nbytes / (e2e_ms / args.steps * 1e-3) / 1e9) / pcie_min if pcie_min > 0 else None,
                     "pageable": pageable},
@@ -805,13 +841,15 @@ def main():
             if res is not None and res["out"] is not None:
                 want = res["out"]
                 d1 = np.abs(out_dev.astype(np.int16) - want.astype(np.int16))
-                d2 = np.abs(out_e2e.astype(np.int16) - want.astype(np.int16))
+                d2 = np.maximum(np.abs(out_e2e.astype(np.int16) - want.astype(np.int16)),
+                                np.abs(out_stream.astype(np.int16) - want.astype(np.int16)))
                 line["parity_check"] = {"max_abs": int(max(d1.max(), d2.max())), "n_diff": int(np.count_nonzero(d1)),
                                         "device_path_max_abs": int(d1.max()), "e2e_path_max_abs": int(d2.max()),
                                         "e2e_n_diff": int(np.count_nonzero(d2)), "n_bytes": int(want.size), "vs": "oracle/_ref",
-                                        "what": "d_out after the timed loop and the host buffer after the e2e loop vs the "
-                                                "compiled reference's output for the same image"}
-                if line["parity_check"]["max_abs"] > 1:
+                                        "what": "d_out after the timed loop, the host buffer after the single-call e2e loop and "
+                                                "the last frame of the streamed e2e run vs the compiled reference's output "
+                                                "for the same image"}
+                if line["parity_check"]["max_abs"] > 1 or not stream_same:
                     rc = 3
         if bcheck is not None and bcheck.get("max_abs", 0) > 1:
             rc = 3

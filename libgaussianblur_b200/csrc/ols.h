@@ -15,10 +15,13 @@ struct RowPlan;  // device tables: twiddles, block gains, Nyquist coefficient, p
 
 // taps: the reference's normalised taps; n_ref: the reference's transform length along a row
 // n_ref_col: its transform length along a column (0: the column pass is not wanted)
-cudaError_t row_plan_create(RowPlan** out, const std::vector<float>& taps, int n_ref, int n_ref_col = 0);
+// dil: 1, or 3 for rows of three interleaved channels (RGB) run as byte rows — the block gains then belong to the taps
+// spread three samples apart (row pass only)
+cudaError_t row_plan_create(RowPlan** out, const std::vector<float>& taps, int n_ref, int n_ref_col = 0, int dil = 1);
 void row_plan_destroy(RowPlan* p);
 
-// RGBA with all four channels processed, panel intermediate for a two-sequence column plan, no peer/split stores
+// RGBA with all four channels processed (panel intermediate for a two-sequence column plan), one channel, or RGB with
+// a plan made with dil = 3; no peer/split stores
 bool row_eligible(const RowPlan* p, const RowLaunch& a);
 
 // The 1024-sample blocks cost nblk * 1024 transform points per row against the whole line's n_ref: worth it for wide

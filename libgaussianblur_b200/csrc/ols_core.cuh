@@ -59,6 +59,7 @@ struct RowParams {
   int blk_np, blk_padq;
   int pair_major;          // 1: the 32 floats of a panel row are ordered [pair][pixel][2] instead of [pixel][pair][2]
   int slot_origin;         // the panel buffer starts at this slot of the padded column (halo-sharded runs), else 0
+  int Tpx, padpx;          // interleaved 3-channel rows run as one byte row (T, pad, L in BYTES): pixels per row, pad in pixels
   long long blk_frame_stride;
   const float4* qa;        // per image row: (K[0] - K[N/2]) / N * alternating sum, one float per channel
   const float2* tw;        // tw[lane * kTwStride + k] = exp(-2 pi i lane k / 1024)
@@ -73,6 +74,16 @@ __device__ __forceinline__ int reflect_src(int n, int pad, int T) {
   if (t < 0) t = -t;
   if (t >= T) t = 2 * T - 2 - t;
   return (n < T + 2 * pad) ? t : -1;
+}
+
+// The same for a row of DIL interleaved channels seen as one byte row: padded byte n is channel n % DIL of padded pixel
+// n / DIL, so its source is byte DIL * reflect + channel. (An RGB row convolved per channel = the byte row convolved with
+// the taps spread DIL bytes apart: one transform serves all channels and every store is a contiguous run of floats.)
+template <int DIL>
+__device__ __forceinline__ int reflect_src_dil(int n, int padpx, int Tpx) {
+  const int pp = n / DIL, ch = n - DIL * pp;  // n >= 0
+  const int t = reflect_src(pp, padpx, Tpx);
+  return t < 0 ? -1 : DIL * t + ch;
 }
 
 // weight of pixel x in the alternating sum over the padded line: (-1)^(pad + x) times the number of padded
@@ -154,7 +165,7 @@ __device__ __forceinline__ RowDst make_row_dst(const RowParams& P, long long r_g
   RowDst d;
   const long long f = (r_global + P.row_offset) / P.rows_per_frame;
   const int r = (int)(r_global + P.row_offset - f * P.rows_per_frame);
-  const int Tc = P.rows_per_frame, pad = P.pad;
+  const int Tc = P.rows_per_frame, pad = P.padpx;  // the pad along a column is in pixels also where the row runs in bytes
   const int p1 = phys_slot(pad + r, P.blk_padq) - P.slot_origin;
   d.base = P.inter + f * P.blk_frame_stride + (long long)p1 * 32;
   d.gstride = (long long)P.blk_np * 32;
@@ -234,7 +245,7 @@ __device__ __forceinline__ float2 u8x2_to_f32(uint32_t a, uint32_t b) {
   return make_float2((float)a, (float)b);
 #endif
 }
-template <bool INTERIOR>
+template <bool INTERIOR, int DIL = 1>
 __device__ __forceinline__ void load_block_staged_c1(float2 (&c)[kR], const RowParams& P, const uint8_t* __restrict__ st0,
                                                      const uint8_t* __restrict__ st1, int s, int lane) {
   const int x_lo = stage_x_lo_c1(s, P.pad);
@@ -245,7 +256,7 @@ __device__ __forceinline__ void load_block_staged_c1(float2 (&c)[kR], const RowP
   } else {
 #pragma unroll
     for (int i = 0; i < kR; ++i) {
-      const int x = reflect_src(s + lane + kR * i, P.pad, P.T);
+      const int x = DIL == 1 ? reflect_src(s + lane + kR * i, P.pad, P.T) : reflect_src_dil<DIL>(s + lane + kR * i, P.padpx, P.Tpx);
       const int o = x < 0 ? 0 : x - x_lo;
       const float2 v = u8x2_to_f32(st0[o], st1[o]);
       c[i] = (x < 0) ? make_float2(0.f, 0.f) : v;
@@ -255,21 +266,42 @@ __device__ __forceinline__ void load_block_staged_c1(float2 (&c)[kR], const RowP
 
 // lane l, register j hold 1024 (y_r[n] + i y_{r+1}[n]), n = (32 - l) + 32 (31 - j): two scalar stores per sample, one
 // into each row's slot (32 lanes = 128 contiguous bytes of a panel row). second = false: row r + 1 does not exist.
+// qa0 / qa1: the rows' Nyquist terms; DIL == 1 uses .x, DIL == 3 one component per channel — byte b = 3 x + ch gets
+// (-1)^(padpx + x) qa[ch], and b mod 6 (which fixes both ch and the parity of x) advances by 32 = 2 mod 6 from one
+// register to the next, so three add vectors serve the whole loop.
+template <int DIL = 1>
 __device__ __forceinline__ void store_block_c1(const float2 (&c)[kR], const RowParams& P, const RowDst& d0, const RowDst& d1,
-                                               float qa0, float qa1, int s, int lane, bool second) {
+                                               float4 qa0, float4 qa1, int s, int lane, bool second) {
+  static_assert(DIL == 1 || DIL == 3, "one channel, or three interleaved");
   const int l1 = kR - lane;
-  const float sg = ((s + l1) & 1) ? -1.0f : 1.0f;
-  const float2 add = make_float2(qa0 * sg, qa1 * sg);
+  const int x0 = s + l1 - P.pad;  // float column x = x0 + 32 i: panel (x0 >> 5) + i, float x0 & 31
+  float2 add[DIL];
+  if constexpr (DIL == 1) {
+    const float sg = ((s + l1) & 1) ? -1.0f : 1.0f;
+    add[0] = make_float2(qa0.x * sg, qa1.x * sg);
+  } else {
+    int m0 = x0 % 6;
+    if (m0 < 0) m0 += 6;
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      int m = m0 + 2 * k;
+      if (m >= 6) m -= 6;
+      const int ch = m >= 3 ? m - 3 : m;
+      const bool neg = ((m >= 3) != ((P.padpx & 1) != 0));
+      const float a0 = ch == 0 ? qa0.x : (ch == 1 ? qa0.y : qa0.z);
+      const float a1 = ch == 0 ? qa1.x : (ch == 1 ? qa1.y : qa1.z);
+      add[k] = make_float2(neg ? -a0 : a0, neg ? -a1 : a1);
+    }
+  }
   const int lo = P.pad - l1;
   const int hi = min(P.pad + P.L, P.T - s + P.pad) - l1;
-  const int x0 = s + l1 - P.pad;  // pixel x = x0 + 32 i: panel (x0 >> 5) + i, float x0 & 31
   const long long off = (long long)(x0 >> 5) * d0.gstride + (x0 & 31);
   float* p0 = d0.base + off;
   float* p1 = d1.base + off;
 #pragma unroll
   for (int i = 0; i < kR; ++i) {
     if (kR * i >= lo && kR * i < hi) {
-      const float2 v = pk_add(c[kR - 1 - i], add);
+      const float2 v = pk_add(c[kR - 1 - i], add[DIL == 1 ? 0 : i % 3]);
       *p0 = v.x;
       if (d0.dl) p0[d0.dl] = v.x;
       if (d0.dr) p0[d0.dr] = v.x;
@@ -282,11 +314,36 @@ __device__ __forceinline__ void store_block_c1(const float2 (&c)[kR], const RowP
     p0 += d0.gstride;
     p1 += d0.gstride;
   }
-  if (P.pad == 0 && lane == 0 && s < P.T) {  // a one-tap window: block index 0 sits at "index 1024" of lane 0
+  if (DIL == 1 && P.pad == 0 && lane == 0 && s < P.T) {  // a one-tap window: block index 0 sits at "index 1024" of lane 0
     const float sg0 = (s & 1) ? -1.0f : 1.0f;
     const long long o0 = (long long)(s >> 5) * d0.gstride + (s & 31);
-    d0.base[o0] = c[0].x + qa0 * sg0;
-    if (second) d1.base[o0] = c[0].y + qa1 * sg0;
+    d0.base[o0] = c[0].x + qa0.x * sg0;
+    if (second) d1.base[o0] = c[0].y + qa1.x * sg0;
+  }
+}
+
+// one lane's share of the alternating sums of a row of three interleaved channels (16 bytes per load, rows 16-byte
+// aligned and a multiple of 16 bytes long): a[ch] += weight(x) * byte(3 x + ch)
+__device__ __forceinline__ void altsum_lane_c3(const uint8_t* __restrict__ row, int Tpx, int padpx, int lane, int (&a)[3]) {
+  const uint4* row4 = reinterpret_cast<const uint4*>(row);
+  const int n16 = (3 * Tpx) >> 4;
+  for (int g = lane; g < n16; g += 32) {
+    const uint4 v = GBLUR_OLS_LDG(row4 + g);
+    const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+    int x = (16 * g) / 3, ch = 16 * g - 3 * x;
+    int m = altsum_weight(x, padpx, Tpx);
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      const int byte = (int)((w4[k >> 2] >> (8 * (k & 3))) & 255u);
+      if (ch == 0) a[0] += m * byte;
+      if (ch == 1) a[1] += m * byte;
+      if (ch == 2) a[2] += m * byte;
+      if (++ch == 3) {
+        ch = 0;
+        ++x;
+        m = altsum_weight(x < Tpx ? x : Tpx - 1, padpx, Tpx);
+      }
+    }
   }
 }
 

@@ -19,7 +19,9 @@ struct HostTables {
 };
 
 // taps.size() must not exceed 1024 - 512 + 1 (pad <= 256)
-inline HostTables build_tables(const std::vector<float>& taps, int n_ref, int n_ref_col = 0) {
+// dil > 1: the block gains of the taps spread dil samples apart (rows of dil interleaved channels run as one row); the
+// Nyquist coefficients stay those of the taps themselves at the reference's lengths
+inline HostTables build_tables(const std::vector<float>& taps, int n_ref, int n_ref_col = 0, int dil = 1) {
   constexpr int NB = 1024, R = 32, GS = 36, TS = 34;
   constexpr double two_pi = 6.28318530717958647692528676655900577;
   HostTables t;
@@ -30,7 +32,9 @@ inline HostTables build_tables(const std::vector<float>& taps, int n_ref, int n_
       t.tw[2 * (a * TS + b)] = (float)std::cos(ang);
       t.tw[2 * (a * TS + b) + 1] = (float)(-std::sin(ang));
     }
-  const std::vector<double> kb = host::kernel_gains(taps, NB);
+  std::vector<float> spread(((size_t)taps.size() - 1) * (size_t)dil + 1, 0.0f);
+  for (size_t j = 0; j < taps.size(); ++j) spread[j * (size_t)dil] = taps[j];
+  const std::vector<double> kb = host::kernel_gains(spread, NB);
   t.gains.assign((size_t)R * GS, 0.0f);
   for (int k1 = 0; k1 < R; ++k1)
     for (int k2 = 0; k2 < R; ++k2) {

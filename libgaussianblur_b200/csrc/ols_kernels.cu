@@ -26,6 +26,7 @@ struct RowPlan {
   float* d_gains = nullptr;
   float q = 0.f;
   int ksize = 0;
+  int dil = 1;              // 3: the block gains belong to taps spread three bytes apart (interleaved RGB rows)
   float4* d_qa = nullptr;
   long long qa_rows = 0;
   // column pass
@@ -178,9 +179,29 @@ __global__ void __launch_bounds__(kAltsumWarps * 32)
   if (lane == 0) qa[r] = q * (float)a;
 }
 
+// rows of three interleaved channels (RGB): per row (q * sum_ch) as a float4 (w unused)
+__global__ void __launch_bounds__(kAltsumWarps * 32)
+    altsum_rows_c3_kernel(const uint8_t* __restrict__ in, long long in_pitch, int Tpx, int padpx, float q, long long rows_total,
+                          float4* __restrict__ qa) {
+  const int lane = threadIdx.x & 31;
+  const long long r = (long long)blockIdx.x * kAltsumWarps + (threadIdx.x >> 5);
+  if (r >= rows_total) return;
+  int a[3] = {0, 0, 0};
+  altsum_lane_c3(in + r * in_pitch, Tpx, padpx, lane, a);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a[0] += __shfl_xor_sync(0xffffffffu, a[0], o);
+    a[1] += __shfl_xor_sync(0xffffffffu, a[1], o);
+    a[2] += __shfl_xor_sync(0xffffffffu, a[2], o);
+  }
+  if (lane == 0) qa[r] = make_float4(q * (float)a[0], q * (float)a[1], q * (float)a[2], 0.f);
+}
+
 // One item = one block of a PAIR of image rows (row r is the real part of the complex sequence, row r + 1 the imaginary
 // part); both rows' bytes are staged by bulk copies one item ahead, as in the RGBA kernel above.
-template <int WARPS, int MAXREG>
+// DIL == 3: the rows hold three interleaved channels and run as byte rows (P.T, P.pad, P.L in bytes; ols_core.cuh
+// reflect_src_dil): the block gains are those of the taps spread three bytes apart, the Nyquist term is per channel.
+template <int WARPS, int MAXREG, int DIL>
 __global__ void __maxnreg__(MAXREG) ols_row_c1_kernel(const __grid_constant__ RowParams P, long long rows_total) {
   extern __shared__ __align__(16) unsigned char smem_raw[];
   float2* tw = reinterpret_cast<float2*>(smem_raw);
@@ -225,20 +246,27 @@ __global__ void __maxnreg__(MAXREG) ols_row_c1_kernel(const __grid_constant__ Ro
     const long long r = 2 * rp;
     const bool second = r + 1 < rows_total;
     const bool interior = s - P.pad >= 0 && s - P.pad + kNB <= P.T;
-    const float qa0 = __ldg(qa + r), qa1 = second ? __ldg(qa + r + 1) : 0.f;
+    float4 qa0 = make_float4(0.f, 0.f, 0.f, 0.f), qa1 = qa0;
+    if constexpr (DIL == 1) {
+      qa0.x = __ldg(qa + r);
+      if (second) qa1.x = __ldg(qa + r + 1);
+    } else {
+      qa0 = __ldg(P.qa + r);
+      if (second) qa1 = __ldg(P.qa + r + 1);
+    }
     const RowDst d0 = make_row_dst(P, r), d1 = make_row_dst(P, second ? r + 1 : r);
     mbar_wait(bar, parity);
     parity ^= 1;
     float2 c[kR];
     // without a second row its staging buffer holds stale bytes: the imaginary part is computed and dropped
     if (interior)
-      load_block_staged_c1<true>(c, P, st0, st1, s, lane);
+      load_block_staged_c1<true, DIL>(c, P, st0, st1, s, lane);
     else
-      load_block_staged_c1<false>(c, P, st0, st1, s, lane);
+      load_block_staged_c1<false, DIL>(c, P, st0, st1, s, lane);
     __syncwarp();  // every lane has read the staging buffers
     if (lane == 0 && b + stride < nitems) issue(b + stride);
     block_passes(c, lane, ex, twl, gains);
-    store_block_c1(c, P, d0, d1, qa0, qa1, s, lane, second);
+    store_block_c1<DIL>(c, P, d0, d1, qa0, qa1, s, lane, second);
   }
 }
 
@@ -451,11 +479,14 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
   if (tid == 0) bulk_wait<0>();
 }
 
-cudaError_t row_plan_create(RowPlan** out, const std::vector<float>& taps, int n_ref, int n_ref_col) {
+cudaError_t row_plan_create(RowPlan** out, const std::vector<float>& taps, int n_ref, int n_ref_col, int dil) {
   *out = nullptr;
-  if ((int)taps.size() > 2 * kMaxPad + 1) return cudaSuccess;  // window too wide for 1024-sample blocks: not eligible
-  const HostTables t = build_tables(taps, n_ref, n_ref_col);
+  if (dil != 1 && dil != 3) return cudaErrorInvalidValue;
+  // window too wide for 1024-sample blocks (spread taps: dil * pad samples on either side): not eligible
+  if (((int)taps.size() - 1) * dil > 2 * kMaxPad || (dil != 1 && taps.size() < 3)) return cudaSuccess;
+  const HostTables t = build_tables(taps, n_ref, n_ref_col, dil);
   RowPlan* p = new RowPlan();
+  p->dil = dil;
   p->q = t.q;
   p->q_col = t.q_col;
   p->ksize = (int)taps.size();
@@ -488,12 +519,23 @@ bool row_eligible(const RowPlan* p, const RowLaunch& a) {
     return false;
   if (a.C == 4 && a.Cp == 4)
     return a.blk.L == 4 && (a.in_pitch % 4) == 0 && (reinterpret_cast<uintptr_t>(a.in) % 4) == 0;
+  if (p->dil != (a.C == 3 ? 3 : 1)) return false;
   if (a.C == 1 && a.Cp == 1)  // one channel: staged rows only (16-byte aligned rows of whole 16-pixel groups), natural order
     return a.blk.pair_major == 0 && (a.in_pitch % 16) == 0 && (reinterpret_cast<uintptr_t>(a.in) % 16) == 0 && (a.T % 16) == 0;
+  if (a.C == 3 && a.Cp == 3) {  // RGB as byte rows: the same, plus a last block that still holds a whole pixel
+    const int TB = 3 * a.T, L = kNB - 6 * a.pad;
+    return a.blk.pair_major == 0 && (a.in_pitch % 16) == 0 && (reinterpret_cast<uintptr_t>(a.in) % 16) == 0 && (TB % 16) == 0 &&
+           3 * a.pad <= kMaxPad && a.pad >= 1 && (TB % L == 0 || TB % L >= 3);
+  }
   return false;
 }
 
 bool row_profitable(const RowLaunch& a, int n_ref) {
+  // RGB byte rows are never picked automatically: measured on 512 x 1080p RGB sigma=10 (B200, profiles/r02/
+  // bench_video_rgb_ols_rowpass_{on,off}.json) 45.3 Gpixel/s against 58.8 with the whole-line kernels — the short
+  // 2048-point lines run four CTAs per SM there, the byte rows transform 17 % more points and the one-channel block
+  // kernel pays two byte loads and two scalar stores per sample. GBLUR_ROW_OLS=1 still forces them (parity-tested).
+  if (a.C == 3) return false;
   const int L = kNB - 2 * a.pad;
   if (L < 1 || a.T < 4096) return false;
   const long long nblk = (a.T + L - 1) / L;
@@ -564,10 +606,10 @@ cudaError_t launch_blocks_staged(const RowParams& P, int num_sms, cudaStream_t s
 }  // namespace
 
 namespace {
-template <int WARPS, int MAXREG>
+template <int WARPS, int MAXREG, int DIL>
 cudaError_t launch_blocks_c1(const RowParams& P, long long rows_total, int num_sms, cudaStream_t stream) {
   constexpr size_t smem = kTableBytes + (size_t)WARPS * (kExch * 8 + 2 * kStageC1 + 8);
-  auto k = ols_row_c1_kernel<WARPS, MAXREG>;
+  auto k = ols_row_c1_kernel<WARPS, MAXREG, DIL>;
   static PerDevice pd;
   int device = 0;
   cudaGetDevice(&device);
@@ -603,6 +645,8 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
   P.in_pitch = a.in_pitch;
   P.T = a.T;
   P.pad = a.pad;
+  P.Tpx = a.T;
+  P.padpx = a.pad;
   P.L = kNB - 2 * a.pad;
   P.nblk = (a.T + P.L - 1) / P.L;
   P.nitems = a.rows_total * P.nblk * 2;
@@ -625,7 +669,20 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
     count_launch();
     const cudaError_t e1 = cudaGetLastError();
     if (e1 != cudaSuccess) return e1;
-    return launch_blocks_c1<16, 128>(P, a.rows_total, num_sms, stream);
+    return launch_blocks_c1<16, 128, 1>(P, a.rows_total, num_sms, stream);
+  }
+  if (a.C == 3) {  // byte rows
+    P.Tpx = a.T;
+    P.padpx = a.pad;
+    P.T = 3 * a.T;
+    P.pad = 3 * a.pad;
+    P.L = kNB - 2 * P.pad;
+    P.nblk = (P.T + P.L - 1) / P.L;
+    altsum_rows_c3_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total, p->d_qa);
+    count_launch();
+    const cudaError_t e3 = cudaGetLastError();
+    if (e3 != cudaSuccess) return e3;
+    return launch_blocks_c1<16, 128, 3>(P, a.rows_total, num_sms, stream);
   }
   altsum_rows_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total, p->d_qa);
   count_launch();

@@ -29,8 +29,8 @@ int ols_emulate_rowpass(const uint8_t* in, int rows, int T, float sigma, int ksi
   ols::RowParams P{};
   P.in = in;
   P.in_pitch = (long long)T * 4;
-  P.T = T;
-  P.pad = pad;
+  P.T = P.Tpx = T;
+  P.pad = P.padpx = pad;
   P.L = ols::kNB - 2 * pad;
   P.nblk = (T + P.L - 1) / P.L;
   P.nitems = (long long)rows * P.nblk * 2;
@@ -106,6 +106,110 @@ int ols_emulate_rowpass(const uint8_t* in, int rows, int T, float sigma, int ksi
 
 }  // extern "C"
 
+// One-channel rows (C == 1) and rows of three interleaved channels (C == 3, run as byte rows with the taps spread three
+// bytes apart) through the lane functions of ols_row_c1_kernel<.., DIL = C>: a complex sequence carries image rows r and
+// r + 1, both staged as the kernel's bulk copies stage them (bytes [x_lo, x_hi) of the row, 16-byte granules).
+// in: rows x (T * C) u8. out: rows x (T * C) floats (element (r, C x + ch)). Returns 0 or a negative code.
+template <int DIL>
+static int emulate_rowpass_c(const uint8_t* in, int rows, int T, float sigma, int ksize, int n_ref, int padq, float* out) {
+  const std::vector<float> taps = host::gaussian_taps(sigma, ksize);
+  const ols::HostTables tb = ols::build_tables(taps, n_ref, 0, DIL);
+  const int padpx = (ksize - 1) / 2;
+  ols::RowParams P{};
+  P.in = in;
+  P.in_pitch = (long long)T * DIL;
+  P.Tpx = T;
+  P.padpx = padpx;
+  P.T = T * DIL;
+  P.pad = padpx * DIL;
+  if (P.pad > ols::kMaxPad) return -20;
+  P.L = ols::kNB - 2 * P.pad;
+  P.nblk = (P.T + P.L - 1) / P.L;
+  P.rows_per_frame = rows;
+  P.blk_padq = padq;
+  P.blk_np = ols::phys_slot(rows + 2 * padpx, padq) + 3;
+  const long long panels = ((long long)P.T + 31) / 32;
+  P.blk_frame_stride = panels * P.blk_np * 32;
+  std::vector<float> inter((size_t)P.blk_frame_stride, -12345.0f);
+  P.inter = inter.data();
+  std::vector<float4> qa((size_t)rows);
+  for (int r = 0; r < rows; ++r) {
+    const uint8_t* row = in + (size_t)r * P.in_pitch;
+    int chk[3] = {0, 0, 0};
+    for (int x = 0; x < T; ++x)
+      for (int ch = 0; ch < DIL; ++ch) chk[ch] += ols::altsum_weight(x, padpx, T) * (int)row[(size_t)x * DIL + ch];
+    int a[3] = {0, 0, 0};
+    if (DIL == 1) {
+      for (int lane = 0; lane < 32; ++lane) a[0] += ols::altsum_lane_c1(row, T, padpx, lane);
+    } else {
+      for (int lane = 0; lane < 32; ++lane) ols::altsum_lane_c3(row, T, padpx, lane, a);
+    }
+    for (int ch = 0; ch < DIL; ++ch)
+      if (chk[ch] != a[ch]) return -3;
+    qa[(size_t)r] = make_float4(tb.q * (float)a[0], tb.q * (float)a[1], tb.q * (float)a[2], 0.f);
+  }
+  P.tw = reinterpret_cast<const float2*>(tb.tw.data());
+  P.gains = tb.gains.data();
+  std::vector<float4> exbuf((size_t)ols::kExch / 2 + 8);
+  float2* ex = reinterpret_cast<float2*>(exbuf.data());
+  std::vector<uint8_t> st0(ols::kStageC1), st1(ols::kStageC1);
+  const long long npairs = (rows + 1) / 2;
+  static float2 regs[32][ols::kR];
+  for (long long rp = 0; rp < npairs; ++rp)
+    for (int j = 0; j < P.nblk; ++j) {
+      const int s = j * P.L;
+      const long long r = 2 * rp;
+      const bool second = r + 1 < rows;
+      // the bulk copies of the kernel's issue(): bytes [x_lo, x_hi) of both rows, stale bytes elsewhere
+      const int x_lo = ols::stage_x_lo_c1(s, P.pad);
+      int x_hi = s - P.pad + ols::kNB;
+      x_hi = ((x_hi < P.T ? x_hi : P.T) + 15) & ~15;
+      if (x_hi - x_lo > ols::kStageC1 || x_hi > (int)P.in_pitch) return -21;
+      std::fill(st0.begin(), st0.end(), (uint8_t)0xA5);
+      std::fill(st1.begin(), st1.end(), (uint8_t)0x5A);
+      std::memcpy(st0.data(), in + (size_t)r * P.in_pitch + x_lo, (size_t)(x_hi - x_lo));
+      if (second) std::memcpy(st1.data(), in + (size_t)(r + 1) * P.in_pitch + x_lo, (size_t)(x_hi - x_lo));
+      const bool interior = s - P.pad >= 0 && s - P.pad + ols::kNB <= P.T;
+      for (int lane = 0; lane < 32; ++lane) {
+        if (interior)
+          ols::load_block_staged_c1<true, DIL>(regs[lane], P, st0.data(), st1.data(), s, lane);
+        else
+          ols::load_block_staged_c1<false, DIL>(regs[lane], P, st0.data(), st1.data(), s, lane);
+      }
+      for (int q = 0; q < 4; ++q) {
+        for (int lane = 0; lane < 32; ++lane) dft<ols::kR, false>(regs[lane]);
+        if ((q & 1) == 0) {
+          for (int lane = 0; lane < 32; ++lane) ols::tw_write_col(regs[lane], lane, ex, P.tw + lane * ols::kTwStride);
+          for (int lane = 0; lane < 32; ++lane) ols::read_row(regs[lane], lane, ex);
+        } else if (q == 1) {
+          for (int lane = 0; lane < 32; ++lane) ols::mid_gains(regs[lane], lane, P.gains);
+        }
+      }
+      const ols::RowDst d0 = ols::make_row_dst(P, r), d1 = ols::make_row_dst(P, second ? r + 1 : r);
+      const float4 q0 = qa[(size_t)r], q1 = second ? qa[(size_t)r + 1] : make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int lane = 0; lane < 32; ++lane) ols::store_block_c1<DIL>(regs[lane], P, d0, d1, q0, q1, s, lane, second);
+    }
+  auto at = [&](int slot_logical, int w) -> float {
+    const int slot = ols::phys_slot(slot_logical, padq);
+    return inter[(size_t)(w >> 5) * P.blk_np * 32 + (size_t)slot * 32 + (w & 31)];
+  };
+  for (int r = 0; r < rows; ++r)
+    for (int w = 0; w < P.T; ++w) {
+      const float v = at(padpx + r, w);
+      out[(size_t)r * P.T + w] = v;
+      if (r >= 1 && r <= padpx && at(padpx - r, w) != v) return -1;
+      if (r >= rows - 1 - padpx && r <= rows - 2 && at(padpx + 2 * rows - 2 - r, w) != v) return -2;
+    }
+  return 0;
+}
+
+extern "C" int ols_emulate_rowpass_c(const uint8_t* in, int rows, int T, int C, float sigma, int ksize, int n_ref, int padq,
+                                     float* out) {
+  if (C == 1) return emulate_rowpass_c<1>(in, rows, T, sigma, ksize, n_ref, padq, out);
+  if (C == 3) return emulate_rowpass_c<3>(in, rows, T, sigma, ksize, n_ref, padq, out);
+  return -30;
+}
+
 // Whole blur through the emulated kernels: row pass into the panel intermediate (no bank-padding holes), column sums
 // -> synthetic row u -> its row pass -> column terms, then the column pass: the four TMA tile loads of an item are
 // emulated as a copy into the landing area under the 64-byte swizzle (col_landing_offset is the kernel's own map of it),
@@ -120,8 +224,8 @@ static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int 
   ols::RowParams P{};
   P.in = in;
   P.in_pitch = (long long)T * 4;
-  P.T = T;
-  P.pad = pad;
+  P.T = P.Tpx = T;
+  P.pad = P.padpx = pad;
   P.L = ols::kNB - 2 * pad;
   P.nblk = (T + P.L - 1) / P.L;
   P.nitems = (long long)rows * P.nblk * 2;

@@ -101,6 +101,69 @@ def test_emulated_rowpass_adversarial(emu, pattern):
 
 
 @pytest.fixture(scope="module")
+def emu_c(tmp_path_factory):
+    """ols_row_c1_kernel<.., DIL>: one-channel rows (DIL = 1) and RGB rows run as byte rows (DIL = 3)"""
+    so = tmp_path_factory.mktemp("ols3") / "libols_emu3.so"
+    cmd = ["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-w", "-I", "/usr/local/cuda/include",
+           "-I", os.path.join(ROOT, "libgaussianblur_b200", "csrc"), os.path.join(ROOT, "tests", "cpp", "ols_emulate.cpp"),
+           "-o", str(so)]
+    r = subprocess.run(cmd, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr[-3000:]
+    lib = ctypes.CDLL(str(so))
+    lib.ols_emulate_rowpass_c.restype = ctypes.c_int
+
+    def run(img, sigma, padq=0):
+        rows, cols, ch = img.shape
+        ksize, pad, n_rp, _, _, _ = go.plan_sizes(rows, cols, sigma)
+        img = np.ascontiguousarray(img)
+        out = np.empty((rows, cols * ch), np.float32)
+        rc = lib.ols_emulate_rowpass_c(img.ctypes.data_as(ctypes.c_void_p), rows, cols, ch, ctypes.c_float(sigma), ksize, n_rp,
+                                       padq, out.ctypes.data_as(ctypes.c_void_p))
+        assert rc == 0, f"emulation failed ({rc})"
+        want = np.empty((rows, cols * ch), np.float64)
+        for c in range(ch):
+            want[:, c::ch] = go.conv_lines(img[:, :, c].astype(np.float64), sigma, ksize, pad, n_rp)
+        return out, want, pad
+
+    return run
+
+
+@pytest.mark.parametrize("rows,cols,ch,sigma,padq", [
+    (70, 1920, 3, 10.0, 0),    # the video workload's row: 5760 bytes, pad 96 bytes, 7 blocks of 832
+    (71, 1920, 3, 5.0, 12),    # config 1's row, odd row count (the last pair has one row), slots with holes
+    (90, 1280, 3, 20.0, 0),    # pad 65 pixels = 195 bytes
+    (80, 4096, 3, 25.0, 0),    # pad 82 pixels = 246 bytes, close to the widest window byte rows take
+    (40, 336, 3, 3.0, 0),      # one block holds the whole padded row
+    (60, 3840, 3, 1.0, 0),     # pad 2
+    (66, 1920, 1, 10.0, 0),    # one channel through the same emulation
+    (41, 2016, 1, 20.0, 0),
+])
+def test_emulated_rowpass_interleaved_and_one_channel(emu_c, rows, cols, ch, sigma, padq):
+    img = go.synth_u8((rows, cols, ch), 0x33 + cols)
+    out, want, _ = emu_c(img, sigma, padq)
+    assert np.abs(out - want).max() <= TOL
+
+
+@pytest.mark.parametrize("pattern", ["altcols", "altcols_mixed", "const255", "impulse"])
+def test_emulated_rowpass_rgb_adversarial(emu_c, pattern):
+    """alternating pixel columns, per channel in opposite phase: the per-channel Nyquist terms of the byte-row pass"""
+    rows, cols, sigma = 40, 1920, 10.0
+    img = np.zeros((rows, cols, 3), np.uint8)
+    if pattern == "altcols":
+        img[:, ::2] = 255
+    elif pattern == "altcols_mixed":
+        img[:, ::2, 0] = 255
+        img[:, 1::2, 1] = 255
+        img[:, ::2, 2] = 128
+    elif pattern == "const255":
+        img[:] = 255
+    else:
+        img[20, 960, 1] = 255
+    out, want, _ = emu_c(img, sigma)
+    assert np.abs(out - want).max() <= TOL
+
+
+@pytest.fixture(scope="module")
 def emu_blur(emu, tmp_path_factory):
     so = tmp_path_factory.mktemp("ols2") / "libols_emu2.so"
     cmd = ["g++", "-std=c++17", "-O2", "-shared", "-fPIC", "-w", "-I", "/usr/local/cuda/include",
