@@ -112,7 +112,7 @@ struct gblur_plan {
   int last_row_kind = 0, last_col_kind = 0;  // kernels of the last pass launched: 0 = whole line, 1 = overlap-save
   // halo-sharded plan (gblur_plan_create_halo): this rank owns the column-pass blocks [blk0, blk1) of the padded column
   bool halo = false;
-  int h_L = 0, h_blk0 = 0, h_blk1 = 0;
+  int h_L = 0, h_blk0 = 0, h_blk1 = 0, h_ranks = 1;
   int h_out0 = 0, h_out1 = 0;  // image rows this rank writes
   int h_in0 = 0, h_in1 = 0;    // image rows this rank reads (its own plus the halo of pad rows on either side)
   int h_np = 0;                // slots of the local panel buffer
@@ -1091,6 +1091,7 @@ int gblur_plan_create_halo(gblur_plan** out, int device, int full_rows, int full
     }
   }
   p->halo = true;
+  p->h_ranks = n_ranks;
   p->h_L = 1024 - 2 * p->sz.pad;
   p->h_blk0 = o0 / p->h_L;
   p->h_blk1 = o1 > o0 ? (o1 + p->h_L - 1) / p->h_L : p->h_blk0;
@@ -1183,7 +1184,16 @@ int gblur_halo_rowpass_device(gblur_plan* p, const uint8_t* d_in_rows, int row_b
   a.row_offset = row_begin;
   if (!ols::row_eligible(p->ols_row, a))
     return fail(GBLUR_E_UNSUPPORTED, "halo sharding: geometry not eligible for the overlap-save kernels (alignment)");
-  CU(ols::launch_row(p->ols_row, a, p->num_sms, static_cast<cudaStream_t>(cuda_stream)));
+  // The block kernel is persistent and takes every register of the SMs it runs on: communication kernels enqueued
+  // beside it (the binding's halo send/recv and the all-reduce of the column sums) would wait for it to END. A few
+  // SMs left free (GBLUR_HALO_RESERVE_SMS, read once; default 4) let them run under it: measured on 8 B200, 32768^2
+  // sigma=50: 1.068 ms per step with 0, 1.036 with 4, 1.044 with 8 (profiles/r02/scale/n8_reserve*.json).
+  static const int reserve = [] {
+    const char* e = getenv("GBLUR_HALO_RESERVE_SMS");
+    return e ? std::max(0, atoi(e)) : 4;
+  }();
+  const int sms = std::max(1, p->num_sms - (p->h_ranks > 1 ? reserve : 0));
+  CU(ols::launch_row(p->ols_row, a, sms, static_cast<cudaStream_t>(cuda_stream)));
   p->last_row_kind = 1;
   return GBLUR_OK;
 }

@@ -458,27 +458,53 @@ class HaloShardedBlur:
                     dist.all_reduce(self.u, group=self.group)
             main.wait_stream(self.side)
             return self.out
+        prof = getattr(self, "profile", False)
+        marks = {}
+
+        def mark(name, stream):
+            if prof:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record(stream)
+                marks[name] = e
+
+        mark("start", main)
         with torch.cuda.stream(self.xs):
             self.xs.wait_stream(main)
             self._halo_exchange()
+            mark("halo_rows_arrived", self.xs)
         with torch.cuda.stream(self.side):
             self.side.wait_stream(main)
             self.u.zero_()
             plan.colsum(buf, self.u, stream=self.side)
+            mark("colsum_done", self.side)
         plan.rowpass(buf, o0, o1)
+        mark("rowpass_own_done", main)
         # the all-reduce is enqueued after the send/recv on every rank (one communicator: same order everywhere)
         with torch.cuda.stream(self.side):
             self.side.wait_stream(self.xs)
             if self.world > 1:
                 dist.all_reduce(self.u, group=self.group)
+            mark("allreduce_done", self.side)
         main.wait_stream(self.xs)
         if i0 < o0:
             plan.rowpass(buf, i0, o0)
         if o1 < i1:
             plan.rowpass(buf, o1, i1)
+        mark("rowpass_halo_done", main)
         main.wait_stream(self.side)
+        mark("terms_ready", main)
         plan.colpass(self.u, self.out)
+        mark("colpass_done", main)
+        if prof:
+            self._marks = marks
         return self.out
+
+    def phase_ms(self) -> dict:
+        """after a run_aligned() with self.profile = True: when each point of the three streams was reached, in ms from the
+        start of the call (device clocks)"""
+        torch.cuda.synchronize()
+        m = self._marks
+        return {"t_" + k: m["start"].elapsed_time(v) for k, v in m.items() if k != "start"}
 
     def _halo_exchange(self):
         """pad rows above and below from the ranks that own them (out_ranges partition), into the persistent buffer"""
