@@ -145,6 +145,10 @@ int gblur_halo_run_device(gblur_plan* plan, const uint8_t* d_in_rows, const int*
 /* the two halves of gblur_halo_run_device: the row pass of a sub-range of the rank's rows (so it can start on the rows
  * it holds while the halo is on the link), and column terms + column blocks */
 int gblur_halo_rowpass_device(gblur_plan* plan, const uint8_t* d_in_rows, int row_begin, int row_end, void* cuda_stream);
+/* the same over two row ranges (end_a <= begin_b; either may be empty) in ONE launch: the halo rows above and below the
+ * rank's band, once they have arrived (two short launches cost 2.5 x what the same rows cost inside one) */
+int gblur_halo_rowpass2_device(gblur_plan* plan, const uint8_t* d_in_rows, int begin_a, int end_a, int begin_b, int end_b,
+                               void* cuda_stream);
 int gblur_halo_colpass_device(gblur_plan* plan, const int* d_u_total, uint8_t* d_out, void* cuda_stream);
 
 /* ---- several GPUs of one box behind ONE handle, single process (csrc/multi_gpu.cpp) ----

@@ -33,7 +33,7 @@ EXPORTED_SYMBOLS = [
     "gblur_plan_panel_geometry", "gblur_band_panel_alloc", "gblur_ipc_export", "gblur_ipc_open", "gblur_ipc_close",
     "gblur_rowpass_peer_device", "gblur_colpass_panel_device", "gblur_panel_push_device",
     "gblur_halo_partition", "gblur_plan_create_halo", "gblur_halo_info", "gblur_halo_colsum_device", "gblur_halo_run_device",
-    "gblur_halo_rowpass_device", "gblur_halo_colpass_device",
+    "gblur_halo_rowpass_device", "gblur_halo_rowpass2_device", "gblur_halo_colpass_device",
     "gblur_mg_create", "gblur_mg_destroy", "gblur_mg_info", "gblur_mg_run_frames", "gblur_mg_run_bands", "gblur_mg_last_error",
     "gblur_colsum_noalloc",
     "gblur_dump_intermediate", "gblur_launch_count", "gblur_last_error", "gblur_device_count",
@@ -94,6 +94,7 @@ def lib():
         "gblur_colsum_noalloc": (C.c_int, [C.c_int, u8p, C.c_int, C.c_int, C.c_int, C.c_float, vp, vp]),
         "gblur_halo_run_device": (C.c_int, [vp, u8p, vp, u8p, vp]),
         "gblur_halo_rowpass_device": (C.c_int, [vp, u8p, C.c_int, C.c_int, vp]),
+        "gblur_halo_rowpass2_device": (C.c_int, [vp, u8p, C.c_int, C.c_int, C.c_int, C.c_int, vp]),
         "gblur_halo_colpass_device": (C.c_int, [vp, vp, u8p, vp]),
         "gblur_mg_create": (C.c_int, [pp, C.c_int, ip, C.c_int, C.c_int, C.c_int, C.c_float]),
         "gblur_mg_destroy": (None, [vp]),
@@ -347,6 +348,10 @@ class HaloPlan:
 
     def rowpass(self, d_in_rows, row_begin: int, row_end: int, stream=None):
         _check(lib().gblur_halo_rowpass_device(self._h, _ptr(d_in_rows), row_begin, row_end, _stream_ptr(stream)))
+
+    def rowpass2(self, d_in_rows, begin_a: int, end_a: int, begin_b: int, end_b: int, stream=None):
+        """row pass of two row ranges in one launch (the halo rows above and below the band)"""
+        _check(lib().gblur_halo_rowpass2_device(self._h, _ptr(d_in_rows), begin_a, end_a, begin_b, end_b, _stream_ptr(stream)))
 
     def colpass(self, d_u_total, d_out, stream=None):
         _check(lib().gblur_halo_colpass_device(self._h, _ptr(d_u_total), _ptr(d_out), _stream_ptr(stream)))

@@ -290,6 +290,8 @@ int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pi
     return fail(GBLUR_E_UNSUPPORTED, "pair-major panel layout, but the overlap-save row pass is not eligible");
   if (p->ols_row && ols::row_eligible(p->ols_row, a) &&
       ((blk && blk->pair_major) || p->ols_mode == 1 || (fused_single && ols::row_profitable(a, p->sz.n_rowpass)))) {
+    // (Leaving a few SMs out of this persistent grid for the column-term kernels on the side stream was measured and
+    // dropped: 0.5785 ms per 8K step with 0 SMs reserved, 0.5790 with 2, 0.5886 with 4 — profiles/r02/row_reserve.jsonl.)
     CU(ols::launch_row(p->ols_row, a, p->num_sms, s));
     p->last_row_kind = 1;
     return GBLUR_OK;
@@ -1164,24 +1166,25 @@ int gblur_halo_colsum_device(gblur_plan* p, const uint8_t* d_in_rows, int* d_u, 
 /* Row pass of the image rows [row_begin, row_end) (a sub-range of [in_row0, in_row1); d_in_rows still points at
  * in_row0) into the rank's panel buffer. A rank can start on the rows it holds while the halo rows are still on the
  * link and run them in a second call. */
-int gblur_halo_rowpass_device(gblur_plan* p, const uint8_t* d_in_rows, int row_begin, int row_end, void* cuda_stream) {
-  if (!p || !p->halo) return fail(GBLUR_E_INVALID, "not a halo plan");
-  if (p->h_out1 <= p->h_out0 || row_end <= row_begin) return GBLUR_OK;
-  if (!d_in_rows) return fail(GBLUR_E_INVALID, "null argument");
-  if (row_begin < p->h_in0 || row_end > p->h_in1) return fail(GBLUR_E_INVALID, "rows outside [in_row0, in_row1)");
+namespace {
+int halo_rowpass(gblur_plan* p, const uint8_t* d_in_rows, int a0, int a1, int b0, int b1, void* cuda_stream) {
   DeviceGuard guard(p->device);
   const int C = p->channels;
   const ColLaunch c = halo_col_launch(p, nullptr);
   RowLaunch a{};
   a.in_pitch = (long long)p->full_cols * C;
-  a.in = d_in_rows + (long long)(row_begin - p->h_in0) * a.in_pitch;
+  a.in = d_in_rows + (long long)(a0 - p->h_in0) * a.in_pitch;
   a.C = a.Cp = C;
   a.T = p->full_cols;
   a.pad = p->sz.pad;
-  a.rows_total = row_end - row_begin;
+  a.rows_total = (a1 - a0) + (b1 - b0);
   a.inter = p->d_halo_panel;
   a.blk = c.blk;
-  a.row_offset = row_begin;
+  a.row_offset = a0;
+  if (b1 > b0) {
+    a.split_at = a1 - a0;
+    a.split_gap = b0 - a1;
+  }
   if (!ols::row_eligible(p->ols_row, a))
     return fail(GBLUR_E_UNSUPPORTED, "halo sharding: geometry not eligible for the overlap-save kernels (alignment)");
   // The block kernel is persistent and takes every register of the SMs it runs on: communication kernels enqueued
@@ -1196,6 +1199,33 @@ int gblur_halo_rowpass_device(gblur_plan* p, const uint8_t* d_in_rows, int row_b
   CU(ols::launch_row(p->ols_row, a, sms, static_cast<cudaStream_t>(cuda_stream)));
   p->last_row_kind = 1;
   return GBLUR_OK;
+}
+}  // namespace
+
+int gblur_halo_rowpass_device(gblur_plan* p, const uint8_t* d_in_rows, int row_begin, int row_end, void* cuda_stream) {
+  if (!p || !p->halo) return fail(GBLUR_E_INVALID, "not a halo plan");
+  if (p->h_out1 <= p->h_out0 || row_end <= row_begin) return GBLUR_OK;
+  if (!d_in_rows) return fail(GBLUR_E_INVALID, "null argument");
+  if (row_begin < p->h_in0 || row_end > p->h_in1) return fail(GBLUR_E_INVALID, "rows outside [in_row0, in_row1)");
+  return halo_rowpass(p, d_in_rows, row_begin, row_end, row_end, row_end, cuda_stream);
+}
+
+/* The same over TWO row ranges [begin_a, end_a) and [begin_b, end_b) (end_a <= begin_b) in ONE launch: the halo rows
+ * above and below a rank's band once they have arrived. Two launches of 165 rows each cost 0.125 ms on a B200 where the
+ * same rows inside one launch cost 0.05. Either range may be empty. */
+int gblur_halo_rowpass2_device(gblur_plan* p, const uint8_t* d_in_rows, int begin_a, int end_a, int begin_b, int end_b,
+                               void* cuda_stream) {
+  if (!p || !p->halo) return fail(GBLUR_E_INVALID, "not a halo plan");
+  if (p->h_out1 <= p->h_out0) return GBLUR_OK;
+  if (!d_in_rows) return fail(GBLUR_E_INVALID, "null argument");
+  if (end_a < begin_a) end_a = begin_a;
+  if (end_b < begin_b) end_b = begin_b;
+  if (end_a == begin_a && end_b == begin_b) return GBLUR_OK;
+  if (end_a == begin_a) return gblur_halo_rowpass_device(p, d_in_rows, begin_b, end_b, cuda_stream);
+  if (end_b == begin_b) return gblur_halo_rowpass_device(p, d_in_rows, begin_a, end_a, cuda_stream);
+  if (begin_a < p->h_in0 || end_b > p->h_in1 || begin_b < end_a)
+    return fail(GBLUR_E_INVALID, "row ranges must be ordered, disjoint and inside [in_row0, in_row1)");
+  return halo_rowpass(p, d_in_rows, begin_a, end_a, begin_b, end_b, cuda_stream);
 }
 
 /* Column terms from the summed d_u_total, then the column blocks of the owned rows into d_out

@@ -56,6 +56,9 @@ struct RowLaunch {
   int npeers = 0;              // panel layout only: see RowParams::peer
   int peer_panels = 0;
   int row_offset = 0;
+  // overlap-save row pass only: the launch covers two row ranges; logical rows >= split_at lie split_gap rows further on
+  // in the input (and in the frame's row numbering). split_gap == 0: one range.
+  long long split_at = 0, split_gap = 0;
 };
 
 struct ColLaunch {

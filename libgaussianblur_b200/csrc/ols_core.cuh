@@ -59,6 +59,7 @@ struct RowParams {
   int blk_np, blk_padq;
   int pair_major;          // 1: the 32 floats of a panel row are ordered [pair][pixel][2] instead of [pixel][pair][2]
   int slot_origin;         // the panel buffer starts at this slot of the padded column (halo-sharded runs), else 0
+  long long split_at, split_gap;  // a launch over two row ranges: logical rows >= split_at lie split_gap rows further on
   int Tpx, padpx;          // interleaved 3-channel rows run as one byte row (T, pad, L in BYTES): pixels per row, pad in pixels
   long long blk_frame_stride;
   const float4* qa;        // per image row: (K[0] - K[N/2]) / N * alternating sum, one float per channel
@@ -67,6 +68,13 @@ struct RowParams {
 };
 
 __device__ __forceinline__ int phys_slot(int p, int padq) { return padq ? p + p / padq : p; }
+
+// Row of the input buffer (and of the frame stack) behind logical row r of the launch. One launch can cover two row
+// ranges — the halo rows above and below a rank's band (capi.cpp gblur_halo_rowpass2_device): two short launches cost
+// 0.125 ms where the same rows inside one launch cost 0.05 (profiles/r02/scale).
+__device__ __forceinline__ long long phys_row(const RowParams& P, long long r) {
+  return r + ((P.split_gap != 0 && r >= P.split_at) ? P.split_gap : 0);
+}
 
 // reflect_101 source pixel of padded position n, -1 in the zero tail (src/gaussianblur.cpp:217-228)
 __device__ __forceinline__ int reflect_src(int n, int pad, int T) {

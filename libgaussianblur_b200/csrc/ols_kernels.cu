@@ -55,11 +55,11 @@ constexpr int kAltsumWarps = 8;
 
 __global__ void __launch_bounds__(kAltsumWarps * 32)
     altsum_rows_kernel(const uint8_t* __restrict__ in, long long in_pitch, int T, int pad, float q, long long rows_total,
-                       float4* __restrict__ qa) {
+                       float4* __restrict__ qa, long long split_at, long long split_gap) {
   const int lane = threadIdx.x & 31;
   const long long r = (long long)blockIdx.x * kAltsumWarps + (threadIdx.x >> 5);
   if (r >= rows_total) return;
-  const uint32_t* row = reinterpret_cast<const uint32_t*>(in + r * in_pitch);
+  const uint32_t* row = reinterpret_cast<const uint32_t*>(in + (r + (r >= split_at ? split_gap : 0)) * in_pitch);
   int a[4] = {0, 0, 0, 0};
   altsum_lane(row, T, pad, lane, a);
 #pragma unroll
@@ -87,14 +87,15 @@ __global__ void __maxnreg__(MAXREG) ols_row_rgba_kernel(const __grid_constant__ 
     const long long r = bj / P.nblk;
     const int j = (int)(bj - r * P.nblk);
     const int s = j * P.L;
-    const uint32_t* row = reinterpret_cast<const uint32_t*>(P.in + r * P.in_pitch);
+    const long long rphys = phys_row(P, r);
+    const uint32_t* row = reinterpret_cast<const uint32_t*>(P.in + rphys * P.in_pitch);
     float2 c[kR];
     if (s - P.pad >= 0 && s - P.pad + kNB <= P.T)
       load_block<true>(c, P, row, s, pair, lane);
     else
       load_block<false>(c, P, row, s, pair, lane);
     block_passes(c, lane, ex, twl, gains);
-    const RowDst d = make_row_dst(P, r);
+    const RowDst d = make_row_dst(P, rphys);
     const float4 q4 = __ldg(P.qa + r);
     store_block(c, P, d, pair ? make_float2(q4.z, q4.w) : make_float2(q4.x, q4.y), s, pair, lane);
   }
@@ -134,7 +135,7 @@ __global__ void __maxnreg__(MAXREG) ols_row_rgba_staged_kernel(const __grid_cons
     x_hi = ((x_hi < P.T ? x_hi : P.T) + 3) & ~3;
     const uint32_t bytes = (uint32_t)(x_hi - x_lo) * 4u;
     mbar_expect_tx(bar, bytes);
-    bulk_g2s(stage, P.in + (long long)r * P.in_pitch + (long long)x_lo * 4, bytes, bar);
+    bulk_g2s(stage, P.in + phys_row(P, r) * P.in_pitch + (long long)x_lo * 4, bytes, bar);
   };
   int b = (int)blockIdx.x * WARPS + warp;
   if (lane == 0 && b < nblocks) issue(b);
@@ -144,7 +145,7 @@ __global__ void __maxnreg__(MAXREG) ols_row_rgba_staged_kernel(const __grid_cons
     const int s = (b - r * P.nblk) * P.L;
     const bool interior = s - P.pad >= 0 && s - P.pad + kNB <= P.T;
     const float4 q4 = __ldg(P.qa + r);
-    const RowDst d = make_row_dst(P, r);
+    const RowDst d = make_row_dst(P, phys_row(P, r));
     mbar_wait(bar, parity);
     parity ^= 1;
     // both channel pairs through ONE copy of the code (rolled: the item's instructions must stay inside the SM's
@@ -169,11 +170,11 @@ __global__ void __maxnreg__(MAXREG) ols_row_rgba_staged_kernel(const __grid_cons
 // ---- one-channel images (BASELINE.json config 4) ----
 __global__ void __launch_bounds__(kAltsumWarps * 32)
     altsum_rows_c1_kernel(const uint8_t* __restrict__ in, long long in_pitch, int T, int pad, float q, long long rows_total,
-                          float* __restrict__ qa) {
+                          float* __restrict__ qa, long long split_at, long long split_gap) {
   const int lane = threadIdx.x & 31;
   const long long r = (long long)blockIdx.x * kAltsumWarps + (threadIdx.x >> 5);
   if (r >= rows_total) return;
-  int a = altsum_lane_c1(in + r * in_pitch, T, pad, lane);
+  int a = altsum_lane_c1(in + (r + (r >= split_at ? split_gap : 0)) * in_pitch, T, pad, lane);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
   if (lane == 0) qa[r] = q * (float)a;
@@ -182,12 +183,12 @@ __global__ void __launch_bounds__(kAltsumWarps * 32)
 // rows of three interleaved channels (RGB): per row (q * sum_ch) as a float4 (w unused)
 __global__ void __launch_bounds__(kAltsumWarps * 32)
     altsum_rows_c3_kernel(const uint8_t* __restrict__ in, long long in_pitch, int Tpx, int padpx, float q, long long rows_total,
-                          float4* __restrict__ qa) {
+                          float4* __restrict__ qa, long long split_at, long long split_gap) {
   const int lane = threadIdx.x & 31;
   const long long r = (long long)blockIdx.x * kAltsumWarps + (threadIdx.x >> 5);
   if (r >= rows_total) return;
   int a[3] = {0, 0, 0};
-  altsum_lane_c3(in + r * in_pitch, Tpx, padpx, lane, a);
+  altsum_lane_c3(in + (r + (r >= split_at ? split_gap : 0)) * in_pitch, Tpx, padpx, lane, a);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     a[0] += __shfl_xor_sync(0xffffffffu, a[0], o);
@@ -233,9 +234,8 @@ __global__ void __maxnreg__(MAXREG) ols_row_c1_kernel(const __grid_constant__ Ro
     const uint32_t bytes = (uint32_t)(x_hi - x_lo);
     const bool second = 2 * rp + 1 < rows_total;
     mbar_expect_tx(bar, second ? 2 * bytes : bytes);
-    const uint8_t* src = P.in + 2 * rp * P.in_pitch + x_lo;
-    bulk_g2s(st0, src, bytes, bar);
-    if (second) bulk_g2s(st1, src + P.in_pitch, bytes, bar);
+    bulk_g2s(st0, P.in + phys_row(P, 2 * rp) * P.in_pitch + x_lo, bytes, bar);
+    if (second) bulk_g2s(st1, P.in + phys_row(P, 2 * rp + 1) * P.in_pitch + x_lo, bytes, bar);
   };
   long long b = (long long)blockIdx.x * WARPS + warp;
   if (lane == 0 && b < nitems) issue(b);
@@ -254,7 +254,7 @@ __global__ void __maxnreg__(MAXREG) ols_row_c1_kernel(const __grid_constant__ Ro
       qa0 = __ldg(P.qa + r);
       if (second) qa1 = __ldg(P.qa + r + 1);
     }
-    const RowDst d0 = make_row_dst(P, r), d1 = make_row_dst(P, second ? r + 1 : r);
+    const RowDst d0 = make_row_dst(P, phys_row(P, r)), d1 = make_row_dst(P, phys_row(P, second ? r + 1 : r));
     mbar_wait(bar, parity);
     parity ^= 1;
     float2 c[kR];
@@ -658,6 +658,8 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
   P.blk_frame_stride = a.blk.frame_stride;
   P.pair_major = a.blk.pair_major;
   P.slot_origin = a.blk.slot_origin;
+  P.split_at = a.split_gap ? a.split_at : (1LL << 62);
+  P.split_gap = a.split_gap;
   P.qa = p->d_qa;
   P.tw = p->d_tw;
   P.gains = p->d_gains;
@@ -665,7 +667,7 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
   const unsigned nb = (unsigned)((a.rows_total + kAltsumWarps - 1) / kAltsumWarps);
   if (a.C == 1) {
     altsum_rows_c1_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total,
-                                                                reinterpret_cast<float*>(p->d_qa));
+                                                                reinterpret_cast<float*>(p->d_qa), P.split_at, P.split_gap);
     count_launch();
     const cudaError_t e1 = cudaGetLastError();
     if (e1 != cudaSuccess) return e1;
@@ -678,13 +680,15 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
     P.pad = 3 * a.pad;
     P.L = kNB - 2 * P.pad;
     P.nblk = (P.T + P.L - 1) / P.L;
-    altsum_rows_c3_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total, p->d_qa);
+    altsum_rows_c3_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total, p->d_qa,
+                                                                P.split_at, P.split_gap);
     count_launch();
     const cudaError_t e3 = cudaGetLastError();
     if (e3 != cudaSuccess) return e3;
     return launch_blocks_c1<16, 128, 3>(P, a.rows_total, num_sms, stream);
   }
-  altsum_rows_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total, p->d_qa);
+  altsum_rows_kernel<<<nb, kAltsumWarps * 32, 0, stream>>>(a.in, a.in_pitch, a.T, a.pad, p->q, a.rows_total, p->d_qa,
+                                                           P.split_at, P.split_gap);
   count_launch();
   cudaError_t e = cudaGetLastError();
   if (e != cudaSuccess) return e;

@@ -486,10 +486,7 @@ class HaloShardedBlur:
                 dist.all_reduce(self.u, group=self.group)
             mark("allreduce_done", self.side)
         main.wait_stream(self.xs)
-        if i0 < o0:
-            plan.rowpass(buf, i0, o0)
-        if o1 < i1:
-            plan.rowpass(buf, o1, i1)
+        plan.rowpass2(buf, i0, o0, o1, i1)  # the halo rows above and below in one launch
         mark("rowpass_halo_done", main)
         main.wait_stream(self.side)
         mark("terms_ready", main)
