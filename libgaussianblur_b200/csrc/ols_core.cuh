@@ -639,6 +639,35 @@ __device__ __forceinline__ void colsum_lane(const uint8_t* __restrict__ in, long
   }
 }
 
+// the same for 16 consecutive byte columns (one 16-byte load per image row, four rows in flight): the column-sum kernel
+// is a pure stream over the u8 input, so bytes in flight per thread are what sets its speed
+__device__ __forceinline__ void colsum_lane16(const uint8_t* __restrict__ in, long long in_pitch, int x16, int r0, int r1,
+                                              int pad, int rows, int (&a)[16]) {
+  const uint8_t* p = in + (long long)r0 * in_pitch + 16LL * x16;
+  auto acc = [&](const uint4& v, int r) {
+    const int m = altsum_weight(r, pad, rows);
+    const uint32_t w4[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int k = 0; k < 16; ++k) a[k] += m * (int)((w4[k >> 2] >> (8 * (k & 3))) & 255u);
+  };
+  int r = r0;
+  for (; r + 4 <= r1; r += 4) {
+    const uint4 v0 = GBLUR_OLS_LDG(reinterpret_cast<const uint4*>(p));
+    const uint4 v1 = GBLUR_OLS_LDG(reinterpret_cast<const uint4*>(p + in_pitch));
+    const uint4 v2 = GBLUR_OLS_LDG(reinterpret_cast<const uint4*>(p + 2 * in_pitch));
+    const uint4 v3 = GBLUR_OLS_LDG(reinterpret_cast<const uint4*>(p + 3 * in_pitch));
+    acc(v0, r);
+    acc(v1, r + 1);
+    acc(v2, r + 2);
+    acc(v3, r + 3);
+    p += 4 * in_pitch;
+  }
+  for (; r < r1; ++r) {
+    acc(GBLUR_OLS_LDG(reinterpret_cast<const uint4*>(p)), r);
+    p += in_pitch;
+  }
+}
+
 // block loader for the synthetic row (int32 sums, always through the reflect map)
 __device__ __forceinline__ void load_block_u(float2 (&c)[kR], const int* __restrict__ u, int T, int pad, int s, int pair,
                                              int lane) {

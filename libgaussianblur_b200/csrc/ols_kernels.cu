@@ -288,6 +288,22 @@ __global__ void __launch_bounds__(128) colsum_kernel(const uint8_t* __restrict__
   for (int c = 0; c < 4; ++c) atomicAdd(u + 4 * x + c, a[c]);  // integer atomics: exact, order-independent
 }
 
+// 16 byte columns per thread (rows of whole 16-byte groups, 16-byte aligned). Measured in the fused 8K step, where this
+// kernel runs beside the row pass's own pre-kernel over the same input: 0.5785 -> 0.5690 ms per step.
+__global__ void __launch_bounds__(128) colsum16_kernel(const uint8_t* __restrict__ in, long long in_pitch, int groups16, int rows,
+                                                       int pad, int* __restrict__ u, int row_begin, int row_end, int row_base) {
+  const int x = blockIdx.x * 128 + threadIdx.x;
+  if (x >= groups16) return;
+  const int r0 = row_begin + blockIdx.y * kColsumRows;
+  const int r1 = min(row_end, r0 + kColsumRows);
+  int a[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) a[k] = 0;
+  colsum_lane16(in - (long long)row_base * in_pitch, in_pitch, x, r0, r1, pad, rows, a);
+#pragma unroll
+  for (int k = 0; k < 16; ++k) atomicAdd(u + 16 * x + k, a[k]);
+}
+
 // The row pass of the synthetic row: a few CTAs of kUWarps warps over the nblk * 2 items (every CTA forms u's own
 // alternating sum itself: T integers). Writes the column terms qc.
 constexpr int kUWarps = 16;
@@ -745,7 +761,15 @@ cudaError_t launch_colsum(const ColLaunch& a, const uint8_t* d_in, long long in_
                           int row_base, int rows, cudaStream_t stream) {
   const int cols = a.W / 4;
   if (row_end <= row_begin) return cudaSuccess;
-  const dim3 cgrid((unsigned)((cols + 127) / 128), (unsigned)((row_end - row_begin + kColsumRows - 1) / kColsumRows));
+  const unsigned gy = (unsigned)((row_end - row_begin + kColsumRows - 1) / kColsumRows);
+  if ((a.W % 16) == 0 && (in_pitch % 16) == 0 && (reinterpret_cast<uintptr_t>(d_in) % 16) == 0) {
+    const int g16 = a.W / 16;
+    colsum16_kernel<<<dim3((unsigned)((g16 + 127) / 128), gy), 128, 0, stream>>>(d_in, in_pitch, g16, rows, a.pad, d_u, row_begin,
+                                                                                  row_end, row_base);
+    count_launch();
+    return cudaGetLastError();
+  }
+  const dim3 cgrid((unsigned)((cols + 127) / 128), gy);
   colsum_kernel<<<cgrid, 128, 0, stream>>>(d_in, in_pitch, cols, rows, a.pad, d_u, row_begin, row_end, row_base);
   count_launch();
   return cudaGetLastError();
