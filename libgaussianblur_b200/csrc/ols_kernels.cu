@@ -222,28 +222,29 @@ __global__ void __maxnreg__(MAXREG) ols_row_c1_kernel(const __grid_constant__ Ro
   __syncthreads();
   const float2* twl = tw + lane * kTwStride;
   const float* qa = reinterpret_cast<const float*>(P.qa);
-  const long long npairs = (rows_total + 1) >> 1;
-  const long long nitems = npairs * P.nblk;
-  const long long stride = (long long)gridDim.x * WARPS;
-  auto issue = [&](long long b) {  // one lane: the bytes the block reads from both rows, clipped to the row
-    const long long rp = b / P.nblk;
-    const int s = (int)(b - rp * P.nblk) * P.L;
+  // 32-bit item arithmetic (launch_blocks_c1 refuses more than 2^31 items: a 64-bit division is ~70 instructions)
+  const unsigned npairs = (unsigned)((rows_total + 1) >> 1);
+  const unsigned nitems = npairs * (unsigned)P.nblk;
+  const unsigned stride = gridDim.x * WARPS;
+  auto issue = [&](unsigned b) {  // one lane: the bytes the block reads from both rows, clipped to the row
+    const unsigned rp = b / (unsigned)P.nblk;
+    const int s = (int)(b - rp * (unsigned)P.nblk) * P.L;
     const int x_lo = stage_x_lo_c1(s, P.pad);
     int x_hi = s - P.pad + kNB;
     x_hi = ((x_hi < P.T ? x_hi : P.T) + 15) & ~15;
     const uint32_t bytes = (uint32_t)(x_hi - x_lo);
-    const bool second = 2 * rp + 1 < rows_total;
+    const bool second = 2LL * rp + 1 < rows_total;
     mbar_expect_tx(bar, second ? 2 * bytes : bytes);
-    bulk_g2s(st0, P.in + phys_row(P, 2 * rp) * P.in_pitch + x_lo, bytes, bar);
-    if (second) bulk_g2s(st1, P.in + phys_row(P, 2 * rp + 1) * P.in_pitch + x_lo, bytes, bar);
+    bulk_g2s(st0, P.in + phys_row(P, 2LL * rp) * P.in_pitch + x_lo, bytes, bar);
+    if (second) bulk_g2s(st1, P.in + phys_row(P, 2LL * rp + 1) * P.in_pitch + x_lo, bytes, bar);
   };
-  long long b = (long long)blockIdx.x * WARPS + warp;
+  unsigned b = blockIdx.x * WARPS + warp;
   if (lane == 0 && b < nitems) issue(b);
   uint32_t parity = 0;
   for (; b < nitems; b += stride) {
-    const long long rp = b / P.nblk;
-    const int s = (int)(b - rp * P.nblk) * P.L;
-    const long long r = 2 * rp;
+    const unsigned rp = b / (unsigned)P.nblk;
+    const int s = (int)(b - rp * (unsigned)P.nblk) * P.L;
+    const long long r = 2LL * rp;
     const bool second = r + 1 < rows_total;
     const bool interior = s - P.pad >= 0 && s - P.pad + kNB <= P.T;
     float4 qa0 = make_float4(0.f, 0.f, 0.f, 0.f), qa1 = qa0;
@@ -426,13 +427,14 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
 
   // consecutive items = the blocks of one unit, then the neighbouring unit: the 2 * pad slots two blocks share and the
   // 128-byte lines two units share are fetched by CTAs that run at the same time (second reader hits L2)
-  auto decode = [&](long long it, int& f, int& unit, int& s) {
-    const long long fu = it / P.nblk;
-    s = (int)(it - fu * P.nblk) * P.L;
-    f = (int)(fu / P.nunits);
-    unit = P.unit0 + (int)(fu - (long long)f * P.nunits);
+  // (32-bit item arithmetic: launch_col refuses more than 2^31 items; a 64-bit division is ~70 instructions a thread)
+  auto decode = [&](unsigned it, int& f, int& unit, int& s) {
+    const unsigned fu = it / (unsigned)P.nblk;
+    s = (int)(it - fu * (unsigned)P.nblk) * P.L;
+    f = (int)(fu / (unsigned)P.nunits);
+    unit = P.unit0 + (int)(fu - (unsigned)f * (unsigned)P.nunits);
   };
-  auto request = [&](long long it) {  // one thread: the four landing boxes of item `it`
+  auto request = [&](unsigned it) {  // one thread: the four landing boxes of item `it`
     int f, unit, s;
     decode(it, f, unit, s);
     mbar_expect_tx(bar, kNB * kColFloats * 4);
@@ -457,13 +459,17 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
   }
   load_tables(tw, gains, P.tw, P.gains, tid, kColWarps * 32);
   __syncthreads();
-  long long it = blockIdx.x;
-  if (tid == 0 && it < P.nitems) request(it);
+  const unsigned nitems = (unsigned)P.nitems;
+  unsigned it = blockIdx.x;
+  if (tid == 0 && it < nitems) request(it);
   const float2* twl = tw + lane * kTwStride;
   uint32_t parity = 0;
-  for (; it < P.nitems; it += gridDim.x) {
+  for (; it < nitems; it += gridDim.x) {
     int f, unit, s;
     decode(it, f, unit, s);
+    // the item's column term: requested now, used after the last DFT (it was the kernel's only exposed global load)
+    const int pairidx = PAIR_MAJOR ? (unit * 4 + (w & 3)) * 2 + (w >> 2) : unit * kColWarps + w;
+    const float2 qc = P.qc ? __ldg(P.qc + f * P.qc_frame_stride + pairidx) : make_float2(0.f, 0.f);
     mbar_wait(bar, parity);
     parity ^= 1;
     float2 c[kR];
@@ -472,15 +478,13 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
     else
       read_col_nat(c, lane, w, region);
     __syncthreads();  // the landing area is consumed: it becomes the exchange slices
-    const long long next = it + gridDim.x;
+    const unsigned next = it + gridDim.x;
     block_passes(c, lane, ex, twl, gains, [&] {
       if (tid == 0) bulk_wait_read<0>();  // the previous item's stores have read the tile
       fence_proxy_async();                // order this thread's exchange traffic before the next TMA writes
       __syncthreads();                    // exchanges done: the region is free, and so is the tile
-      if (tid == 0 && next < P.nitems) request(next);  // lands under the last DFT and the epilogue
+      if (tid == 0 && next < nitems) request(next);  // lands under the last DFT and the epilogue
     });
-    const int pairidx = PAIR_MAJOR ? (unit * 4 + (w & 3)) * 2 + (w >> 2) : unit * kColWarps + w;
-    const float2 qc = P.qc ? __ldg(P.qc + f * P.qc_frame_stride + pairidx) : make_float2(0.f, 0.f);
     col_to_tile(c, qc, s, P.sign_origin, P.pad, P.L, PAIR_MAJOR ? 4 * (w & 3) + 2 * (w >> 2) : 2 * w, lane, tile);
     fence_proxy_async();  // the tile writes become visible to the async proxy
     __syncthreads();
@@ -640,6 +644,7 @@ cudaError_t launch_blocks_c1(const RowParams& P, long long rows_total, int num_s
   if (pd.err[device] != cudaSuccess) return pd.err[device];
   long long grid = (long long)num_sms * pd.per_sm[device];
   const long long need = (((rows_total + 1) >> 1) * P.nblk + WARPS - 1) / WARPS;
+  if ((need + grid) * WARPS >= (1LL << 31)) return cudaErrorNotSupported;  // the kernel counts items in 32 bits
   if (grid > need) grid = need;
   k<<<(unsigned)grid, WARPS * 32, smem, stream>>>(P, rows_total);
   count_launch();
@@ -849,6 +854,7 @@ cudaError_t launch_col(RowPlan* p, const ColLaunch& a, int num_sms, cudaStream_t
   P.nunits = (w_end - a.w_begin) / kColFloats;
   P.frames = a.frames;
   P.nitems = (long long)P.frames * P.nunits * P.nblk;
+  if (P.nitems + 2 * (long long)num_sms >= (1LL << 31)) return cudaErrorNotSupported;  // the kernel counts items in 32 bits
   P.panels_per_frame = (int)(a.blk.frame_stride / ((long long)a.blk.np * 32));
   P.st_rows_a = 256;
   P.st_na = P.L / 256;
