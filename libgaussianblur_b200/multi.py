@@ -57,6 +57,13 @@ def exchange(send: Sequence[torch.Tensor], recv: Sequence[torch.Tensor], group=N
             dist.send(send[peer].contiguous(), src, group=group)
 
 
+def panel_exchange_ok(cols: int, cp: int, world: int) -> bool:
+    """Can the fused / staged exchange (row pass stores into the owners' panel buffers) be used? It splits the float
+    columns evenly over the owners, so the pixel-column bands of shard_range must be equal and start on panel (32-float)
+    boundaries: cols = 64, world = 3, RGB passes the first condition alone and would shift columns."""
+    return (cols * cp) % (32 * world) == 0 and cols % world == 0 and ((cols // world) * cp) % 32 == 0 and world <= 8
+
+
 class BandShardedBlur:
     """One (rows x cols x channels) image sharded by row bands over the ranks of `group`.
 
@@ -212,7 +219,7 @@ class BandShardedBlur:
             return self
         # the panel exchange splits the float columns evenly over the owners: the pixel-column bands must be equal and
         # start on panel boundaries (cols = 64, world = 3, RGB passes the first test alone and would shift columns)
-        if fused and (cols * cp) % (32 * world) == 0 and cols % world == 0 and ((cols // world) * cp) % 32 == 0 and world <= 8:
+        if fused and panel_exchange_ok(cols, cp, world):
             # Fused exchange: every rank's row pass stores its lines straight into the panel buffer of the rank
             # that owns those columns (CUDA IPC mapping of the peers' buffers, NVLink stores). Two tiny
             # all-reduces on the compute stream order the passes across ranks: nobody overwrites a panel that

@@ -74,7 +74,21 @@ def _worker(rank, world, port, rows, cols, ch, alpha, sigma, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,ch,alpha", [(2, 3, False), (2, 4, False), (3, 4, True)])
+def test_panel_exchange_needs_equal_panel_aligned_bands():
+    """the fused / staged exchange is only taken when every rank's column band is the same whole number of panels
+    (round-1 advisor finding: cols = 64, world = 3, RGB passed the float-column test alone)"""
+    assert not multi.panel_exchange_ok(64, 3, 3)       # 192 float columns = 6 panels, but bands of 22 / 21 / 21 pixels
+    assert not multi.panel_exchange_ok(96, 3, 6)       # 16-pixel bands = 48 floats: not whole panels
+    assert multi.panel_exchange_ok(96, 4, 3)           # 32-pixel bands of 128 floats
+    assert multi.panel_exchange_ok(32768, 1, 8) and multi.panel_exchange_ok(65536, 3, 8)
+    assert not multi.panel_exchange_ok(32768, 1, 16)   # more ranks than the peer table holds
+    for cols, cp, world in ((64, 3, 3), (50, 3, 2), (96, 4, 3), (1920, 3, 4)):
+        if multi.panel_exchange_ok(cols, cp, world):
+            bands = [multi.shard_range(cols, world, r) for r in range(world)]
+            assert all((c0 * cp) % 32 == 0 and (c1 - c0) == cols // world for c0, c1 in bands)
+
+
+@pytest.mark.parametrize("world,ch,alpha", [(2, 3, False), (2, 4, False), (3, 4, True), (3, 3, False)])
 def test_band_sharded_exchange_matches_single_process(world, ch, alpha):
     rows, cols, sigma = 37, 50, 2.0
     img = go.synth_u8((rows, cols, ch), 0x77)
