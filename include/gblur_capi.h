@@ -159,12 +159,18 @@ int gblur_halo_colpass_device(gblur_plan* plan, const int* d_u_total, uint8_t* d
  *                        the hardware allows; geometry and sigma as in gblur_plan_create. Plans are built lazily.
  *   gblur_mg_run_frames  n_frames contiguous HWC frames in host memory, blurred in place; frames are cut into
  *                        contiguous blocks, one per GPU, each GPU streams its block (H2D || blur || D2H): no exchange.
- *   gblur_mg_run_bands   ONE image in host memory, blurred in place. Row bands: every GPU runs the row pass of its
- *                        band and stores the fp32 intermediate straight into the panel buffer of the GPU owning those
- *                        pixel columns (NVLink peer stores — the exchange is the row pass's own store), then every GPU
- *                        runs the column pass of its column band. Needs peer access, cols % n_gpus == 0 and
- *                        (cols / n_gpus) * Cp % 32 == 0; otherwise the whole image runs on the first device
- *                        (gblur_mg_info tells which).
+ *   gblur_mg_run_bands   ONE image in host memory, blurred in place, cut into row bands.
+ *                        Halo mode (1 channel, or 4 with alpha blurred; pad <= 256; cols * channels % 16 == 0): row
+ *                        bands for BOTH passes — every GPU takes its rows plus `pad` rows on either side from the host
+ *                        image, the host adds the GPUs' integer column sums (cols * channels values each) and hands the
+ *                        total back, every GPU returns its output rows. Nothing crosses between the GPUs and no peer
+ *                        access is needed (gblur_halo_*; GBLUR_MG_BANDS=exchange turns it off).
+ *                        Otherwise the exchange: every GPU runs the row pass of its band and stores the fp32
+ *                        intermediate straight into the panel buffer of the GPU owning those pixel columns (NVLink peer
+ *                        stores), then every GPU runs the column pass of its column band. Needs peer access,
+ *                        cols % n_gpus == 0 and (cols / n_gpus) * Cp % 32 == 0; otherwise the whole image runs on the
+ *                        first device. gblur_mg_info tells which, per alpha mode, after the first run: 2 = halo,
+ *                        1 = exchange, 0 = one device.
  * One call at a time per handle (calls on one handle serialise); errors: gblur_mg_last_error(). */
 typedef struct gblur_mg gblur_mg;
 int gblur_mg_create(gblur_mg** out, int n_gpus, const int* devices, int rows, int cols, int channels, float sigma);

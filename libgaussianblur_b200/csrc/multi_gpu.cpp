@@ -6,7 +6,9 @@
 // parallelism go to the GPUs of one box, behind plain C entry points a C++ caller of gaussianblur() can reach:
 //   * frames  — a batch is cut into contiguous blocks of frames, one block per GPU, no exchange at all
 //               (BASELINE.json config 3); one host thread per GPU drives that GPU's H2D || blur || D2H pipeline.
-//   * bands   — ONE image is cut into row bands (config 4/5): every GPU runs the row pass of its band and stores each
+//   * bands   — ONE image is cut into row bands (config 4/5). Where the overlap-save kernels take the shape the bands
+//               serve BOTH passes (halo mode, run_bands_halo below: pad rows from the host image + the host's sum of
+//               the integer column sums; nothing crosses between the GPUs). Otherwise: every GPU runs the row pass of its band and stores each
 //               128-byte line of the fp32 intermediate straight into the panel buffer of the GPU that owns those pixel
 //               columns (peer stores over NVLink, cudaDeviceEnablePeerAccess; the exchange IS the row pass's store, no
 //               collective), events order the passes across devices, and every GPU then runs the column pass of its
@@ -51,6 +53,14 @@ struct DevState {
   uint8_t* d_in = nullptr;   // the row band
   uint8_t* d_out = nullptr;  // the column band [rows][band_cols * C]
   size_t in_bytes = 0, out_bytes = 0;
+  // halo mode (row bands for both passes)
+  gblur_plan* halo_plan = nullptr;
+  int out0 = 0, out1 = 0, in0 = 0, in1 = 0;
+  uint8_t* d_hin = nullptr;   // image rows [in0, in1)
+  uint8_t* d_hout = nullptr;  // image rows [out0, out1)
+  int* d_u = nullptr;         // column sums: this device's rows, then the total
+  int* h_u = nullptr;         // pinned: this device's partial sums
+  cudaEvent_t ev_in = nullptr, ev_u = nullptr;
 };
 
 }  // namespace
@@ -61,6 +71,8 @@ struct gblur_mg {
   float sigma = 0.f;
   std::vector<DevState> dev;
   bool peer_ok = false;  // every pair of devices can address each other's memory
+  int halo_state = 0;    // 0 = not tried, 1 = ready, -1 = not eligible
+  int* h_usum = nullptr; // pinned: column sums over all devices
   std::mutex mu;         // one call at a time per handle
   std::string err;
 };
@@ -123,6 +135,96 @@ int ensure_band_state(gblur_mg* m, int alpha) {
       MG_CU(cudaMalloc(&d.d_out, outb));
       d.out_bytes = outb;
     }
+  }
+  return GBLUR_OK;
+}
+
+
+// ---- halo mode: row bands for BOTH passes (include/gblur_capi.h gblur_halo_*). Every device takes the rows of its
+// blocks plus `pad` rows on either side straight from the host image (the halo travels over PCIe twice: + 2 pad rows
+// per band), forms the column sums of its own rows, the host adds the n partial sums (cols * channels integers each)
+// and hands the total back, and every device runs its row pass and its column blocks. Nothing crosses between the
+// GPUs: no peer access needed, any width that is a whole number of 16-byte groups, contiguous copies both ways.
+// 1 channel, or 4 with alpha blurred; pad <= 256.
+bool halo_shape_ok(const gblur_mg* m, int alpha) {
+  if (m->n < 2) return false;
+  if (const char* e = getenv("GBLUR_MG_BANDS"))
+    if (std::strcmp(e, "exchange") == 0) return false;
+  if (!(m->channels == 1 || (m->channels == 4 && alpha))) return false;
+  if (((long long)m->cols * m->channels) % 16) return false;
+  int o0, o1, i0, i1;
+  return gblur_halo_partition(m->rows, m->cols, m->sigma, m->n, 0, &o0, &o1, &i0, &i1) == GBLUR_OK;
+}
+
+int ensure_halo_state(gblur_mg* m) {
+  if (m->halo_state != 0) return GBLUR_OK;
+  const size_t W = (size_t)m->cols * m->channels;
+  m->halo_state = -1;
+  for (int g = 0; g < m->n; ++g) {
+    DevState& d = m->dev[(size_t)g];
+    MG_CU(cudaSetDevice(d.device));
+    const int rc = gblur_plan_create_halo(&d.halo_plan, d.device, m->rows, m->cols, m->channels, m->sigma, m->n, g);
+    if (rc == GBLUR_E_UNSUPPORTED) return GBLUR_OK;  // stays -1: the caller falls back to the exchange
+    if (rc != GBLUR_OK) {
+      g_mg_err = gblur_last_error();
+      return rc;
+    }
+    MG_RC(gblur_halo_info(d.halo_plan, &d.out0, &d.out1, &d.in0, &d.in1));
+    if (d.out1 > d.out0) {
+      MG_CU(cudaMalloc(&d.d_hin, (size_t)(d.in1 - d.in0) * W));
+      MG_CU(cudaMalloc(&d.d_hout, (size_t)(d.out1 - d.out0) * W));
+    }
+    MG_CU(cudaMalloc(&d.d_u, W * sizeof(int)));
+    MG_CU(cudaHostAlloc(&d.h_u, W * sizeof(int), cudaHostAllocPortable));
+    MG_CU(cudaEventCreateWithFlags(&d.ev_in, cudaEventDisableTiming));
+    MG_CU(cudaEventCreateWithFlags(&d.ev_u, cudaEventDisableTiming));
+  }
+  MG_CU(cudaHostAlloc(&m->h_usum, W * sizeof(int), cudaHostAllocPortable));
+  m->halo_state = 1;
+  return GBLUR_OK;
+}
+
+int run_bands_halo(gblur_mg* m, uint8_t* hwc) {
+  const size_t W = (size_t)m->cols * m->channels;
+  // 1. rows + halo host -> device, column sums of the own rows back to the host, row pass
+  for (int g = 0; g < m->n; ++g) {
+    DevState& d = m->dev[(size_t)g];
+    MG_CU(cudaSetDevice(d.device));
+    if (d.out1 > d.out0) {
+      MG_CU(cudaMemcpyAsync(d.d_hin, hwc + (size_t)d.in0 * W, (size_t)(d.in1 - d.in0) * W, cudaMemcpyHostToDevice, d.stream));
+      MG_CU(cudaEventRecord(d.ev_in, d.stream));
+      MG_CU(cudaMemsetAsync(d.d_u, 0, W * sizeof(int), d.stream));
+      MG_RC(gblur_halo_colsum_device(d.halo_plan, d.d_hin, d.d_u, d.stream));
+      MG_CU(cudaMemcpyAsync(d.h_u, d.d_u, W * sizeof(int), cudaMemcpyDeviceToHost, d.stream));
+      MG_CU(cudaEventRecord(d.ev_u, d.stream));
+      MG_RC(gblur_halo_rowpass_device(d.halo_plan, d.d_hin, d.in0, d.in1, d.stream));
+    }
+  }
+  // 2. the integer column sums of the whole image (exact: the order of the additions does not matter)
+  std::memset(m->h_usum, 0, W * sizeof(int));
+  for (int g = 0; g < m->n; ++g) {
+    DevState& d = m->dev[(size_t)g];
+    if (d.out1 <= d.out0) continue;
+    MG_CU(cudaSetDevice(d.device));
+    MG_CU(cudaEventSynchronize(d.ev_u));
+    for (size_t i = 0; i < W; ++i) m->h_usum[i] += d.h_u[i];
+  }
+  // 3. column terms + column blocks; the output rows overwrite the input image, so no device may still be reading its
+  //    halo from the host buffer: every copy back waits for every copy in
+  for (int g = 0; g < m->n; ++g) {
+    DevState& d = m->dev[(size_t)g];
+    if (d.out1 <= d.out0) continue;
+    MG_CU(cudaSetDevice(d.device));
+    MG_CU(cudaMemcpyAsync(d.d_u, m->h_usum, W * sizeof(int), cudaMemcpyHostToDevice, d.stream));
+    MG_RC(gblur_halo_colpass_device(d.halo_plan, d.d_u, d.d_hout, d.stream));
+    for (int h = 0; h < m->n; ++h)
+      if (h != g && m->dev[(size_t)h].out1 > m->dev[(size_t)h].out0)
+        MG_CU(cudaStreamWaitEvent(d.stream, m->dev[(size_t)h].ev_in, 0));
+    MG_CU(cudaMemcpyAsync(hwc + (size_t)d.out0 * W, d.d_hout, (size_t)(d.out1 - d.out0) * W, cudaMemcpyDeviceToHost, d.stream));
+  }
+  for (int g = 0; g < m->n; ++g) {
+    MG_CU(cudaSetDevice(m->dev[(size_t)g].device));
+    MG_CU(cudaStreamSynchronize(m->dev[(size_t)g].stream));
   }
   return GBLUR_OK;
 }
@@ -213,9 +315,17 @@ void gblur_mg_destroy(gblur_mg* m) {
     }
     if (d.d_in) cudaFree(d.d_in);
     if (d.d_out) cudaFree(d.d_out);
+    if (d.halo_plan) gblur_plan_destroy(d.halo_plan);
+    if (d.d_hin) cudaFree(d.d_hin);
+    if (d.d_hout) cudaFree(d.d_hout);
+    if (d.d_u) cudaFree(d.d_u);
+    if (d.h_u) cudaFreeHost(d.h_u);
+    if (d.ev_in) cudaEventDestroy(d.ev_in);
+    if (d.ev_u) cudaEventDestroy(d.ev_u);
     if (d.ev_row) cudaEventDestroy(d.ev_row);
     if (d.stream) cudaStreamDestroy(d.stream);
   }
+  if (m->h_usum) cudaFreeHost(m->h_usum);
   cudaSetDevice(prev);
   delete m;
 }
@@ -224,8 +334,15 @@ int gblur_mg_info(const gblur_mg* m, int* n_gpus, int* peer_access, int* bands_f
   if (!m) return mg_fail(GBLUR_E_INVALID, "null handle");
   if (n_gpus) *n_gpus = m->n;
   if (peer_access) *peer_access = m->peer_ok ? 1 : 0;
-  if (bands_fused_alpha0) *bands_fused_alpha0 = (m->n > 1 && m->peer_ok && bands_divisible(m, 0)) ? 1 : 0;
-  if (bands_fused_alpha1) *bands_fused_alpha1 = (m->n > 1 && m->peer_ok && bands_divisible(m, 1)) ? 1 : 0;
+  // 2 = halo mode (row bands for both passes), 1 = row bands + peer-store exchange, 0 = whole image on one device
+  for (int a = 0; a < 2; ++a) {
+    int* out = a ? bands_fused_alpha1 : bands_fused_alpha0;
+    if (!out) continue;
+    if (halo_shape_ok(m, a) && m->halo_state >= 0)
+      *out = 2;
+    else
+      *out = (m->n > 1 && m->peer_ok && bands_divisible(m, a)) ? 1 : 0;
+  }
   return GBLUR_OK;
 }
 
@@ -273,6 +390,10 @@ int gblur_mg_run_bands(gblur_mg* m, uint8_t* hwc, int apply_to_alpha) {
     int d;
     ~Restore() { cudaSetDevice(d); }
   } restore{prev};
+  if (halo_shape_ok(m, alpha)) {
+    MG_RC(ensure_halo_state(m));
+    if (m->halo_state == 1) return run_bands_halo(m, hwc);
+  }
   if (m->n == 1 || !m->peer_ok || !bands_divisible(m, alpha)) {
     // one GPU, no peer access, or a width the panel exchange cannot split evenly: the whole image on the first device
     DevState& d = m->dev[0];

@@ -87,7 +87,8 @@ int main(int argc, char** argv) {
       std::printf("frames: %d frames over %d GPUs identical to one-plan results\n", nf, n);
     }
   }
-  {  // ---- bands, one channel ----
+  for (int mode = 0; mode < 2; ++mode) {  // ---- bands, one channel: halo mode, then the peer-store exchange ----
+    if (mode == 1) setenv("GBLUR_MG_BANDS", "exchange", 1);
     const int rows = side, cols = side;
     std::vector<uint8_t> img((size_t)rows * cols), want;
     fill(img, 0x77);
@@ -95,24 +96,48 @@ int main(int argc, char** argv) {
     gblur_mg* mg = nullptr;
     MG(gblur_mg_create(&mg, n, nullptr, rows, cols, 1, 50.0f));
     int ng = 0, peer = 0, sh0 = 0, sh1 = 0;
-    MG(gblur_mg_info(mg, &ng, &peer, &sh0, &sh1));
     MG(gblur_mg_run_bands(mg, img.data(), 0));  // first call builds the plans
+    MG(gblur_mg_info(mg, &ng, &peer, &sh0, &sh1));
     std::vector<uint8_t> again = want;
     const auto t0 = std::chrono::steady_clock::now();
     MG(gblur_mg_run_bands(mg, again.data(), 0));
     const double secs = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     gblur_mg_destroy(mg);
+    unsetenv("GBLUR_MG_BANDS");
     if (std::memcmp(img.data(), again.data(), img.size()) != 0) {
       std::printf("FAIL bands: two runs differ\n");
       return 1;
     }
-    std::printf("bands: %d x %d x 1 sigma 50 on %d GPUs (peer access %d, row-band sharded %d): %.1f ms host to host\n", rows, cols, ng,
-                peer, sh0, secs * 1e3);
+    std::printf("bands: %d x %d x 1 sigma 50 on %d GPUs (peer access %d, sharding %d: 2 = halo, 1 = exchange, 0 = one GPU): %.1f ms host to host\n",
+                rows, cols, ng, peer, sh0, secs * 1e3);
+    if (ng > 1 && sh0 != (mode == 0 ? 2 : (peer ? 1 : 0))) {
+      std::printf("FAIL bands: expected the %s path\n", mode == 0 ? "halo" : "exchange");
+      return 1;
+    }
     if (ref_plane) {
       ref_plane(want.data(), rows, cols, 50.0f);
       size_t nd;
       const int mx = max_diff(want.data(), img.data(), img.size(), &nd);
       std::printf("bands: vs reference max |delta| = %d (%zu of %zu bytes differ)\n", mx, nd, img.size());
+      if (mx > 1) return 1;
+    }
+  }
+  {  // ---- bands, RGBA with all four channels blurred: halo mode with pair-major panels ----
+    const int rows = 6000, cols = 2064, C = 4;
+    std::vector<uint8_t> img((size_t)rows * cols * C), want;
+    fill(img, 0x55);
+    want = img;
+    gblur_mg* mg = nullptr;
+    MG(gblur_mg_create(&mg, n, nullptr, rows, cols, C, 20.0f));
+    MG(gblur_mg_run_bands(mg, img.data(), 1));
+    int ng = 0, peer = 0, sh0 = 0, sh1 = 0;
+    MG(gblur_mg_info(mg, &ng, &peer, &sh0, &sh1));
+    gblur_mg_destroy(mg);
+    if (ref_blur) {
+      ref_blur(want.data(), rows, cols, C, 20.0f, 1);
+      size_t nd;
+      const int mx = max_diff(want.data(), img.data(), img.size(), &nd);
+      std::printf("bands RGBA, alpha blurred (sharding %d): vs reference max |delta| = %d (%zu bytes differ)\n", sh1, mx, nd);
       if (mx > 1) return 1;
     }
   }
