@@ -109,6 +109,8 @@ struct gblur_plan {
   int ols_mode = 2;
   // overlap-save column pass, same plan object. GBLUR_COL_OLS: 1 = wherever eligible, 0 = never, unset = kColOlsAuto
   int ols_col_mode = 0;
+  bool last_alpha_restore = false;  // the last fused run took that route (gblur_dump_intermediate)
+  bool ols_alpha_restore = true;  // RGBA, alpha not blurred: four channels through the overlap-save passes + alpha restore
   int last_row_kind = 0, last_col_kind = 0;  // kernels of the last pass launched: 0 = whole line, 1 = overlap-save
   // halo-sharded plan (gblur_plan_create_halo): this rank owns the column-pass blocks [blk0, blk1) of the padded column
   bool halo = false;
@@ -226,6 +228,7 @@ int create_common(gblur_plan** out, int device, int full_rows, int full_cols, in
     if (p->ols_mode != 0 && !band) {
       const char* ec = getenv("GBLUR_COL_OLS");
       p->ols_col_mode = ec ? (atoi(ec) > 0 ? 1 : 0) : kColOlsAuto;
+      if (const char* ea = getenv("GBLUR_OLS_ALPHA_RESTORE")) p->ols_alpha_restore = atoi(ea) > 0;
       // three channels: the row pass only, on byte rows (block gains of the taps spread three bytes apart)
       const cudaError_t ce = channels == 3 ? ols::row_plan_create(&p->ols_row, taps, sz.n_rowpass, 0, 3)
                                            : ols::row_plan_create(&p->ols_row, taps, sz.n_rowpass, sz.n_colpass);
@@ -325,7 +328,7 @@ bool panel_tensor_map(gblur_plan* p, const float* base, const BlockedLayout& b, 
 // of the previous launch on this plan (column bands of one image)
 int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d_out, long long out_pitch, int frames,
                 int alpha, cudaStream_t s, const BlockedLayout* blk = nullptr, int w_begin = 0, int w_end = 0,
-                const uint8_t* ols_in = nullptr, bool ols_terms = true) {
+                const uint8_t* ols_in = nullptr, bool ols_terms = true, const uint8_t* alpha_src = nullptr) {
   const int cp = processed_channels(p, alpha);
   ColLaunch a{};
   a.inter = d_inter;
@@ -351,6 +354,10 @@ int run_colpass(gblur_plan* p, const float* d_inter, long long pitch, uint8_t* d
       a.tma_rows = p->tmap_rows;
     }
   }
+  a.alpha_src = alpha_src;
+  a.alpha_pitch = (long long)p->full_cols * p->channels;
+  if (alpha_src && !(ols_in && blk && blk->padq == 0 && ols_col_wanted(p, cp, frames) && ols::col_eligible(p->ols_row, a)))
+    return fail(GBLUR_E_UNSUPPORTED, "alpha pass-through on four channels needs the overlap-save column pass");
   if (ols_in && blk && blk->padq == 0 && ols_col_wanted(p, cp, frames) && ols::col_eligible(p->ols_row, a)) {
     if (ols_terms) CU(ols::launch_col_terms(p->ols_row, a, ols_in, (long long)p->full_cols * p->channels, s));
     CU(ols::launch_col(p->ols_row, a, p->num_sms, s));
@@ -469,14 +476,30 @@ struct FusedCtx {
   const BlockedLayout* bp = nullptr;  // null: row-major intermediate
   long long pitch = 0;
   int cp = 0;
+  // RGBA with alpha passed through, on the overlap-save passes: all four channels are transformed (cp = 4, the passes
+  // are called with alpha = 1) and the column kernel restores the input's alpha byte in its output tile
+  bool alpha_restore = false;
+  int alpha = 0;  // what the passes are called with
+  bool ols_col = false;  // the column pass runs as overlap-save blocks (pair-major / hole-free panel layout)
 };
 
 // Workspace, layout choice and (when the layout changes) the zero fill, ordered on stream s.
-int fused_prepare(gblur_plan* p, int n_frames, int apply_to_alpha, cudaStream_t s, FusedCtx& c) {
+// io_aligned: the caller's image pointers are 16-byte aligned (the overlap-save column pass moves its tiles with TMA);
+// unaligned buffers keep the whole-line kernels instead of failing later
+int fused_prepare(gblur_plan* p, int n_frames, int apply_to_alpha, cudaStream_t s, FusedCtx& c, bool io_aligned = true) {
   if (p->band) return fail(GBLUR_E_INVALID, "band plans run through gblur_rowpass_device / gblur_colpass_device");
   if (n_frames < 1 || n_frames > p->max_frames)
     return fail(GBLUR_E_INVALID, "n_frames %d outside [1, %d]", n_frames, p->max_frames);
   c.cp = processed_channels(p, apply_to_alpha);
+  c.alpha = apply_to_alpha ? 1 : 0;
+  if (p->channels == 4 && !apply_to_alpha && n_frames == 1 && p->ols_alpha_restore && io_aligned &&
+      ols_col_wanted(p, 4, n_frames)) {
+    // a fourth channel costs the block kernels a third more work and they are still well ahead of the whole-line
+    // kernels on three channels (GBLUR_OLS_ALPHA_RESTORE=0 at plan creation keeps the whole-line path)
+    c.alpha_restore = true;
+    c.alpha = 1;
+    c.cp = 4;
+  }
   // workspace sized for the widest layout (all channels processed)
   const BlockedLayout widest = blocked_layout(p, p->channels);
   const size_t rowmajor_floats = (size_t)p->rows * (size_t)default_pitch((long long)p->cols * p->channels);
@@ -488,7 +511,8 @@ int fused_prepare(gblur_plan* p, int n_frames, int apply_to_alpha, cudaStream_t 
     const char* e = getenv("GBLUR_LAYOUT");
     return e && std::strcmp(e, "rowmajor") == 0;
   }();
-  const bool ols_col = ols_col_wanted(p, c.cp, n_frames);
+  const bool ols_col = io_aligned && ols_col_wanted(p, c.cp, n_frames);
+  c.ols_col = ols_col;
   c.blk = blocked_layout(p, c.cp, ols_col);
   // single-GPU run with a cluster column pass: the row-major intermediate is a little faster (cheaper stores)
   static const bool panel_forced = [] {
@@ -505,6 +529,7 @@ int fused_prepare(gblur_plan* p, int n_frames, int apply_to_alpha, cudaStream_t 
   }
   p->inter_cp = layout_tag;
   p->last_cp = c.cp;
+  p->last_alpha_restore = c.alpha_restore;
   p->last_frames = n_frames;
   return GBLUR_OK;
 }
@@ -516,13 +541,14 @@ static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_f
   DeviceGuard guard(p->device);
   cudaStream_t s = static_cast<cudaStream_t>(cuda_stream);
   FusedCtx c;
-  int rc = fused_prepare(p, n_frames, apply_to_alpha, s, c);
+  const bool io_aligned = ((reinterpret_cast<uintptr_t>(d_in) | reinterpret_cast<uintptr_t>(d_out)) & 15) == 0;
+  int rc = fused_prepare(p, n_frames, apply_to_alpha, s, c, io_aligned);
   if (rc != GBLUR_OK) return rc;
   // The column terms of the overlap-save column pass depend on the input image only: in a two-stage run they are
   // computed on a side stream while the row pass runs (one pass over the u8 input, hidden under a pass that is not
   // memory-bound), and joined before the column blocks.
   bool terms_forked = false;
-  if (stages == 3 && n_frames == 1 && c.bp && c.blk.padq == 0 && ols_col_wanted(p, c.cp, n_frames)) {
+  if (stages == 3 && n_frames == 1 && c.bp && c.blk.padq == 0 && c.ols_col) {
     if (!p->s_side) CU(cudaStreamCreateWithFlags(&p->s_side, cudaStreamNonBlocking));
     if (!p->ev_fork) CU(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
     if (!p->ev_join) CU(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
@@ -539,15 +565,17 @@ static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_f
     terms_forked = true;
   }
   if (stages & 1) {
-    rc = run_rowpass(p, d_in, p->d_inter, c.pitch, n_frames, apply_to_alpha, s, c.bp, 0, 0, 0, 0, n_frames == 1);
+    rc = run_rowpass(p, d_in, p->d_inter, c.pitch, n_frames, c.alpha, s, c.bp, 0, 0, 0, 0, n_frames == 1);
     if (rc != GBLUR_OK) return rc;
   }
   if (!(stages & 2)) return GBLUR_OK;
   if (terms_forked) CU(cudaStreamWaitEvent(s, p->ev_join, 0));
   if (d_in != d_out && c.cp < p->channels)
     CU(launch_copy_channel(d_in, d_out, (long long)p->rows * p->cols * n_frames, p->channels, 3, s));
-  return run_colpass(p, p->d_inter, c.pitch, d_out, (long long)p->cols * p->channels, n_frames, apply_to_alpha, s, c.bp,
-                     0, 0, n_frames == 1 ? d_in : nullptr, !terms_forked);
+  // alpha restore: the column kernel takes the alpha bytes from the input image (d_out itself when the call is in place:
+  // an item reads exactly the bytes it then overwrites); a stage-2-only call finds them in d_in as well
+  return run_colpass(p, p->d_inter, c.pitch, d_out, (long long)p->cols * p->channels, n_frames, c.alpha, s, c.bp,
+                     0, 0, n_frames == 1 ? d_in : nullptr, !terms_forked, c.alpha_restore ? d_in : nullptr);
 }
 
 int gblur_run_batch_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
@@ -743,7 +771,7 @@ int run_host_single_pipelined(gblur_plan* p, uint8_t* hwc, int alpha, int K) {
     CU(cudaMemcpyAsync(p->d_stage + r0 * row_bytes, src, (size_t)(r1 - r0) * row_bytes, cudaMemcpyHostToDevice, p->s_in));
     CU(cudaEventRecord(p->events[k], p->s_in));
     CU(cudaStreamWaitEvent(sc, p->events[k], 0));
-    rc = run_rowpass(p, p->d_stage, p->d_inter, c.pitch, 1, alpha, sc, c.bp, 0, 0, r0, r1 - r0, true);
+    rc = run_rowpass(p, p->d_stage, p->d_inter, c.pitch, 1, c.alpha, sc, c.bp, 0, 0, r0, r1 - r0, true);
     if (rc != GBLUR_OK) return rc;
   }
   // column bands on 32-pixel boundaries (=> float-column boundaries on multiples of 32 for any Cp)
@@ -761,8 +789,8 @@ int run_host_single_pipelined(gblur_plan* p, uint8_t* hwc, int alpha, int K) {
   for (int x0 = 0; x0 < p->cols && nb < 64; x0 += px_per_band, ++e, ++nb) {
     const int x1 = std::min(p->cols, x0 + px_per_band);
     bands[nb] = {x0, x1};
-    rc = run_colpass(p, p->d_inter, c.pitch, p->d_stage, (long long)row_bytes, 1, alpha, sc, c.bp, x0 * c.cp, x1 * c.cp,
-                     p->d_stage, x0 == 0);
+    rc = run_colpass(p, p->d_inter, c.pitch, p->d_stage, (long long)row_bytes, 1, c.alpha, sc, c.bp, x0 * c.cp, x1 * c.cp,
+                     p->d_stage, x0 == 0, c.alpha_restore ? p->d_stage : nullptr);
     if (rc != GBLUR_OK) return rc;
     CU(cudaEventRecord(p->events[e], sc));
     CU(cudaStreamWaitEvent(p->s_out, p->events[e], 0));
@@ -1257,7 +1285,10 @@ int gblur_dump_intermediate(gblur_plan* p, float* host_out, int apply_to_alpha) 
   if (!p || !host_out) return fail(GBLUR_E_INVALID, "null argument");
   if (!p->d_inter || p->inter_cp == 0) return fail(GBLUR_E_INVALID, "no run has happened on this plan");
   DeviceGuard guard(p->device);
-  const int cp = processed_channels(p, apply_to_alpha);
+  int cp = processed_channels(p, apply_to_alpha);
+  // RGBA with alpha passed through on the overlap-save passes: the intermediate holds all four channels
+  const bool drop_alpha = (cp == 3 && p->channels == 4 && p->inter_cp == 4 + 16 && p->last_alpha_restore);
+  if (drop_alpha) cp = 4;
   if (cp != p->inter_cp && -cp != p->inter_cp && cp + 16 != p->inter_cp)
     return fail(GBLUR_E_INVALID, "last run used a different apply_to_alpha");
   if (p->inter_cp < 0) {  // row-major layout
@@ -1278,7 +1309,11 @@ int gblur_dump_intermediate(gblur_plan* p, float* host_out, int apply_to_alpha) 
     for (long long x = 0; x < w; ++x) {
       const int k = (int)(x % 32);  // pixel-major position 4 px + 2 pair + c  ->  pair-major 16 pair + 2 px + c
       const int kk = b.pair_major ? ((k >> 1) & 1) * 16 + (k >> 2) * 2 + (k & 1) : k;
-      host_out[(size_t)r * w + x] = blk[(size_t)((x / 32) * b.np + slot) * 32 + (size_t)kk];
+      const float v = blk[(size_t)((x / 32) * b.np + slot) * 32 + (size_t)kk];
+      if (!drop_alpha)
+        host_out[(size_t)r * w + x] = v;
+      else if ((x & 3) != 3)  // [rows][cols * 3]: the caller asked for the three blurred channels
+        host_out[(size_t)r * (w / 4 * 3) + (x >> 2) * 3 + (x & 3)] = v;
     }
   }
   return GBLUR_OK;

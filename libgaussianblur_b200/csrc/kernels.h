@@ -77,6 +77,11 @@ struct ColLaunch {
   BlockedLayout blk;
   int panel_in = 0;  // the column pass of a cluster plan reads the panel layout through its loader
   int row_origin = 0;  // halo-sharded runs: image row of the first row of `out` (and of slot blk.slot_origin + pad)
+  // overlap-save column pass of an RGBA image whose alpha is NOT blurred: all four channels run through both passes and
+  // the column kernel puts the ORIGINAL alpha byte (row r, pixel x: alpha_src[r * alpha_pitch + 4 x + 3]) into its output
+  // tile; alpha_src may be the output buffer itself (in place: an item reads exactly the bytes it is about to overwrite)
+  const uint8_t* alpha_src = nullptr;
+  long long alpha_pitch = 0;
   const CUtensorMap* tmap = nullptr;  // host copy of the tensor map over the panel intermediate (TMA gather), or null
   int tma_rows = 0;
 };

@@ -555,6 +555,8 @@ struct ColParams {
   int st_na, st_rows_a, st_rows_b;  // store boxes: st_na boxes of st_rows_a rows, then one of st_rows_b rows (0 = none)
   int sign_origin;          // parity offset of the block positions (halo-sharded runs: the buffer's first slot), else 0
   long long qc_frame_stride;        // float2 per frame of qc
+  const uint8_t* alpha_src; // RGBA with alpha passed through: the image the alpha bytes come from (else null)
+  long long alpha_pitch;
   const float2* qc;         // per column pair 2x + pair: (K[0] - K[N/2]) / N of the column length * row pass of u
   const float2* tw;
   const float* gains;
@@ -604,8 +606,10 @@ __device__ __forceinline__ uint32_t to_u8x2(float2 v) {
 // lane l, register j hold 1024 y[n], n = (32 - l) + 32 (31 - j): two bytes per output row into tile[n - pad][2w, 2w+1]
 // wb: byte offset of the warp's two outputs in the 16-byte tile row (pair-major RGBA: 4 (w & 3) + 2 (w >> 2): pixel
 // w & 3, channels 2g, 2g + 1; natural order: 2 w)
+// keep_hi: write only the first of the two bytes — the second one (alpha of an RGBA image whose alpha is passed through)
+// is already in the tile, put there by a TMA load of the input image
 __device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, int s, int sign_origin, int pad, int L, int wb,
-                                            int lane, unsigned char* __restrict__ tile) {
+                                            int lane, unsigned char* __restrict__ tile, bool keep_hi = false) {
   const int l1 = kR - lane;
   const float sg = ((s + sign_origin + l1) & 1) ? -1.0f : 1.0f;
   const float2 add = make_float2(fmaf(qc.x, sg, 0.5f), fmaf(qc.y, sg, 0.5f));
@@ -613,13 +617,21 @@ __device__ __forceinline__ void col_to_tile(const float2 (&c)[kR], float2 qc, in
   unsigned char* tp = tile + (l1 - pad) * kColFloats + wb;
 #pragma unroll
   for (int i = 0; i < kR; ++i) {
-    if (kR * i >= lo && kR * i < hi)
-      *reinterpret_cast<uint16_t*>(tp + i * (kR * kColFloats)) = (uint16_t)to_u8x2(pk_add(c[kR - 1 - i], add));
+    if (kR * i >= lo && kR * i < hi) {
+      const uint32_t v = to_u8x2(pk_add(c[kR - 1 - i], add));
+      if (keep_hi)
+        tp[i * (kR * kColFloats)] = (unsigned char)v;
+      else
+        *reinterpret_cast<uint16_t*>(tp + i * (kR * kColFloats)) = (uint16_t)v;
+    }
   }
   if (pad == 0 && lane == 0) {
     const float sg0 = ((s + sign_origin) & 1) ? -1.0f : 1.0f;
-    *reinterpret_cast<uint16_t*>(tile + wb) =
-        (uint16_t)to_u8x2(make_float2(c[0].x + fmaf(qc.x, sg0, 0.5f), c[0].y + fmaf(qc.y, sg0, 0.5f)));
+    const uint32_t v = to_u8x2(make_float2(c[0].x + fmaf(qc.x, sg0, 0.5f), c[0].y + fmaf(qc.y, sg0, 0.5f)));
+    if (keep_hi)
+      tile[wb] = (unsigned char)v;
+    else
+      *reinterpret_cast<uint16_t*>(tile + wb) = (uint16_t)v;
   }
 }
 

@@ -35,9 +35,10 @@ struct RowPlan {
   float2* d_qc = nullptr;   // 2 * cols column-pair terms
   int u_cols = 0;
   // tensor maps of the column pass, rebuilt when the buffers or the geometry change
-  CUtensorMap in_map, out_a, out_b;
+  CUtensorMap in_map, out_a, out_b, alpha_a, alpha_b;
   const void* map_inter = nullptr;
   const void* map_out = nullptr;
+  const void* map_alpha = nullptr;
   long long map_key[6] = {0, 0, 0, 0, 0, 0};
 };
 
@@ -409,11 +410,15 @@ struct ColKernelParams {
   CUtensorMap in_map;  // panel intermediate {32 floats, np slots, panels}, box {8, 256, 1}, 32-byte swizzle
   CUtensorMap out_a;   // u8 image {row bytes, rows, frames}, box {16, st_rows_a, 1}
   CUtensorMap out_b;   // same tensor, box {16, st_rows_b, 1}
+  CUtensorMap alpha_a; // the INPUT image with the boxes of out_a / out_b: RGBA with alpha passed through (P.alpha_src)
+  CUtensorMap alpha_b;
 };
 
 constexpr size_t kColSmem = (size_t)kColRegion + kColTileBytes + kTableBytes + 16;
 
-template <bool PAIR_MAJOR>
+// ALPHA_KEEP (RGBA with alpha passed through) is a template parameter: as a run-time flag its branches in the epilogue
+// cost the plain kernel 1.6 % (0.5667 -> 0.5760 ms per 8K step)
+template <bool PAIR_MAJOR, bool ALPHA_KEEP>
 __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid_constant__ ColKernelParams K) {
   extern __shared__ __align__(1024) unsigned char smem_raw[];
   unsigned char* region = smem_raw;                 // landing area (first 64 KB), then the warps' exchange slices
@@ -453,8 +458,11 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
     }
   };
 
+  uint64_t* bar2 = bar + 1;  // alpha pass-through: the item's strip of the input image has landed in the tile
+  constexpr bool alpha_keep = PAIR_MAJOR && ALPHA_KEEP;
   if (tid == 0) {
     mbar_init(bar, 1);
+    mbar_init(bar2, 1);
     fence_proxy_async();
   }
   load_tables(tw, gains, P.tw, P.gains, tid, kColWarps * 32);
@@ -463,7 +471,7 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
   unsigned it = blockIdx.x;
   if (tid == 0 && it < nitems) request(it);
   const float2* twl = tw + lane * kTwStride;
-  uint32_t parity = 0;
+  uint32_t parity = 0, parity2 = 0;
   for (; it < nitems; it += gridDim.x) {
     int f, unit, s;
     decode(it, f, unit, s);
@@ -483,9 +491,28 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
       if (tid == 0) bulk_wait_read<0>();  // the previous item's stores have read the tile
       fence_proxy_async();                // order this thread's exchange traffic before the next TMA writes
       __syncthreads();                    // exchanges done: the region is free, and so is the tile
-      if (tid == 0 && next < nitems) request(next);  // lands under the last DFT and the epilogue
+      if (tid == 0) {
+        if constexpr (alpha_keep) {
+          // RGBA, alpha not blurred: this item's [rows][16 bytes] strip of the INPUT image goes into the tile (the boxes
+          // of the stores below, rows past the image zero-filled); the epilogue then writes the three blurred bytes of
+          // every pixel around the alpha byte. In place this reads exactly the bytes the item's own stores overwrite.
+          mbar_expect_tx(bar2, (uint32_t)P.L * kColFloats);
+          const int c0 = unit * kColFloats;
+#pragma unroll 1
+          for (int b = 0; b < P.st_na; ++b)
+            tma_load_3d(tile + b * P.st_rows_a * kColFloats, &K.alpha_a, c0, s + b * P.st_rows_a, f, bar2);
+          if (P.st_rows_b)
+            tma_load_3d(tile + P.st_na * P.st_rows_a * kColFloats, &K.alpha_b, c0, s + P.st_na * P.st_rows_a, f, bar2);
+        }
+        if (next < nitems) request(next);  // lands under the last DFT and the epilogue
+      }
     });
-    col_to_tile(c, qc, s, P.sign_origin, P.pad, P.L, PAIR_MAJOR ? 4 * (w & 3) + 2 * (w >> 2) : 2 * w, lane, tile);
+    if constexpr (alpha_keep) {
+      mbar_wait(bar2, parity2);
+      parity2 ^= 1;
+    }
+    col_to_tile(c, qc, s, P.sign_origin, P.pad, P.L, PAIR_MAJOR ? 4 * (w & 3) + 2 * (w >> 2) : 2 * w, lane, tile,
+                alpha_keep && (w >> 2) == 1);
     fence_proxy_async();  // the tile writes become visible to the async proxy
     __syncthreads();
     if (tid == 0) {
@@ -864,11 +891,16 @@ cudaError_t launch_col(RowPlan* p, const ColLaunch& a, int num_sms, cudaStream_t
   P.qc = p->d_qc;
   P.tw = p->d_tw;
   P.gains = p->d_gains;
+  P.alpha_src = (a.C == 4 && a.blk.pair_major) ? a.alpha_src : nullptr;
+  if (P.alpha_src && ((reinterpret_cast<uintptr_t>(P.alpha_src) % 16) != 0 || (a.alpha_pitch % 16) != 0))
+    return cudaErrorNotSupported;  // TMA tiles of the input image
+  P.alpha_pitch = a.alpha_pitch;
 
   const long long panels_total = (long long)P.panels_per_frame * a.frames;
   const long long key[6] = {a.blk.np, panels_total, rows, a.out_pitch, a.out_frame_stride,
                             ((long long)a.frames << 40) | ((long long)a.blk.pair_major << 36) | (unsigned)a.W};
-  bool same = p->map_inter == a.inter && p->map_out == a.out;
+  const uint8_t* alpha_src = (a.C == 4 && a.blk.pair_major) ? a.alpha_src : nullptr;
+  bool same = p->map_inter == a.inter && p->map_out == a.out && p->map_alpha == alpha_src;
   for (int i = 0; i < 6; ++i) same = same && p->map_key[i] == key[i];
   if (!same) {
     const unsigned long long idims[3] = {32, (unsigned long long)a.blk.np, (unsigned long long)panels_total};
@@ -884,31 +916,49 @@ cudaError_t launch_col(RowPlan* p, const ColLaunch& a, int num_sms, cudaStream_t
       p->map_inter = nullptr;
       return cudaErrorNotSupported;
     }
+    if (alpha_src) {
+      // the input image seen through the boxes of the output tile (same geometry: a.alpha_pitch bytes per row)
+      const unsigned long long astr[2] = {(unsigned long long)a.alpha_pitch, (unsigned long long)a.alpha_pitch * (unsigned long long)rows};
+      if (!encode_tensor_map(&p->alpha_a, 1, 3, alpha_src, odims, astr, obox_a, 0) ||
+          !encode_tensor_map(&p->alpha_b, 1, 3, alpha_src, odims, astr, obox_b, 0)) {
+        p->map_inter = nullptr;
+        return cudaErrorNotSupported;
+      }
+    }
     p->map_inter = a.inter;
     p->map_out = a.out;
+    p->map_alpha = alpha_src;
     for (int i = 0; i < 6; ++i) p->map_key[i] = key[i];
   }
   K.in_map = p->in_map;
   K.out_a = p->out_a;
   K.out_b = p->out_b;
+  if (alpha_src) {
+    K.alpha_a = p->alpha_a;
+    K.alpha_b = p->alpha_b;
+  }
 
   std::call_once(cpd.once[device], [&] {
     cpd.per_sm[device] = 0;
-    cpd.err[device] = cudaFuncSetAttribute(ols_col_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kColSmem);
+    cpd.err[device] = cudaFuncSetAttribute(ols_col_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kColSmem);
     if (cpd.err[device] == cudaSuccess)
-      cpd.err[device] = cudaFuncSetAttribute(ols_col_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kColSmem);
+      cpd.err[device] = cudaFuncSetAttribute(ols_col_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kColSmem);
+    if (cpd.err[device] == cudaSuccess)
+      cpd.err[device] = cudaFuncSetAttribute(ols_col_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kColSmem);
     if (cpd.err[device] == cudaSuccess)
       cpd.err[device] =
-          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cpd.per_sm[device], ols_col_kernel<true>, kColWarps * 32, kColSmem);
+          cudaOccupancyMaxActiveBlocksPerMultiprocessor(&cpd.per_sm[device], ols_col_kernel<true, true>, kColWarps * 32, kColSmem);
     if (cpd.err[device] == cudaSuccess && cpd.per_sm[device] < 1) cpd.err[device] = cudaErrorLaunchOutOfResources;
   });
   if (cpd.err[device] != cudaSuccess) return cpd.err[device];
   long long grid = (long long)num_sms * cpd.per_sm[device];
   if (grid > P.nitems) grid = P.nitems;
-  if (a.blk.pair_major)
-    ols_col_kernel<true><<<(unsigned)grid, kColWarps * 32, kColSmem, stream>>>(K);
+  if (a.blk.pair_major && alpha_src)
+    ols_col_kernel<true, true><<<(unsigned)grid, kColWarps * 32, kColSmem, stream>>>(K);
+  else if (a.blk.pair_major)
+    ols_col_kernel<true, false><<<(unsigned)grid, kColWarps * 32, kColSmem, stream>>>(K);
   else
-    ols_col_kernel<false><<<(unsigned)grid, kColWarps * 32, kColSmem, stream>>>(K);
+    ols_col_kernel<false, false><<<(unsigned)grid, kColWarps * 32, kColSmem, stream>>>(K);
   count_launch();
   return cudaGetLastError();
 }

@@ -54,9 +54,8 @@ def test_headline_8k_device_path_vs_reference(gb, headline, alpha):
     mx, nd = _cmp(out, want[alpha])
     assert mx <= 1, f"max |delta| = {mx} LSB ({nd} bytes differ), kernels {kinds}"
     assert np.array_equal(out, out_inplace)
-    if alpha:
-        assert kinds == ("overlap_save_1024", "overlap_save_1024"), kinds  # the kernels of the headline number
-    else:
+    assert kinds == ("overlap_save_1024", "overlap_save_1024"), kinds  # the kernels of the headline number, both modes
+    if not alpha:
         assert np.array_equal(out[..., 3], img[..., 3])
 
 

@@ -92,3 +92,53 @@ def test_overlap_save_adversarial_patterns(gb, refcheck):
         out, inter, _ = _blur_device(gb, img, sigma, {"GBLUR_ROW_OLS": "1", "GBLUR_COL_OLS": "1"})
         want = refcheck.blur(img, sigma, True)
         assert np.abs(out.astype(np.int16) - want.astype(np.int16)).max() <= 1, pat
+
+
+@pytest.mark.parametrize("rows,cols,sigma", [(1500, 4100, 7.0), (160, 7680, 20.0), (2100, 1028, 0.4)])
+def test_rgba_alpha_passed_through_on_the_overlap_save_passes(gb, refcheck, rows, cols, sigma):
+    """RGBA with apply_to_alpha = false (the reference's command-line default, examples/desktop/main.cpp:80): all four
+    channels run through the block kernels and the column kernel puts the input's alpha byte back into its output tile
+    (csrc/ols_kernels.cu). Alpha must come back bit-identical (tests/test_gaussianblur.cpp:115-118), RGB within 1 LSB,
+    out of place and in place; sigma = 0.4 is the one-tap window (pad 0)."""
+    import torch
+
+    img = go.synth_u8((rows, cols, 4), rows * 5 + cols)
+    saved = {k: os.environ.get(k) for k in ("GBLUR_ROW_OLS", "GBLUR_COL_OLS")}
+    os.environ.update({"GBLUR_ROW_OLS": "1", "GBLUR_COL_OLS": "1"})
+    try:
+        plan = gb.Plan(rows, cols, 4, sigma)
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    d_in = torch.from_numpy(img).cuda()
+    d_out = torch.full_like(d_in, 0x5A)
+    plan.run_device(d_in, d_out, False)
+    torch.cuda.synchronize()
+    kinds = plan.last_kernels()
+    out = d_out.cpu().numpy()
+    inter = plan.dump_intermediate(False)
+    plan.run_device(d_in, d_in, False)  # in place: an item reads the alpha bytes it is about to overwrite
+    torch.cuda.synchronize()
+    out_inplace = d_in.cpu().numpy()
+    # a buffer that is not 16-byte aligned keeps the whole-line kernels (TMA tiles need the alignment) and the result
+    flat = torch.empty(img.size + 4, dtype=torch.uint8, device="cuda")
+    d_off = flat[4:].view(rows, cols, 4)
+    d_off.copy_(torch.from_numpy(img))
+    plan.run_device(d_off, d_off, False)
+    torch.cuda.synchronize()
+    kinds_off = plan.last_kernels()
+    out_off = d_off.cpu().numpy()
+    plan.close()
+    assert kinds == ("overlap_save_1024", "overlap_save_1024"), kinds
+    assert kinds_off[1] != "overlap_save_1024", kinds_off
+    want = refcheck.blur(img, sigma, False)
+    for name, got in (("out of place", out), ("in place", out_inplace), ("unaligned", out_off)):
+        assert np.array_equal(got[..., 3], img[..., 3]), f"{name}: alpha changed"
+        d = np.abs(got.astype(np.int16) - want.astype(np.int16))
+        assert d.max() <= 1, f"{name}: max |delta| = {d.max()} LSB"
+    assert np.array_equal(out, out_inplace)
+    got2 = inter.reshape(rows, cols, 3)[..., 2]
+    assert np.abs(got2 - refcheck.rowpass(img, 2, sigma)).max() < INTER_TOL

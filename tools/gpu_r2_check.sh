@@ -11,3 +11,5 @@ print({k:d.get(k) for k in ("value","ms_per_step","gpu_launches","kernels_ms")},
 print(d["secondary"]["band_32k_gray_sigma50"]["ms_per_step"], d["secondary"]["band_32k_gray_sigma50"]["phases_ms"], d.get("parity_check",{}).get("max_abs"))
 PY
 timeout 300 python tools/step_time.py 2>/dev/null | tee gpurun_out/chk/step_time.json
+STEP_ALPHA=0 timeout 300 python tools/step_time.py 2>/dev/null | tee gpurun_out/chk/step_time_alpha0.json
+STEP_ALPHA=0 GBLUR_OLS_ALPHA_RESTORE=0 timeout 300 python tools/step_time.py 2>/dev/null | tee gpurun_out/chk/step_time_alpha0_wholeline.json

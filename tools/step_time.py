@@ -11,20 +11,21 @@ import libgaussianblur_b200 as gb
 from libgaussianblur_b200.synth import synth_u8
 
 rows, cols, ch, sigma = 4320, 7680, 4, 20.0
+alpha = os.environ.get("STEP_ALPHA", "1") != "0"
 plan = gb.Plan(rows, cols, ch, sigma)
 d_in = torch.from_numpy(synth_u8((rows, cols, ch), 0x1235)).cuda()
 d_out = torch.empty_like(d_in)
 for _ in range(10):
-    plan.run_device(d_in, d_out, True)
+    plan.run_device(d_in, d_out, alpha)
 torch.cuda.synchronize()
 best = []
 for rep in range(3):
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(200):
-        plan.run_device(d_in, d_out, True)
+        plan.run_device(d_in, d_out, alpha)
     e1.record()
     torch.cuda.synchronize()
     best.append(e0.elapsed_time(e1) / 200)
-print(json.dumps({"knobs": {k: v for k, v in os.environ.items() if k.startswith("GBLUR_")}, "ms_per_step": best,
+print(json.dumps({"apply_to_alpha": alpha, "knobs": {k: v for k, v in os.environ.items() if k.startswith("GBLUR_")}, "ms_per_step": best,
                   "kernels": plan.last_kernels()}))
