@@ -430,8 +430,12 @@ __global__ void __launch_bounds__(kColWarps * 32, 2) ols_col_kernel(const __grid
   const int tid = threadIdx.x, w = tid >> 5, lane = tid & 31;
   float2* ex = reinterpret_cast<float2*>(region) + w * kExch;
 
-  // consecutive items = the blocks of one unit, then the neighbouring unit: the 2 * pad slots two blocks share and the
-  // 128-byte lines two units share are fetched by CTAs that run at the same time (second reader hits L2)
+  // consecutive items = the blocks of one unit, then the neighbouring unit, dealt out round-robin: at any moment the
+  // CTAs of the grid work on neighbouring units and blocks. Two units share every 32-byte sector of the OUTPUT rows and
+  // four units every 128-byte line of the panel rows, so their partners must be in flight together. (Measured: giving
+  // every CTA a contiguous run of items instead — to make the second fetch of the 2 * pad slots two blocks share an L2
+  // hit — took the kernel from 0.29 to 0.48 ms, DRAM reads from 612 MB to 1.39 GB and writes from 129 to 260 MB:
+  // half-written output sectors are read back, and every 32-byte box read pulls a whole line.)
   // (32-bit item arithmetic: launch_col refuses more than 2^31 items; a 64-bit division is ~70 instructions a thread)
   auto decode = [&](unsigned it, int& f, int& unit, int& s) {
     const unsigned fu = it / (unsigned)P.nblk;

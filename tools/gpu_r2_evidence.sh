@@ -20,4 +20,5 @@ ncu --set full --clock-control none --import-source on -k regex:ols_col_kernel -
     tools/ols_gpu_check 4320 7680 20 auto 0 > gpurun_out/ev/ncu_ols_col.log 2>&1
 ncu --set full --clock-control none -k regex:'altsum_rows_kernel|colsum_kernel|u_rowpass_kernel' -s 6 -c 3 -f -o gpurun_out/ev/prof_ols_pre \
     tools/ols_gpu_check 4320 7680 20 auto 0 > gpurun_out/ev/ncu_ols_pre.log 2>&1
-tail -2 gpurun_out/ev/ncu_ols_*.log; ls -la gpurun_out/ev/
+for f in gpurun_out/ev/ncu_ols_*.log; do tail -n 2 $f; done
+timeout 300 python tools/step_time.py 2>/dev/null | tee gpurun_out/ev/step_time.json
