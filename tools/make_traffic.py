@@ -31,7 +31,7 @@ def main(out, row_csv, col_csv, pre_csv):
         by.setdefault(k["kernel"].split("::")[-1], k)
     alt = by.get("altsum_rows_kernel")
     cs, ur = by.get("colsum_kernel"), by.get("u_rowpass_kernel")
-    src = "profiles/r02/ncu_full_ols_v4_summary.txt (ncu --set full --clock-control none, one launch each)"
+    src = "profiles/r02/ncu_full_ols_v5_summary.txt (ncu --set full --clock-control none, one launch each)"
     t = {
         "row_pass": {"traffic": int(row["read"] + row["write"] + (alt["read"] + alt["write"] if alt else 0)), "source": src,
                      "kernels": {row["kernel"]: int(row["read"] + row["write"]),
