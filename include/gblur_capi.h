@@ -80,7 +80,9 @@ int gblur_run_batch_device(gblur_plan* plan, const uint8_t* d_in, uint8_t* d_out
                            void* cuda_stream);
 
 /* Profiling hook: the same fused run restricted to stages = 1 (row pass into the plan's workspace),
- * 2 (column pass out of it) or 3 (both); lets bench.py time each kernel with CUDA events. */
+ * 2 (column pass out of it), 3 (both) or 4 (the column kernel alone: an overlap-save column pass reuses the column
+ * terms of its previous run on this plan, so only the block kernel is launched; otherwise the same as 2); lets bench.py
+ * time each kernel with CUDA events. */
 int gblur_run_stage_device(gblur_plan* plan, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
                            void* cuda_stream, int stages);
 

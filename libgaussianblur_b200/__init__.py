@@ -257,7 +257,8 @@ class Plan:
         return d_out
 
     def run_stage(self, stages: int, d_in, d_out=None, apply_to_alpha: bool = False, n_frames: int = 1, stream=None):
-        """Profiling hook: 1 = row pass only, 2 = column pass only, 3 = both (same kernels as run_device)."""
+        """Profiling hook: 1 = row pass only, 2 = column pass only, 3 = both (same kernels as run_device), 4 = the column
+        kernel alone (an overlap-save column pass reuses the column terms of its previous run on this plan)."""
         d_out = d_in if d_out is None else d_out
         _check(lib().gblur_run_stage_device(self._h, _ptr(d_in), _ptr(d_out), n_frames, int(bool(apply_to_alpha)),
                                             _stream_ptr(stream), stages))

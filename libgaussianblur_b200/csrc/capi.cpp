@@ -568,14 +568,17 @@ static int run_fused(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_f
     rc = run_rowpass(p, d_in, p->d_inter, c.pitch, n_frames, c.alpha, s, c.bp, 0, 0, 0, 0, n_frames == 1);
     if (rc != GBLUR_OK) return rc;
   }
-  if (!(stages & 2)) return GBLUR_OK;
+  // stages == 4: the column kernel alone — an overlap-save column pass reuses the column terms its last run on this
+  // plan left behind (same image), so the launch that is timed is the block kernel and nothing else
+  const bool col_kernel_only = stages == 4;
+  if (!(stages & 2) && !col_kernel_only) return GBLUR_OK;
   if (terms_forked) CU(cudaStreamWaitEvent(s, p->ev_join, 0));
   if (d_in != d_out && c.cp < p->channels)
     CU(launch_copy_channel(d_in, d_out, (long long)p->rows * p->cols * n_frames, p->channels, 3, s));
   // alpha restore: the column kernel takes the alpha bytes from the input image (d_out itself when the call is in place:
   // an item reads exactly the bytes it then overwrites); a stage-2-only call finds them in d_in as well
   return run_colpass(p, p->d_inter, c.pitch, d_out, (long long)p->cols * p->channels, n_frames, c.alpha, s, c.bp,
-                     0, 0, n_frames == 1 ? d_in : nullptr, !terms_forked, c.alpha_restore ? d_in : nullptr);
+                     0, 0, n_frames == 1 ? d_in : nullptr, !terms_forked && !col_kernel_only, c.alpha_restore ? d_in : nullptr);
 }
 
 int gblur_run_batch_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
@@ -585,7 +588,8 @@ int gblur_run_batch_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, i
 
 int gblur_run_stage_device(gblur_plan* p, const uint8_t* d_in, uint8_t* d_out, int n_frames, int apply_to_alpha,
                            void* cuda_stream, int stages) {
-  if (stages < 1 || stages > 3) return fail(GBLUR_E_INVALID, "stages must be 1 (row), 2 (column) or 3 (both)");
+  if (stages < 1 || stages > 4)
+    return fail(GBLUR_E_INVALID, "stages must be 1 (row pass), 2 (column pass), 3 (both) or 4 (column kernel alone)");
   return run_fused(p, d_in, d_out, n_frames, apply_to_alpha, cuda_stream, stages);
 }
 

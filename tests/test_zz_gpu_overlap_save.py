@@ -142,3 +142,34 @@ def test_rgba_alpha_passed_through_on_the_overlap_save_passes(gb, refcheck, rows
     assert np.array_equal(out, out_inplace)
     got2 = inter.reshape(rows, cols, 3)[..., 2]
     assert np.abs(got2 - refcheck.rowpass(img, 2, sigma)).max() < INTER_TOL
+
+
+def test_column_kernel_alone_stage_reuses_the_terms(gb):
+    """gblur_run_stage_device(stages = 4), the hook bench.py times the column block kernel with: after a full run on the
+    same image it launches ONE kernel (the column terms of the previous run are reused) and leaves the same bytes"""
+    import torch
+
+    img = go.synth_u8((1800, 4100, 4), 0x4321)
+    saved = {k: os.environ.get(k) for k in ("GBLUR_ROW_OLS", "GBLUR_COL_OLS")}
+    os.environ.update({"GBLUR_ROW_OLS": "1", "GBLUR_COL_OLS": "1"})
+    try:
+        plan = gb.Plan(1800, 4100, 4, 9.0)
+    finally:
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    d_in = torch.from_numpy(img).cuda()
+    d_out = torch.empty_like(d_in)
+    plan.run_device(d_in, d_out, True)
+    torch.cuda.synchronize()
+    want = d_out.cpu().numpy()
+    d_out2 = torch.zeros_like(d_in)
+    before = gb.launch_count()
+    plan.run_stage(4, d_in, d_out2, True)
+    torch.cuda.synchronize()
+    launches = gb.launch_count() - before
+    plan.close()
+    assert launches == 1
+    assert np.array_equal(d_out2.cpu().numpy(), want)
