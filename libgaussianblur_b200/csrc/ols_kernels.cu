@@ -291,7 +291,10 @@ __global__ void __launch_bounds__(128) colsum_kernel(const uint8_t* __restrict__
 }
 
 // 16 byte columns per thread (rows of whole 16-byte groups, 16-byte aligned). Measured in the fused 8K step, where this
-// kernel runs beside the row pass's own pre-kernel over the same input: 0.5785 -> 0.5690 ms per step.
+// kernel runs beside the row pass's own pre-kernel over the same input: 0.5785 -> 0.5690 ms per step. Rows per thread
+// swept afterwards (profiles/r02/colsum_variants.jsonl): 16 -> 0.610, 32 -> 0.581, 64 -> 0.5645, 128 -> 0.5636,
+// 256 -> 0.575 ms (the global atomics are the cost: fewer rows per thread = more of them); four row groups per CTA
+// that meet in shared memory before one atomic per column did not beat 64 rows per thread (0.5687).
 __global__ void __launch_bounds__(128) colsum16_kernel(const uint8_t* __restrict__ in, long long in_pitch, int groups16, int rows,
                                                        int pad, int* __restrict__ u, int row_begin, int row_end, int row_base) {
   const int x = blockIdx.x * 128 + threadIdx.x;
