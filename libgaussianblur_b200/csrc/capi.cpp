@@ -253,14 +253,8 @@ bool ols_col_wanted(const gblur_plan* p, int cp, int frames) {
     return false;
   if (((long long)p->cols * cp) % 16 || ((long long)p->full_cols * p->channels) % 16) return false;
   if (p->ols_col_mode == 1) return true;
-  // automatic: both passes must gain (the pair-major panel rows tie them together)
-  ColLaunch a{};
-  a.T = p->full_rows;
-  a.pad = p->sz.pad;
-  RowLaunch r{};
-  r.T = p->full_cols;
-  r.pad = p->sz.pad;
-  return p->ols_mode != 0 && ols::col_profitable(a, p->sz.n_colpass) && ols::row_profitable(r, p->sz.n_rowpass);
+  // automatic: the two passes together must gain (the pair-major panel rows tie them together)
+  return p->ols_mode != 0 && ols::both_profitable(p->full_cols, p->full_rows, p->sz.pad, p->sz.n_rowpass, p->sz.n_colpass);
 }
 
 // rows_sub > 0: only rows [row0, row0 + rows_sub) of a single frame (d_in / d_inter still point at row 0)

@@ -37,6 +37,9 @@ cudaError_t launch_row(RowPlan* p, const RowLaunch& a, int num_sms, cudaStream_t
 // boundaries, 16-byte aligned output rows
 bool col_eligible(const RowPlan* p, const ColLaunch& a);
 bool col_profitable(const ColLaunch& a, int n_ref_col);
+// both passes as overlap-save blocks (what the automatic rule of fused single-frame runs asks): row_len pixels per row,
+// col_len rows, the reference's transform lengths along a row / a column
+bool both_profitable(int row_len, int col_len, int pad, int n_ref_row, int n_ref_col);
 // The column terms of the reference's Nyquist behaviour, once per image (two launches: column sums of the u8 input =
 // the synthetic row u, then the row pass of u on one CTA). d_in / in_pitch: the image the intermediate comes from.
 cudaError_t launch_col_terms(RowPlan* p, const ColLaunch& a, const uint8_t* d_in, long long in_pitch, cudaStream_t stream);

@@ -788,6 +788,20 @@ bool col_eligible(const RowPlan* p, const ColLaunch& a) {
          a.T >= 1 && a.frames == 1;  // the column Nyquist terms are built from one frame so far
 }
 
+// Both passes as blocks (the pair-major / hole-free panel layout ties them together). Measured on B200, RGBA, against the
+// whole-line kernels (profiles/r02/gates.jsonl): 3840 x 2160 0.370 -> 0.181 ms (sigma 5 / 10), -> 0.189 ms at sigma 20
+// (blocks: 1.28 x and 1.33 x the reference's transform points), 2560 x 1440 0.179 -> 0.095 ms, but 1920 x 1080 sigma 5
+// 0.0615 -> 0.0712 ms: two blocks for 1080 rows against the reference's 1152 points, and too few items to fill the
+// persistent grids (2160 row items for 2368 warps). Rule: at least 3 Mpixel, both sides >= 1024, and neither pass more
+// than 1.6 x the reference's points (1.5 x where the whole line would need a thread-block cluster, as before).
+bool both_profitable(int row_len, int col_len, int pad, int n_ref_row, int n_ref_col) {
+  const int L = kNB - 2 * pad;
+  if (L < 1 || row_len < 1024 || col_len < 1024 || n_ref_row < 1 || n_ref_col < 1) return false;
+  if ((long long)row_len * col_len < 3000000LL) return false;
+  const double rw = (double)((row_len + L - 1) / L) * kNB / n_ref_row, cw = (double)((col_len + L - 1) / L) * kNB / n_ref_col;
+  return rw <= (n_ref_row > 14000 ? 1.5 : 1.6) && cw <= (n_ref_col > 14000 ? 1.5 : 1.6);
+}
+
 bool col_profitable(const ColLaunch& a, int n_ref_col) {
   const int L = kNB - 2 * a.pad;
   if (L < 1 || a.T < 2048) return false;

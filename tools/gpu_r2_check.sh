@@ -13,3 +13,7 @@ PY
 timeout 300 python tools/step_time.py 2>/dev/null | tee gpurun_out/chk/step_time.json
 STEP_ALPHA=0 timeout 300 python tools/step_time.py 2>/dev/null | tee gpurun_out/chk/step_time_alpha0.json
 STEP_ALPHA=0 GBLUR_OLS_ALPHA_RESTORE=0 timeout 300 python tools/step_time.py 2>/dev/null | tee gpurun_out/chk/step_time_alpha0_wholeline.json
+for shape in "2160 3840 20" "2160 3840 10" "1440 2560 10" "1080 1920 5" "4096 4096 10"; do
+  set -- $shape
+  STEP_ROWS=$1 STEP_COLS=$2 STEP_SIGMA=$3 timeout 200 python tools/step_time.py 2>/dev/null | tee -a gpurun_out/chk/auto_rule.jsonl
+done

@@ -10,7 +10,8 @@ import torch
 import libgaussianblur_b200 as gb
 from libgaussianblur_b200.synth import synth_u8
 
-rows, cols, ch, sigma = 4320, 7680, 4, 20.0
+rows, cols, ch, sigma = (int(os.environ.get("STEP_ROWS", "4320")), int(os.environ.get("STEP_COLS", "7680")), 4,
+                          float(os.environ.get("STEP_SIGMA", "20")))
 alpha = os.environ.get("STEP_ALPHA", "1") != "0"
 plan = gb.Plan(rows, cols, ch, sigma)
 d_in = torch.from_numpy(synth_u8((rows, cols, ch), 0x1235)).cuda()
@@ -27,5 +28,5 @@ for rep in range(3):
     e1.record()
     torch.cuda.synchronize()
     best.append(e0.elapsed_time(e1) / 200)
-print(json.dumps({"apply_to_alpha": alpha, "knobs": {k: v for k, v in os.environ.items() if k.startswith("GBLUR_")}, "ms_per_step": best,
+print(json.dumps({"shape": [rows, cols, ch], "sigma": sigma, "apply_to_alpha": alpha, "knobs": {k: v for k, v in os.environ.items() if k.startswith("GBLUR_")}, "ms_per_step": best,
                   "kernels": plan.last_kernels()}))
