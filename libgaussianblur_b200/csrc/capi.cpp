@@ -167,6 +167,7 @@ BlockedLayout blocked_layout(const gblur_plan* p, int cp, bool ols_col = false) 
   b.padq = (c.cluster > 1 || ols_col) ? 0 : c.padq;
   // RGBA: written by the overlap-save row pass, read by the overlap-save column pass (one channel keeps natural order)
   b.pair_major = (ols_col && p->channels == 4) ? 1 : 0;
+  b.ols_pair = ols_col ? 1 : 0;
   b.rows_per_frame = p->full_rows;
   const long long panels = ((long long)p->cols * cp + 31) / 32;
   b.frame_stride = panels * b.np * 32;
@@ -286,7 +287,8 @@ int run_rowpass(gblur_plan* p, const uint8_t* d_in, float* d_inter, long long pi
   if (blk && blk->pair_major && !(p->ols_row && ols::row_eligible(p->ols_row, a)))
     return fail(GBLUR_E_UNSUPPORTED, "pair-major panel layout, but the overlap-save row pass is not eligible");
   if (p->ols_row && ols::row_eligible(p->ols_row, a) &&
-      ((blk && blk->pair_major) || p->ols_mode == 1 || (fused_single && ols::row_profitable(a, p->sz.n_rowpass)))) {
+      ((blk && (blk->pair_major || blk->ols_pair)) || p->ols_mode == 1 ||
+       (fused_single && ols::row_profitable(a, p->sz.n_rowpass)))) {
     // (Leaving a few SMs out of this persistent grid for the column-term kernels on the side stream was measured and
     // dropped: 0.5785 ms per 8K step with 0 SMs reserved, 0.5790 with 2, 0.5886 with 4 — profiles/r02/row_reserve.jsonl.)
     CU(ols::launch_row(p->ols_row, a, p->num_sms, s));

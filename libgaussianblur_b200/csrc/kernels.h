@@ -36,6 +36,7 @@ struct BlockedLayout {
   int np = 0;                  // slots per unit (column FFT length + bank padding slots)
   int padq = 0;                // column plan's padq
   int pair_major = 0;          // 1: panel rows ordered [pair][pixel][2] (overlap-save row AND column pass, ols_core.cuh)
+  int ols_pair = 0;            // the layout was chosen for the overlap-save column pass: the row pass runs as blocks as well
   int slot_origin = 0;         // halo-sharded runs: the buffer holds the padded-column slots [slot_origin, slot_origin + np)
   int rows_per_frame = 0;
   long long frame_stride = 0;  // floats per frame = panels * np * 32

@@ -10,11 +10,14 @@ import torch
 import libgaussianblur_b200 as gb
 from libgaussianblur_b200.synth import synth_u8
 
-rows, cols, ch, sigma = (int(os.environ.get("STEP_ROWS", "4320")), int(os.environ.get("STEP_COLS", "7680")), 4,
+rows, cols, ch, sigma = (int(os.environ.get("STEP_ROWS", "4320")), int(os.environ.get("STEP_COLS", "7680")),
+                          int(os.environ.get("STEP_CH", "4")),
                           float(os.environ.get("STEP_SIGMA", "20")))
 alpha = os.environ.get("STEP_ALPHA", "1") != "0"
 plan = gb.Plan(rows, cols, ch, sigma)
 d_in = torch.from_numpy(synth_u8((rows, cols, ch), 0x1235)).cuda()
+if ch == 1:
+    alpha = False
 d_out = torch.empty_like(d_in)
 for _ in range(10):
     plan.run_device(d_in, d_out, alpha)
