@@ -215,7 +215,11 @@ extern "C" int ols_emulate_rowpass_c(const uint8_t* in, int rows, int T, int C, 
 // emulated as a copy into the landing area under the 64-byte swizzle (col_landing_offset is the kernel's own map of it),
 // the eight warps run the kernel's lane functions, and the TMA tile stores as a clipped copy of the u8 tile.
 // in / out: rows x cols RGBA u8, cols a multiple of 4. Returns 0 or a negative code.
-static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksize, int n_row, int n_col, uint8_t* out) {
+// alpha_keep: RGBA with alpha passed through (ols_col_kernel<true, true>): the item's strip of the INPUT image is put into
+// the tile first (the kernel's TMA tile loads, rows past the image zero-filled) and the (B, A) warps write only their
+// first byte.
+static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksize, int n_row, int n_col, uint8_t* out,
+                        bool alpha_keep = false) {
   constexpr int CW = ols::kColWarps;
   const std::vector<float> taps = host::gaussian_taps(sigma, ksize);
   const ols::HostTables tb = ols::build_tables(taps, n_row, n_col);
@@ -327,11 +331,19 @@ static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int 
       for (int w = 0; w < CW; ++w)
         for (int lane = 0; lane < 32; ++lane) ols::read_col(regs[w][lane], lane, w, region);
       std::memset(tile, 0xEE, ols::kColTileBytes);
+      if (alpha_keep)
+        for (int k = 0; k < L; ++k) {
+          if (s + k < rows)
+            std::memcpy(tile + (size_t)k * ols::kColFloats, in + (size_t)(s + k) * T * 4 + (size_t)unit * ols::kColFloats,
+                        ols::kColFloats);
+          else
+            std::memset(tile + (size_t)k * ols::kColFloats, 0, ols::kColFloats);
+        }
       for (int w = 0; w < CW; ++w) {
         passes(regs[w], reinterpret_cast<float2*>(region) + w * ols::kExch);
         for (int lane = 0; lane < 32; ++lane)
           ols::col_to_tile(regs[w][lane], qc[((size_t)unit * 4 + (w & 3)) * 2 + (w >> 2)], s, 0, pad, L,
-                           4 * (w & 3) + 2 * (w >> 2), lane, tile);
+                           4 * (w & 3) + 2 * (w >> 2), lane, tile, alpha_keep && (w >> 2) == 1);
       }
       // the tile stores: rows [s, s + L) clipped to the image
       for (int k = 0; k < L && s + k < rows; ++k)
@@ -344,4 +356,9 @@ static int emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int 
 extern "C" int ols_emulate_blur(const uint8_t* in, int rows, int cols, float sigma, int ksize, int n_row, int n_col,
                                 uint8_t* out) {
   return emulate_blur(in, rows, cols, sigma, ksize, n_row, n_col, out);
+}
+
+extern "C" int ols_emulate_blur_keep_alpha(const uint8_t* in, int rows, int cols, float sigma, int ksize, int n_row, int n_col,
+                                           uint8_t* out) {
+  return emulate_blur(in, rows, cols, sigma, ksize, n_row, n_col, out, true);
 }

@@ -174,13 +174,16 @@ def emu_blur(emu, tmp_path_factory):
     lib = ctypes.CDLL(str(so))
     lib.ols_emulate_blur.restype = ctypes.c_int
 
-    def run(img, sigma):
+    lib.ols_emulate_blur_keep_alpha.restype = ctypes.c_int
+
+    def run(img, sigma, keep_alpha=False):
         rows, cols, _ = img.shape
         ksize, pad, n_rp, n_cp, _, _ = go.plan_sizes(rows, cols, sigma)
         img = np.ascontiguousarray(img)
         out = np.empty_like(img)
-        rc = lib.ols_emulate_blur(img.ctypes.data_as(ctypes.c_void_p), rows, cols, ctypes.c_float(sigma), ksize, n_rp, n_cp,
-                                  out.ctypes.data_as(ctypes.c_void_p))
+        fn = lib.ols_emulate_blur_keep_alpha if keep_alpha else lib.ols_emulate_blur
+        rc = fn(img.ctypes.data_as(ctypes.c_void_p), rows, cols, ctypes.c_float(sigma), ksize, n_rp, n_cp,
+                out.ctypes.data_as(ctypes.c_void_p))
         assert rc == 0, rc
         return out
 
@@ -222,3 +225,20 @@ def test_emulated_two_pass_blur_adversarial(emu_blur, pattern):
     out = emu_blur(img, sigma)
     want = go.gaussianblur(img, sigma, True)
     assert np.abs(out.astype(int) - want.astype(int)).max() <= 1
+
+
+@pytest.mark.parametrize("rows,cols,sigma", [(1100, 72, 20.0), (895, 68, 20.0), (300, 132, 5.0)])
+def test_emulated_blur_with_alpha_passed_through(emu_blur, rows, cols, sigma):
+    """RGBA with apply_to_alpha = false on the block kernels (ols_col_kernel<true, true>): all four channels are
+    transformed, the item's strip of the input image lands in the output tile first and the (B, A) warps write only
+    their B byte — alpha comes back bit-identical (the reference's own check, tests/test_gaussianblur.cpp:115-118), the
+    colour channels within 1 LSB of the reference's three-channel result"""
+    img = go.synth_u8((rows, cols, 4), 0x3A + rows)
+    out = emu_blur(img, sigma, keep_alpha=True)
+    assert np.array_equal(out[..., 3], img[..., 3])
+    want = go.gaussianblur(img, sigma, False)
+    assert np.abs(out[..., :3].astype(int) - want[..., :3].astype(int)).max() <= 1
+    if ref_lib.available():
+        ref = ref_lib.gaussianblur(img, sigma, False)
+        assert np.array_equal(ref[..., 3], img[..., 3])
+        assert np.abs(out.astype(int) - ref.astype(int)).max() <= 1
