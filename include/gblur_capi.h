@@ -225,6 +225,10 @@ int gblur_host_spectrum(float sigma, int ksize, int n, float* out_ordered);
 int gblur_host_line_plan(int n, int* radices, int* nstages, int* nseq, int* static_kernel, long long* smem_bytes,
                          int* nthreads);
 int gblur_host_kperm(float sigma, int ksize, int n, float* out_n);
+/* Which kernel family a single-frame fused run takes when nothing is forced: *blocks = 2 both passes as overlap-save
+ * 1024-sample blocks, 1 the row pass only, 0 whole-line transforms of the reference's length (DESIGN.md section 2,
+ * "Selection"; buffers that are not 16-byte aligned keep the whole-line kernels regardless). */
+int gblur_host_kernel_choice(int rows, int cols, int channels, float sigma, int apply_to_alpha, int* blocks);
 
 #ifdef __cplusplus
 }

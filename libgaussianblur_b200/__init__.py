@@ -23,7 +23,7 @@ from . import build as _build
 
 __all__ = ["Plan", "GblurError", "lib", "gaussianblur", "gaussianblur_module", "host_plan_sizes", "host_spectrum",
            "host_line_plan", "host_kperm", "host_taps", "launch_count", "EXPORTED_SYMBOLS", "HaloPlan", "halo_partition",
-           "colsum_noalloc", "NOALLOC_MAX_ROW_BYTES"]
+           "colsum_noalloc", "NOALLOC_MAX_ROW_BYTES", "host_kernel_choice"]
 
 # every symbol include/gblur_capi.h declares
 EXPORTED_SYMBOLS = [
@@ -38,6 +38,7 @@ EXPORTED_SYMBOLS = [
     "gblur_colsum_noalloc",
     "gblur_dump_intermediate", "gblur_launch_count", "gblur_last_error", "gblur_device_count",
     "gblur_host_plan_sizes", "gblur_host_taps", "gblur_host_spectrum", "gblur_host_line_plan", "gblur_host_kperm",
+    "gblur_host_kernel_choice",
 ]
 
 
@@ -111,6 +112,7 @@ def lib():
         "gblur_host_spectrum": (C.c_int, [C.c_float, C.c_int, C.c_int, fp]),
         "gblur_host_line_plan": (C.c_int, [C.c_int, ip, ip, ip, ip, C.POINTER(C.c_longlong), ip]),
         "gblur_host_kperm": (C.c_int, [C.c_float, C.c_int, C.c_int, fp]),
+        "gblur_host_kernel_choice": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_float, C.c_int, ip]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -164,6 +166,13 @@ def host_kperm(sigma: float, ksize: int, n: int) -> np.ndarray:
     out = np.empty(n, dtype=np.float32)
     _check(lib().gblur_host_kperm(sigma, ksize, n, out.ctypes.data_as(C.POINTER(C.c_float))))
     return out
+
+
+def host_kernel_choice(rows: int, cols: int, channels: int, sigma: float, apply_to_alpha: bool = True) -> int:
+    """2: both passes run as overlap-save blocks, 1: the row pass only, 0: whole-line transforms (host only)."""
+    v = C.c_int()
+    _check(lib().gblur_host_kernel_choice(rows, cols, channels, sigma, int(bool(apply_to_alpha)), C.byref(v)))
+    return v.value
 
 
 # ---------------------------------------------------------------------------------------------

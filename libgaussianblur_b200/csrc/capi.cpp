@@ -1375,4 +1375,29 @@ int gblur_host_kperm(float sigma, int ksize, int n, float* out_n) {
   return GBLUR_OK;
 }
 
+/* Which kernel family a single-frame fused run of this shape takes when nothing is forced (no device needed; the same
+ * rule gblur_run_* applies, apart from the 16-byte alignment of the caller's buffers and the GBLUR_*_OLS overrides):
+ * *blocks = 2 both passes as overlap-save blocks, 1 the row pass only, 0 whole-line transforms of the reference's length. */
+int gblur_host_kernel_choice(int rows, int cols, int channels, float sigma, int apply_to_alpha, int* blocks) {
+  if (!blocks) return fail(GBLUR_E_INVALID, "null out");
+  if (rows < 1 || cols < 1 || !(sigma > 0.f)) return fail(GBLUR_E_INVALID, "bad shape or sigma");
+  if (channels != 1 && channels != 3 && channels != 4) return fail(GBLUR_E_INVALID, "Unsupported number of channels");
+  const host::Sizes sz = host::plan_sizes(rows, cols, sigma);
+  *blocks = 0;
+  (void)apply_to_alpha;  // RGBA runs all four channels through the blocks either way (alpha restored in the epilogue)
+  if (sz.pad > 256 /* ols::kMaxPad */ || channels == 3) return GBLUR_OK;
+  const bool groups16 = ((long long)cols * channels) % 16 == 0;  // TMA tiles / staged rows want whole 16-byte groups
+  if (groups16 && ols::both_profitable(cols, rows, sz.pad, sz.n_rowpass, sz.n_colpass)) {
+    *blocks = 2;
+    return GBLUR_OK;
+  }
+  if (channels == 1 && !groups16) return GBLUR_OK;
+  RowLaunch r{};
+  r.T = cols;
+  r.pad = sz.pad;
+  r.C = channels;
+  if ((channels == 1 || (channels == 4 && apply_to_alpha)) && ols::row_profitable(r, sz.n_rowpass)) *blocks = 1;
+  return GBLUR_OK;
+}
+
 }  // extern "C"

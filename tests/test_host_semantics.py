@@ -153,3 +153,30 @@ def test_pybind_module_surface(gb):
     img.data = list(range(12))
     m.gaussianblur(image=img, sigma=0.0, apply_to_alpha=False)
     assert list(img.data) == list(range(12))
+
+
+def test_automatic_kernel_choice_table():
+    """gblur_host_kernel_choice: the rule that picks overlap-save blocks (2 = both passes, 1 = row pass only) or
+    whole-line transforms (0) for a single-frame run, pinned at the shapes it was measured on (B200,
+    profiles/r02/gates.jsonl, auto_rule.jsonl, gates_c1.jsonl): GPU runs report the same through last_kernels()."""
+    import libgaussianblur_b200 as gb
+
+    table = [
+        ((4320, 7680, 4, 20.0, True), 2),     # the headline image
+        ((4320, 7680, 4, 20.0, False), 2),    # alpha passed through: four channels through the blocks + alpha restore
+        ((2160, 3840, 4, 10.0, True), 2),     # 0.370 -> 0.181 ms
+        ((2160, 3840, 4, 20.0, True), 2),     # blocks transform 1.28 x / 1.33 x the reference's points: still 2 x faster
+        ((1440, 2560, 4, 10.0, True), 2),     # 0.179 -> 0.095 ms
+        ((1080, 1920, 4, 5.0, True), 0),      # below 3 Mpixel: whole lines (0.0615 ms against 0.0712)
+        ((1080, 1920, 3, 10.0, False), 0),    # RGB: byte rows are forced-only
+        ((160, 7680, 4, 20.0, True), 1),      # too few rows for column blocks: wide rows still run as blocks
+        ((160, 7680, 4, 20.0, False), 0),
+        ((32768, 32768, 1, 50.0, False), 2),  # BASELINE.json config 4
+        ((4096, 4096, 1, 50.0, False), 2),    # 0.193 -> 0.127 ms
+        ((32768, 65536, 3, 150.0, False), 0), # config 5: pad 498 does not fit a 1024-sample block
+        ((8192, 8192, 4, 150.0, True), 0),
+        ((4320, 7681, 4, 20.0, True), 1),     # rows of 30724 bytes, not whole 16-byte groups: no TMA column blocks
+        ((4320, 7681, 1, 20.0, False), 0),
+    ]
+    for args, want in table:
+        assert gb.host_kernel_choice(*args) == want, args
